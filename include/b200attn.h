@@ -1,0 +1,218 @@
+/*
+ * b200attn.h — C ABI of the B200 (sm_100a) paged-attention decode path.
+ *
+ * This is the drop-in boundary underneath the Python shim that implements vLLM's
+ * AttentionBackend / AttentionImpl interface for vllm-omni's thinker/talker stages.
+ * There is no pre-existing FFI on this path in the reference (it is a Python class
+ * interface); every entry point below cites the reference/vLLM call it replaces.
+ *
+ * Conventions
+ *   - plain C symbols; all pointers are DEVICE pointers unless marked "host";
+ *   - strides are in ELEMENTS of the tensor's dtype (cache strides: elements of the
+ *     cache dtype, i.e. bf16 or u8);
+ *   - the caller owns every buffer; nothing is allocated, freed or synchronised here;
+ *   - every function enqueues on `stream` (a cudaStream_t passed as void*) and returns;
+ *   - return 0 = OK, negative = argument rejected on the host before any launch
+ *     (see B200ATTN_E*), positive = cudaError_t of the failed launch;
+ *   - no exceptions, no exit(); b200attn_last_error() gives a thread-local message;
+ *   - safe under CUDA-graph capture: no host sync, no allocation, grids depend only
+ *     on host arguments (sequence lengths are read on the device).
+ *
+ * Logical KV-cache layout (vLLM, `FlashAttentionBackend.get_kv_cache_shape`,
+ * vllm/v1/attention/backends/flash_attn.py; reader constraint in the reference:
+ * vllm_omni/distributed/omni_connectors/utils/kv_utils.py:417-450):
+ *     kv_cache[2, num_blocks, block_size, num_kv_heads, head_size]
+ * k_cache = kv_cache[0], v_cache = kv_cache[1]; the physical order is free and is
+ * described by (stride_block, stride_slot, stride_head); head_size is contiguous.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_ABI_VERSION 3
+
+#if defined(__GNUC__)
+#define B200ATTN_API __attribute__((visibility("default")))
+#else
+#define B200ATTN_API
+#endif
+
+/* kv_dtype */
+#define B200ATTN_KV_BF16 0
+#define B200ATTN_KV_FP8_E4M3 1
+
+/* host-side argument errors (returned negated) */
+#define B200ATTN_EINVAL 1      /* bad pointer / size / stride / alignment          */
+#define B200ATTN_EUNSUPPORTED 2 /* shape or dtype this build has no kernel for       */
+#define B200ATTN_EWORKSPACE 3  /* workspace too small for the requested split count */
+#define B200ATTN_EDRIVER 4     /* CUDA driver entry point (tensor-map encode) failed */
+
+/* decode kernel variants (for the ncu sweeps; 0 is what the backend uses) */
+#define B200ATTN_VARIANT_AUTO 0
+#define B200ATTN_VARIANT_TMA 1      /* persistent, TMA-staged pages, mbarrier ring       */
+#define B200ATTN_VARIANT_CPASYNC 2  /* one CTA per work item, cp.async-staged pages      */
+
+B200ATTN_API int b200attn_abi_version(void);
+B200ATTN_API const char* b200attn_last_error(void); /* host string, thread-local */
+
+/* Number of SMs of the current device (cached); <=0 on error. */
+B200ATTN_API int b200attn_num_sms(void);
+
+/*
+ * KV-cache write. Replaces vLLM `reshape_and_cache_flash`
+ * (vllm/_custom_ops.py:2591-2610, called from
+ * FlashAttentionImpl.do_kv_cache_update, vllm/v1/attention/backends/flash_attn.py:850-883;
+ * semantics restated in vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:44-124).
+ *
+ * For every token t < num_tokens with slot = slot_mapping[t] >= 0:
+ *     block = slot / block_size, off = slot % block_size
+ *     k_cache[block, off, h, :] = key[t, h, :]      (bf16: bit copy)
+ *     k_cache[block, off, h, :] = e4m3_satfinite(float(key[t,h,:]) / k_scale[h or 0])
+ * and the same for value / v_cache / v_scale. slot < 0 => token skipped.
+ * key/value: bf16 [>=num_tokens, num_kv_heads, head_size], token and head strides given
+ * (they are slices of the fused qkv projection output in the reference's model code,
+ * vllm_omni/model_executor/models/qwen2_5_omni/qwen2_old.py:146-156).
+ * scale_numel: 1 (per-tensor) or num_kv_heads (per-head); scales are device f32.
+ */
+B200ATTN_API int b200attn_reshape_and_cache(
+    const void* key, const void* value,
+    int64_t key_stride_tok, int64_t key_stride_head,
+    int64_t value_stride_tok, int64_t value_stride_head,
+    void* k_cache, void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    const int64_t* slot_mapping, int32_t num_tokens,
+    int32_t num_kv_heads, int32_t head_size, int32_t block_size, int64_t num_blocks,
+    int32_t kv_dtype,
+    const float* k_scale, const float* v_scale, int32_t scale_numel,
+    void* stream);
+
+/*
+ * Split-K heuristic used when num_splits == 0 (exported so the host shim can size the
+ * workspace and so tests can pin it). Pure host arithmetic.
+ */
+B200ATTN_API int32_t b200attn_decode_num_splits(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                   int32_t max_seq_len, int32_t num_sms);
+
+/* Bytes of split-K workspace for (max_batch, num_q_heads, head_size, max_splits). */
+B200ATTN_API size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads,
+                                       int32_t head_size, int32_t max_splits);
+
+/*
+ * Paged decode attention (query length 1 per sequence). Replaces the decode branch of
+ * AttentionImpl.forward in the reference's stock backends
+ * (vllm/v1/attention/backends/flashinfer.py:1694-1822 — TRT-LLM-gen decode, and
+ *  vllm/v1/attention/backends/flash_attn.py:758-819 — flash_attn_varlen_func with
+ *  block_table/seqused_k) plus their split-KV combine.
+ *
+ * For each sequence b < batch and query head h:
+ *     kvh = h / (num_q_heads / num_kv_heads)
+ *     K, V = cache[block_table[b, 0:ceil(S_b/bs)]] flattened, first S_b = seq_lens[b] rows
+ *     out[b, h, :] = softmax(softmax_scale * q[b,h,:] . K[:, kvh, :]^T) . V[:, kvh, :]
+ *     lse[b, h]    = log(sum_j exp(softmax_scale * q.k_j))       (natural log; optional)
+ * fp8 caches are dequantised as float(e4m3) * scale[kvh or 0].
+ * S_b == 0 => out row = 0, lse = -inf.
+ *
+ * Two launches: the split-K partial kernel (online softmax per KV range, fp32 partial
+ * outputs + LSE into `workspace`) and the LSE-reduce kernel. Sequences that fit in one
+ * split are written to `out` directly by the first kernel.
+ *
+ * q:   bf16 [batch, num_q_heads, head_size], token stride given, head stride = head_size
+ * out: bf16 [batch, num_q_heads, head_size], token stride given
+ * block_table: i32 [batch, >=ceil(max_seq_len/bs)], row stride given
+ * seq_lens: i32 [batch] (device; never read on the host)
+ * max_seq_len: host upper bound used for the split heuristic only (longer sequences
+ *              are still handled correctly: the last split extends to S_b)
+ * num_splits: 0 = heuristic, else forced (1 = no split, no reduce launch)
+ * variant: B200ATTN_VARIANT_*
+ */
+B200ATTN_API int b200attn_paged_decode(
+    const void* q, int64_t q_stride_tok,
+    const void* k_cache, const void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    int64_t num_blocks,
+    void* out, int64_t out_stride_tok,
+    float* lse,
+    const int32_t* block_table, int64_t block_table_stride,
+    const int32_t* seq_lens, int32_t batch, int32_t max_seq_len,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+    float softmax_scale, int32_t kv_dtype,
+    const float* k_scale, const float* v_scale, int32_t scale_numel,
+    int32_t num_splits, int32_t variant,
+    void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * The two launches of b200attn_paged_decode, exported separately for profiling sweeps.
+ * `num_splits` must be >= 1 here. partial writes workspace (and `out` rows whose sequence
+ * needs a single split); reduce merges rows that used > 1 split.
+ */
+B200ATTN_API int b200attn_paged_decode_partial(
+    const void* q, int64_t q_stride_tok,
+    const void* k_cache, const void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    int64_t num_blocks,
+    void* out, int64_t out_stride_tok,
+    float* lse,
+    const int32_t* block_table, int64_t block_table_stride,
+    const int32_t* seq_lens, int32_t batch, int32_t max_seq_len,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+    float softmax_scale, int32_t kv_dtype,
+    const float* k_scale, const float* v_scale, int32_t scale_numel,
+    int32_t num_splits, int32_t variant,
+    void* workspace, size_t workspace_bytes, void* stream);
+
+B200ATTN_API int b200attn_lse_reduce(
+    void* out, int64_t out_stride_tok, float* lse,
+    const int32_t* seq_lens, int32_t batch, int32_t max_seq_len,
+    int32_t num_q_heads, int32_t head_size,
+    int32_t num_splits,
+    const void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Causal varlen attention over the paged cache for query length >= 1 (prefill, chunked
+ * prefill / extend, mixed batches). Correctness path for the non-decode tokens a
+ * registered backend also receives (vllm/v1/attention/backends/flash_attn.py:758-819 with
+ * max_query_len > 1). The new tokens' K/V must already be in the cache.
+ *
+ * Sequence b owns query rows [query_start_loc[b], query_start_loc[b+1]); with
+ * q_len = their count and S_b = seq_lens[b], query i (0-based) attends to cache
+ * positions j <= S_b - q_len + i.
+ */
+B200ATTN_API int b200attn_paged_prefill(
+    const void* q, int64_t q_stride_tok,
+    const void* k_cache, const void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    int64_t num_blocks,
+    void* out, int64_t out_stride_tok,
+    const int32_t* block_table, int64_t block_table_stride,
+    const int32_t* seq_lens, const int32_t* query_start_loc,
+    int32_t batch, int32_t num_tokens, int32_t max_query_len,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+    float softmax_scale, int32_t kv_dtype,
+    const float* k_scale, const float* v_scale, int32_t scale_numel,
+    void* stream);
+
+/*
+ * Gather of one request's cached K or V rows into a dense [seq_len, num_kv_heads,
+ * head_size] tensor (same dtype as the cache, no dequantisation). Device-side twin of the
+ * reference's per-layer Python indexing in
+ * vllm_omni/distributed/omni_connectors/kv_transfer_manager.py:829-846
+ * (key_blocks[block_ids].flatten(0,1)[:seq_len]).
+ * block_ids: i32 [num_block_ids] (device).
+ */
+B200ATTN_API int b200attn_gather_kv(
+    const void* cache, int64_t cache_stride_block, int64_t cache_stride_slot,
+    int64_t cache_stride_head, int64_t num_blocks,
+    const int32_t* block_ids, int32_t num_block_ids, int32_t seq_len,
+    int32_t num_kv_heads, int32_t head_size, int32_t block_size, int32_t kv_dtype,
+    void* dst, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

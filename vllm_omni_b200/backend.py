@@ -1,0 +1,248 @@
+"""vLLM AttentionBackend / MetadataBuilder / AttentionImpl for the B200 paged-attention path.
+
+This is layer 1 of the drop-in boundary: the class interface vLLM's `Attention`
+layer calls for vllm-omni's thinker and talker stages
+(vllm/model_executor/layers/attention/attention.py:437-529 -> `impl.do_kv_cache_update`,
+`impl.forward`; caller of both: vllm_omni/worker/gpu_ar_model_runner.py:421-520).
+All arithmetic happens in libb200attn.so through `ops`; there is no other code path.
+
+Selection: `register_backend(AttentionBackendEnum.CUSTOM, ...)` (see `plugin.py`) plus
+`attention_backend: CUSTOM` in the stage's engine_args — the same knob the reference forces for
+ROCm in vllm_omni/engine/stage_init_utils.py:282-293.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import ClassVar
+
+import torch
+from vllm.v1.attention.backend import (
+    AttentionBackend,
+    AttentionCGSupport,
+    AttentionImpl,
+    AttentionMetadataBuilder,
+    AttentionType,
+    CommonAttentionMetadata,
+    MultipleOf,
+)
+from vllm.v1.attention.backends.utils import split_decodes_and_prefills
+
+from . import layout, ops
+
+BACKEND_PATH = "vllm_omni_b200.backend.B200AttentionBackend"
+
+
+class B200AttentionBackend(AttentionBackend):
+    """Static capability + layout contract (vllm/v1/attention/backend.py:55-343)."""
+
+    supported_dtypes: ClassVar[list[torch.dtype]] = [torch.bfloat16]
+    supported_kv_cache_dtypes: ClassVar[list[str]] = ["auto", "bfloat16", "fp8", "fp8_e4m3"]
+    # the cache write is a separate call (unified_kv_cache_update), as for FLASH_ATTN
+    forward_includes_kv_cache_update: bool = False
+
+    @staticmethod
+    def get_name() -> str:
+        # Attention.__init__ does AttentionBackendEnum[backend.get_name()] (attention.py:386)
+        return "CUSTOM"
+
+    @staticmethod
+    def get_impl_cls() -> type["B200AttentionImpl"]:
+        return B200AttentionImpl
+
+    @staticmethod
+    def get_builder_cls() -> type["B200AttentionMetadataBuilder"]:
+        return B200AttentionMetadataBuilder
+
+    @staticmethod
+    def get_supported_kernel_block_sizes() -> list[int | MultipleOf]:
+        return [MultipleOf(16)]
+
+    @staticmethod
+    def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int,
+                           cache_dtype_str: str = "auto") -> tuple[int, ...]:
+        return layout.kv_cache_shape(num_blocks, block_size, num_kv_heads, head_size)
+
+    @staticmethod
+    def get_kv_cache_stride_order(include_num_layers_dimension: bool = False) -> tuple[int, ...]:
+        if include_num_layers_dimension:
+            # (num_blocks, num_kv_heads, num_layers, 2, block_size, head_size)
+            return (2, 4, 0, 1, 3, 5)
+        return layout.KV_CACHE_STRIDE_ORDER
+
+    @classmethod
+    def get_supported_head_sizes(cls) -> list[int]:
+        return [128]
+
+    @classmethod
+    def supports_per_head_quant_scales(cls) -> bool:
+        return True
+
+    @classmethod
+    def supports_compute_capability(cls, capability) -> bool:
+        return capability.major == 10
+
+    @classmethod
+    def supports_attn_type(cls, attn_type: str) -> bool:
+        return attn_type == AttentionType.DECODER
+
+
+@dataclass
+class B200AttentionMetadata:
+    """Per-step metadata, shared by all layers of a KV-cache group (model: FlashAttentionMetadata,
+    vllm/v1/attention/backends/flash_attn.py:222-256). The batch is ordered decodes first."""
+
+    num_actual_tokens: int
+    max_query_len: int
+    query_start_loc: torch.Tensor
+    max_seq_len: int
+    seq_lens: torch.Tensor
+    block_table: torch.Tensor
+    slot_mapping: torch.Tensor
+    num_decodes: int
+    num_decode_tokens: int
+    num_prefills: int
+    num_prefill_tokens: int
+    # prefill slice, rebased so that row 0 is the first prefill token
+    prefill_query_start_loc: torch.Tensor | None
+    prefill_max_query_len: int
+    decode_num_splits: int
+    workspace: ops.DecodeWorkspace
+    causal: bool = True
+
+
+class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadata]):
+    """Builds B200AttentionMetadata once per step (vllm/v1/attention/backend.py:516-663).
+
+    No host sync and no device allocation that a captured graph could outlive: the split-K
+    workspace is allocated once here for the largest decode batch. Deliberately has neither a
+    `scheduler_metadata` nor a `max_num_splits` attribute, so the reference's patch in
+    vllm_omni/worker/gpu_model_runner.py:63-75 leaves it alone.
+    """
+
+    _cudagraph_support: ClassVar[AttentionCGSupport] = AttentionCGSupport.UNIFORM_SINGLE_TOKEN_DECODE
+    reorder_batch_threshold: int = 1
+
+    def __init__(self, kv_cache_spec, layer_names, vllm_config, device):
+        super().__init__(kv_cache_spec, layer_names, vllm_config, device)
+        mc, pc = vllm_config.model_config, vllm_config.parallel_config
+        self.num_heads_q = mc.get_num_attention_heads(pc)
+        self.num_heads_kv = mc.get_num_kv_heads(pc)
+        self.head_size = mc.get_head_size()
+        self.block_size = kv_cache_spec.block_size
+        self.max_model_len = mc.max_model_len
+        self.max_num_seqs = vllm_config.scheduler_config.max_num_seqs
+        self._sms = ops.num_sms()
+        nbytes = 0
+        for b in _batch_sizes(self.max_num_seqs):
+            s = ops.decode_num_splits(b, self.num_heads_q, self.num_heads_kv, self.max_model_len, self._sms)
+            nbytes = max(nbytes, ops.decode_workspace_bytes(b, self.num_heads_q, self.head_size, s))
+        self.workspace = ops.DecodeWorkspace(device, nbytes)
+
+    def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
+              fast_build: bool = False) -> B200AttentionMetadata:
+        cam = common_attn_metadata
+        nd, np_, ndt, npt = split_decodes_and_prefills(cam, decode_threshold=1)
+        splits = 1
+        if nd > 0:
+            splits = ops.decode_num_splits(nd, self.num_heads_q, self.num_heads_kv, cam.max_seq_len,
+                                           self._sms)
+            while splits > 1 and ops.decode_workspace_bytes(
+                    nd, self.num_heads_q, self.head_size, splits) > self.workspace.nbytes:
+                splits -= 1
+        pqsl, pmax = None, 0
+        if np_ > 0:
+            pqsl = cam.query_start_loc[nd:] - ndt
+            cpu = cam.query_start_loc_cpu
+            pmax = int((cpu[nd + 1:] - cpu[nd:-1]).max()) if nd > 0 else cam.max_query_len
+        return B200AttentionMetadata(
+            num_actual_tokens=cam.num_actual_tokens, max_query_len=cam.max_query_len,
+            query_start_loc=cam.query_start_loc, max_seq_len=cam.max_seq_len, seq_lens=cam.seq_lens,
+            block_table=cam.block_table_tensor, slot_mapping=cam.slot_mapping, num_decodes=nd,
+            num_decode_tokens=ndt, num_prefills=np_, num_prefill_tokens=npt,
+            prefill_query_start_loc=pqsl, prefill_max_query_len=pmax, decode_num_splits=splits,
+            workspace=self.workspace, causal=cam.causal)
+
+
+def _batch_sizes(max_num_seqs: int):
+    b = 1
+    while b < max_num_seqs:
+        yield b
+        b = b + 1 if b < 64 else b + 8
+    yield max(1, max_num_seqs)
+
+
+class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
+    """KV-cache write + paged attention through the C ABI (vllm/v1/attention/backend.py:763-841)."""
+
+    can_return_lse_for_decode: bool = True
+    # keep Q in bf16: Attention.forward then skips the fp8 query quantisation (attention.py:461-471)
+    supports_quant_query_input: bool = False
+
+    def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int | None = None,
+                 alibi_slopes: list[float] | None = None, sliding_window: int | None = None,
+                 kv_cache_dtype: str = "auto", logits_soft_cap: float | None = None,
+                 attn_type: str = AttentionType.DECODER,
+                 kv_sharing_target_layer_name: str | None = None, **extra) -> None:
+        self.num_heads = num_heads
+        self.head_size = head_size
+        self.scale = float(scale)
+        self.num_kv_heads = num_kv_heads if num_kv_heads is not None else num_heads
+        self.kv_cache_dtype = kv_cache_dtype
+        self.kv_sharing_target_layer_name = kv_sharing_target_layer_name
+        self.attn_type = attn_type
+        unsupported = []
+        if alibi_slopes is not None:
+            unsupported.append("alibi_slopes")
+        if sliding_window is not None:
+            unsupported.append("sliding_window")
+        if logits_soft_cap:
+            unsupported.append("logits_soft_cap")
+        if extra.get("sinks") is not None:
+            unsupported.append("sinks")
+        if attn_type != AttentionType.DECODER:
+            unsupported.append(f"attn_type={attn_type}")
+        if self.num_heads % self.num_kv_heads != 0:
+            unsupported.append("num_heads not a multiple of num_kv_heads")
+        if unsupported:
+            raise NotImplementedError(f"B200AttentionImpl does not support: {', '.join(unsupported)}")
+        self._kv_code = ops.kv_dtype_code(kv_cache_dtype)
+
+    # ------------------------------------------------------------------ cache write
+    def do_kv_cache_update(self, layer, key: torch.Tensor, value: torch.Tensor,
+                           kv_cache: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+        """`key`/`value` may be padded past slot_mapping (flash_attn.py:850-883): the token count is
+        slot_mapping.shape[0]. Skipped when this layer shares another layer's cache."""
+        if self.kv_sharing_target_layer_name is not None:
+            return
+        k_cache, v_cache = ops.split_kv_cache(kv_cache)
+        ops.reshape_and_cache(key, value, k_cache, v_cache, slot_mapping, self._kv_code,
+                              getattr(layer, "_k_scale", None), getattr(layer, "_v_scale", None))
+
+    # ------------------------------------------------------------------ attention
+    def forward(self, layer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                kv_cache: torch.Tensor, attn_metadata: B200AttentionMetadata,
+                output: torch.Tensor, output_scale: torch.Tensor | None = None,
+                output_block_scale: torch.Tensor | None = None) -> torch.Tensor:
+        if output_scale is not None or output_block_scale is not None:
+            raise NotImplementedError("fused output quantization is not supported by B200AttentionImpl")
+        if attn_metadata is None:  # profiling run
+            return output.fill_(0)
+        md = attn_metadata
+        k_cache, v_cache = ops.split_kv_cache(kv_cache)
+        q = query.view(-1, self.num_heads, self.head_size)
+        out = output.view(-1, self.num_heads, self.head_size)
+        k_scale = getattr(layer, "_k_scale", None)
+        v_scale = getattr(layer, "_v_scale", None)
+        nd, ndt = md.num_decodes, md.num_decode_tokens
+        if nd > 0:
+            ops.paged_decode(q[:ndt], k_cache, v_cache, md.block_table, md.seq_lens, md.max_seq_len,
+                             self.scale, out=out[:ndt], kv_cache_dtype=self._kv_code,
+                             k_scale=k_scale, v_scale=v_scale, num_splits=md.decode_num_splits,
+                             workspace=md.workspace)
+        if md.num_prefills > 0:
+            n = md.num_actual_tokens
+            ops.paged_prefill(q[ndt:n], k_cache, v_cache, md.block_table[nd:], md.seq_lens[nd:],
+                              md.prefill_query_start_loc, md.prefill_max_query_len, self.scale,
+                              out=out[ndt:n], kv_cache_dtype=self._kv_code, k_scale=k_scale,
+                              v_scale=v_scale)
+        return output

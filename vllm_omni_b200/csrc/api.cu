@@ -1,0 +1,499 @@
+// C ABI of libb200attn.so (include/b200attn.h): host-side validation, split-K heuristic,
+// TMA tensor-map encoding and kernel launches. No torch types, no allocation, no sync.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/b200attn.h"
+#include "kernels.h"
+
+using namespace b200;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return -code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+  return static_cast<int>(e);
+}
+
+int cached_num_sms() {
+  static thread_local int cached_dev = -1;
+  static thread_local int cached_sms = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (dev != cached_dev) {
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    cached_dev = dev;
+    cached_sms = sms;
+  }
+  return cached_sms;
+}
+
+bool env_flag(const char* name, bool dflt) {
+  const char* v = getenv(name);
+  if (v == nullptr || *v == '\0') return dflt;
+  return !(v[0] == '0' || v[0] == 'n' || v[0] == 'N' || v[0] == 'f' || v[0] == 'F');
+}
+
+// ---------------------------------------------------------------------------------------------
+// tensor maps
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &p, 12000, cudaEnableDefault,
+                                         &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+struct KvMapKey {
+  const void* ptr;
+  int64_t sb, ss, sh, nb;
+  int32_t hkv, bs, fp8;
+  bool operator==(const KvMapKey& o) const {
+    return ptr == o.ptr && sb == o.sb && ss == o.ss && sh == o.sh && nb == o.nb && hkv == o.hkv &&
+           bs == o.bs && fp8 == o.fp8;
+  }
+};
+struct KvMapEntry {
+  KvMapKey key;
+  CUtensorMap map;
+  CoordPerm perm;
+  bool valid;
+};
+constexpr int kMapCache = 256;  // >= 2 maps x layers of a model; direct-mapped by pointer hash
+thread_local KvMapEntry g_maps[kMapCache];
+
+// Encode (or fetch) the 4-D tensor map of one cache tensor: dims sorted by stride
+// (head_size, then slot/head/block in ascending stride order), box = 64 x 16 tokens x 1 x 1
+// (128 x 16 for e4m3), SWIZZLE_128B.
+int get_kv_map(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv,
+               int32_t bs, int32_t hd, bool fp8, const CUtensorMap** out_map, CoordPerm* out_perm) {
+  KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, fp8 ? 1 : 0};
+  const size_t slot = (reinterpret_cast<uintptr_t>(ptr) >> 8) % kMapCache;
+  KvMapEntry& e = g_maps[slot];
+  if (e.valid && e.key == key) {
+    *out_map = &e.map;
+    *out_perm = e.perm;
+    return 0;
+  }
+  EncodeTiledFn enc = get_encode_fn();
+  if (enc == nullptr) return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled entry point not found");
+  const int64_t es = fp8 ? 1 : 2;
+  // logical dims: 0 = slot, 1 = head, 2 = block
+  int64_t size[3] = {bs, hkv, nb};
+  int64_t stride[3] = {ss * es, sh * es, sb * es};
+  // a size-1 dimension may carry any stride: give it one that keeps the order canonical
+  if (hkv == 1) stride[1] = stride[0] * bs;
+  if (nb == 1) stride[2] = (stride[1] * hkv > stride[0] * bs) ? stride[1] * hkv : stride[0] * bs;
+  int order[3] = {0, 1, 2};
+  for (int i = 0; i < 3; ++i)
+    for (int j = i + 1; j < 3; ++j)
+      if (stride[order[j]] < stride[order[i]]) {
+        int t = order[i];
+        order[i] = order[j];
+        order[j] = t;
+      }
+  cuuint64_t gdim[4] = {static_cast<cuuint64_t>(hd), 0, 0, 0};
+  cuuint64_t gstr[3] = {0, 0, 0};
+  cuuint32_t box[4] = {static_cast<cuuint32_t>(fp8 ? 128 : 64), 1, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  for (int i = 0; i < 3; ++i) {
+    const int d = order[i];
+    gdim[i + 1] = static_cast<cuuint64_t>(size[d]);
+    gstr[i] = static_cast<cuuint64_t>(stride[d]);
+    if (stride[d] <= 0 || (stride[d] % 16) != 0)
+      return fail(B200ATTN_EINVAL, "cache stride %lld B of dim %d is not a positive multiple of 16",
+                  static_cast<long long>(stride[d]), d);
+    if (d == 0) box[i + 1] = kTileTokens;
+  }
+  CUresult r = enc(&e.map, fp8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                   const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    e.valid = false;
+    return fail(B200ATTN_EDRIVER,
+                "cuTensorMapEncodeTiled failed (%d): dims [%llu,%llu,%llu,%llu] strides [%llu,%llu,%llu]",
+                static_cast<int>(r), (unsigned long long)gdim[0], (unsigned long long)gdim[1],
+                (unsigned long long)gdim[2], (unsigned long long)gdim[3], (unsigned long long)gstr[0],
+                (unsigned long long)gstr[1], (unsigned long long)gstr[2]);
+  }
+  e.key = key;
+  e.perm = CoordPerm{order[0], order[1], order[2]};
+  e.valid = true;
+  *out_map = &e.map;
+  *out_perm = e.perm;
+  return 0;
+}
+
+int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64_t ss, int64_t sh,
+                     int64_t nb, int32_t hkv, int32_t hd, int32_t bs, int32_t kv_dtype) {
+  if (k_cache == nullptr || v_cache == nullptr) return fail(B200ATTN_EINVAL, "null cache pointer");
+  if (kv_dtype != B200ATTN_KV_BF16 && kv_dtype != B200ATTN_KV_FP8_E4M3)
+    return fail(B200ATTN_EINVAL, "kv_dtype %d unknown", kv_dtype);
+  if (hd != kHeadDim) return fail(B200ATTN_EUNSUPPORTED, "head_size %d not built (128 only)", hd);
+  if (bs <= 0 || (bs % 16) != 0)
+    return fail(B200ATTN_EUNSUPPORTED, "block_size %d is not a multiple of 16", bs);
+  if (hkv <= 0 || nb <= 0) return fail(B200ATTN_EINVAL, "num_kv_heads/num_blocks must be positive");
+  const int64_t es = kv_dtype == B200ATTN_KV_FP8_E4M3 ? 1 : 2;
+  if (ss <= 0 || (hkv > 1 && sh <= 0) || (nb > 1 && sb <= 0))
+    return fail(B200ATTN_EINVAL, "cache strides must be positive");
+  if (((ss * es) % 16) || (hkv > 1 && ((sh * es) % 16)) || (nb > 1 && ((sb * es) % 16)))
+    return fail(B200ATTN_EINVAL, "cache strides must be multiples of 16 bytes");
+  if ((reinterpret_cast<uintptr_t>(k_cache) % 16) || (reinterpret_cast<uintptr_t>(v_cache) % 16))
+    return fail(B200ATTN_EINVAL, "cache pointers must be 16-byte aligned");
+  return 0;
+}
+
+constexpr int kMaxSplits = 128;
+constexpr int kMinTilesPerSplit = 8;  // 128 tokens
+
+int tiles_per_split_for(int max_seq_len, int num_splits) {
+  int tiles = (max_seq_len + kTileTokens - 1) / kTileTokens;
+  if (tiles < 1) tiles = 1;
+  int c = (tiles + num_splits - 1) / num_splits;
+  c = (c + 1) & ~1;  // whole 2-tile stages
+  return c < 2 ? 2 : c;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200attn_abi_version(void) { return B200ATTN_ABI_VERSION; }
+const char* b200attn_last_error(void) { return g_err; }
+int b200attn_num_sms(void) { return cached_num_sms(); }
+
+int b200attn_reshape_and_cache(const void* key, const void* value, int64_t key_stride_tok,
+                               int64_t key_stride_head, int64_t value_stride_tok,
+                               int64_t value_stride_head, void* k_cache, void* v_cache,
+                               int64_t cache_stride_block, int64_t cache_stride_slot,
+                               int64_t cache_stride_head, const int64_t* slot_mapping,
+                               int32_t num_tokens, int32_t num_kv_heads, int32_t head_size,
+                               int32_t block_size, int64_t num_blocks, int32_t kv_dtype,
+                               const float* k_scale, const float* v_scale, int32_t scale_numel,
+                               void* stream) {
+  if (num_tokens < 0) return fail(B200ATTN_EINVAL, "num_tokens < 0");
+  if (num_tokens == 0) return 0;
+  if (key == nullptr || value == nullptr || slot_mapping == nullptr)
+    return fail(B200ATTN_EINVAL, "null key/value/slot_mapping");
+  if (int rc = check_cache_args(k_cache, v_cache, cache_stride_block, cache_stride_slot,
+                                cache_stride_head, num_blocks, num_kv_heads, head_size, block_size,
+                                kv_dtype))
+    return rc;
+  if ((key_stride_tok % 8) || (key_stride_head % 8) || (value_stride_tok % 8) ||
+      (value_stride_head % 8) || (reinterpret_cast<uintptr_t>(key) % 16) ||
+      (reinterpret_cast<uintptr_t>(value) % 16))
+    return fail(B200ATTN_EINVAL, "key/value rows must be 16-byte aligned");
+  const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
+  if (fp8) {
+    if (k_scale == nullptr || v_scale == nullptr) return fail(B200ATTN_EINVAL, "fp8 cache needs scales");
+    if (scale_numel != 1 && scale_numel != num_kv_heads)
+      return fail(B200ATTN_EINVAL, "scale_numel %d must be 1 or num_kv_heads", scale_numel);
+  }
+  const int sms = cached_num_sms();
+  if (sms <= 0) return cuda_fail(cudaGetLastError(), "device query");
+  CacheWriteParams p;
+  p.key = static_cast<const __nv_bfloat16*>(key);
+  p.value = static_cast<const __nv_bfloat16*>(value);
+  p.key_stride_tok = key_stride_tok;
+  p.key_stride_head = key_stride_head;
+  p.value_stride_tok = value_stride_tok;
+  p.value_stride_head = value_stride_head;
+  p.k_cache = static_cast<uint8_t*>(k_cache);
+  p.v_cache = static_cast<uint8_t*>(v_cache);
+  p.cs_block = cache_stride_block;
+  p.cs_slot = cache_stride_slot;
+  p.cs_head = cache_stride_head;
+  p.slot_mapping = slot_mapping;
+  p.num_tokens = num_tokens;
+  p.num_kv_heads = num_kv_heads;
+  p.head_size = head_size;
+  p.block_size = block_size;
+  p.num_blocks = num_blocks;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.scale_stride = scale_numel > 1 ? 1 : 0;
+  cudaError_t e = launch_cache_write(p, fp8, sms, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "cache_write launch");
+}
+
+int32_t b200attn_decode_num_splits(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                   int32_t max_seq_len, int32_t num_sms) {
+  if (batch <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || num_sms <= 0) return 1;
+  const int group = num_q_heads / num_kv_heads;
+  const int subgroups = (group + kHeadsPerItem - 1) / kHeadsPerItem;
+  const int64_t units = static_cast<int64_t>(batch) * num_kv_heads * subgroups;
+  int tiles = (max_seq_len + kTileTokens - 1) / kTileTokens;
+  if (tiles < 1) tiles = 1;
+  int smax = tiles / kMinTilesPerSplit;
+  if (smax < 1) smax = 1;
+  if (smax > kMaxSplits) smax = kMaxSplits;
+  // cost model of the persistent kernel: every CTA runs ceil(items / SMs) items of
+  // tiles_per_split tiles, plus a fixed per-item epilogue worth ~2 tiles of streaming
+  int best = 1;
+  int64_t best_cost = -1;
+  for (int s = 1; s <= smax; ++s) {
+    const int c = tiles_per_split_for(max_seq_len, s);
+    if (s > 1 && static_cast<int64_t>(s - 1) * c >= tiles) continue;  // last split would be empty
+    const int64_t rounds = (units * s + num_sms - 1) / num_sms;
+    const int64_t cost = rounds * (c + 2);
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best = s;
+    }
+  }
+  return best;
+}
+
+size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads, int32_t head_size,
+                                       int32_t max_splits) {
+  if (max_batch <= 0 || num_q_heads <= 0 || head_size <= 0 || max_splits <= 0) return 0;
+  const size_t rows = static_cast<size_t>(max_batch) * num_q_heads * max_splits;
+  return rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
+}
+
+static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t q_stride_tok,
+                       const void* k_cache, const void* v_cache, int64_t cache_stride_block,
+                       int64_t cache_stride_slot, int64_t cache_stride_head, int64_t num_blocks,
+                       void* out, int64_t out_stride_tok, float* lse, const int32_t* block_table,
+                       int64_t block_table_stride, const int32_t* seq_lens, int32_t batch,
+                       int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
+                       int32_t head_size, int32_t block_size, float softmax_scale, int32_t kv_dtype,
+                       const float* k_scale, const float* v_scale, int32_t scale_numel,
+                       int32_t num_splits, int32_t variant, void* workspace, size_t workspace_bytes,
+                       void* stream_v) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  if (batch < 0) return fail(B200ATTN_EINVAL, "batch < 0");
+  if (batch == 0) return 0;
+  if (out == nullptr || seq_lens == nullptr) return fail(B200ATTN_EINVAL, "null out/seq_lens");
+  if (num_q_heads <= 0 || num_kv_heads <= 0 || (num_q_heads % num_kv_heads) != 0)
+    return fail(B200ATTN_EINVAL, "num_q_heads %d not a multiple of num_kv_heads %d", num_q_heads,
+                num_kv_heads);
+  if (head_size != kHeadDim)
+    return fail(B200ATTN_EUNSUPPORTED, "head_size %d not built (128 only)", head_size);
+  if ((out_stride_tok % 4) || (reinterpret_cast<uintptr_t>(out) % 8))
+    return fail(B200ATTN_EINVAL, "out rows must be 8-byte aligned");
+  if (max_seq_len < 1) max_seq_len = 1;
+  const int sms = cached_num_sms();
+  if (sms <= 0) return cuda_fail(cudaGetLastError(), "device query");
+
+  if (num_splits < 0 || num_splits > kMaxSplits)
+    return fail(B200ATTN_EINVAL, "num_splits %d out of [0, %d]", num_splits, kMaxSplits);
+  if (num_splits == 0) {
+    num_splits = b200attn_decode_num_splits(batch, num_q_heads, num_kv_heads, max_seq_len, sms);
+    // never ask for more splits than the caller's workspace can hold
+    while (num_splits > 1 &&
+           b200attn_decode_workspace_bytes(batch, num_q_heads, head_size, num_splits) > workspace_bytes)
+      --num_splits;
+  }
+  float* part_o = nullptr;
+  float* part_lse = nullptr;
+  if (num_splits > 1) {
+    if (workspace == nullptr ||
+        b200attn_decode_workspace_bytes(batch, num_q_heads, head_size, num_splits) > workspace_bytes)
+      return fail(B200ATTN_EWORKSPACE, "workspace %zu B too small for %d splits (need %zu)",
+                  workspace_bytes, num_splits,
+                  b200attn_decode_workspace_bytes(batch, num_q_heads, head_size, num_splits));
+    if (reinterpret_cast<uintptr_t>(workspace) % 16)
+      return fail(B200ATTN_EINVAL, "workspace must be 16-byte aligned");
+    const size_t rows = static_cast<size_t>(batch) * num_q_heads * num_splits;
+    part_o = static_cast<float*>(workspace);
+    part_lse = part_o + rows * head_size;
+  }
+  const int tiles_per_split = tiles_per_split_for(max_seq_len, num_splits);
+
+  if (run_partial) {
+    if (q == nullptr || block_table == nullptr) return fail(B200ATTN_EINVAL, "null q/block_table");
+    if (int rc = check_cache_args(k_cache, v_cache, cache_stride_block, cache_stride_slot,
+                                  cache_stride_head, num_blocks, num_kv_heads, head_size, block_size,
+                                  kv_dtype))
+      return rc;
+    if ((q_stride_tok % 2) || (reinterpret_cast<uintptr_t>(q) % 4))
+      return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
+    const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
+    if (fp8) return fail(B200ATTN_EUNSUPPORTED, "fp8 KV decode is not built yet");
+    DecodeParams p;
+    p.q = static_cast<const __nv_bfloat16*>(q);
+    p.q_stride_tok = q_stride_tok;
+    p.k_cache = static_cast<const uint8_t*>(k_cache);
+    p.v_cache = static_cast<const uint8_t*>(v_cache);
+    p.cs_block = cache_stride_block;
+    p.cs_slot = cache_stride_slot;
+    p.cs_head = cache_stride_head;
+    p.out = static_cast<__nv_bfloat16*>(out);
+    p.out_stride_tok = out_stride_tok;
+    p.lse = lse;
+    p.block_table = block_table;
+    p.bt_stride = block_table_stride;
+    p.seq_lens = seq_lens;
+    p.batch = batch;
+    p.num_q_heads = num_q_heads;
+    p.num_kv_heads = num_kv_heads;
+    p.group = num_q_heads / num_kv_heads;
+    p.subgroups = (p.group + kHeadsPerItem - 1) / kHeadsPerItem;
+    p.block_size = block_size;
+    p.tiles_per_page = block_size / kTileTokens;
+    p.num_splits = num_splits;
+    p.tiles_per_split = tiles_per_split;
+    const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
+    if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
+    p.total_items = static_cast<int32_t>(items);
+    p.scale_log2 = softmax_scale * kLog2e;
+    p.k_scale = k_scale;
+    p.v_scale = v_scale;
+    p.scale_stride = scale_numel > 1 ? 1 : 0;
+    p.part_o = part_o;
+    p.part_lse = part_lse;
+
+    if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_TMA;
+    cudaError_t e;
+    if (variant == B200ATTN_VARIANT_TMA) {
+      const CUtensorMap *mk = nullptr, *mv = nullptr;
+      CoordPerm pk, pv;
+      if (int rc = get_kv_map(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head,
+                              num_blocks, num_kv_heads, block_size, head_size, fp8, &mk, &pk))
+        return rc;
+      // copy K's map before the second lookup can evict it from the direct-mapped cache
+      const CUtensorMap tm_k = *mk;
+      if (int rc = get_kv_map(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head,
+                              num_blocks, num_kv_heads, block_size, head_size, fp8, &mv, &pv))
+        return rc;
+      const int grid = static_cast<int>(items < sms ? items : sms);
+      e = launch_decode_tma(tm_k, *mv, pk, p, grid, stream);
+    } else if (variant == B200ATTN_VARIANT_CPASYNC) {
+      e = launch_decode_cpasync(p, stream);
+    } else {
+      return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "paged_decode partial launch");
+  }
+  if (run_reduce && num_splits > 1) {
+    const bool pdl = run_partial && env_flag("B200ATTN_PDL", true);
+    cudaError_t e = launch_lse_reduce(static_cast<__nv_bfloat16*>(out), out_stride_tok, lse, seq_lens,
+                                      batch, num_q_heads, num_splits, tiles_per_split, part_o,
+                                      part_lse, pdl, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "lse_reduce launch");
+  }
+  return 0;
+}
+
+int b200attn_paged_decode(const void* q, int64_t q_stride_tok, const void* k_cache,
+                          const void* v_cache, int64_t cache_stride_block, int64_t cache_stride_slot,
+                          int64_t cache_stride_head, int64_t num_blocks, void* out,
+                          int64_t out_stride_tok, float* lse, const int32_t* block_table,
+                          int64_t block_table_stride, const int32_t* seq_lens, int32_t batch,
+                          int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
+                          int32_t head_size, int32_t block_size, float softmax_scale,
+                          int32_t kv_dtype, const float* k_scale, const float* v_scale,
+                          int32_t scale_numel, int32_t num_splits, int32_t variant, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  return decode_impl(true, true, q, q_stride_tok, k_cache, v_cache, cache_stride_block,
+                     cache_stride_slot, cache_stride_head, num_blocks, out, out_stride_tok, lse,
+                     block_table, block_table_stride, seq_lens, batch, max_seq_len, num_q_heads,
+                     num_kv_heads, head_size, block_size, softmax_scale, kv_dtype, k_scale, v_scale,
+                     scale_numel, num_splits, variant, workspace, workspace_bytes, stream);
+}
+
+int b200attn_paged_decode_partial(const void* q, int64_t q_stride_tok, const void* k_cache,
+                                  const void* v_cache, int64_t cache_stride_block,
+                                  int64_t cache_stride_slot, int64_t cache_stride_head,
+                                  int64_t num_blocks, void* out, int64_t out_stride_tok, float* lse,
+                                  const int32_t* block_table, int64_t block_table_stride,
+                                  const int32_t* seq_lens, int32_t batch, int32_t max_seq_len,
+                                  int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size,
+                                  int32_t block_size, float softmax_scale, int32_t kv_dtype,
+                                  const float* k_scale, const float* v_scale, int32_t scale_numel,
+                                  int32_t num_splits, int32_t variant, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  if (num_splits < 1) return fail(B200ATTN_EINVAL, "partial needs an explicit num_splits >= 1");
+  return decode_impl(true, false, q, q_stride_tok, k_cache, v_cache, cache_stride_block,
+                     cache_stride_slot, cache_stride_head, num_blocks, out, out_stride_tok, lse,
+                     block_table, block_table_stride, seq_lens, batch, max_seq_len, num_q_heads,
+                     num_kv_heads, head_size, block_size, softmax_scale, kv_dtype, k_scale, v_scale,
+                     scale_numel, num_splits, variant, workspace, workspace_bytes, stream);
+}
+
+int b200attn_lse_reduce(void* out, int64_t out_stride_tok, float* lse, const int32_t* seq_lens,
+                        int32_t batch, int32_t max_seq_len, int32_t num_q_heads, int32_t head_size,
+                        int32_t num_splits, const void* workspace, size_t workspace_bytes,
+                        void* stream) {
+  if (num_splits < 1) return fail(B200ATTN_EINVAL, "reduce needs an explicit num_splits >= 1");
+  return decode_impl(false, true, nullptr, 0, nullptr, nullptr, 0, 0, 0, 0, out, out_stride_tok, lse,
+                     nullptr, 0, seq_lens, batch, max_seq_len, num_q_heads, num_q_heads, head_size, 16,
+                     1.f, B200ATTN_KV_BF16, nullptr, nullptr, 1, num_splits, 0,
+                     const_cast<void*>(workspace), workspace_bytes, stream);
+}
+
+int b200attn_paged_prefill(const void*, int64_t, const void*, const void*, int64_t, int64_t, int64_t,
+                           int64_t, void*, int64_t, const int32_t*, int64_t, const int32_t*,
+                           const int32_t*, int32_t, int32_t, int32_t, int32_t, int32_t, int32_t,
+                           int32_t, float, int32_t, const float*, const float*, int32_t, void*) {
+  return fail(B200ATTN_EUNSUPPORTED, "paged prefill is not built yet");
+}
+
+int b200attn_gather_kv(const void* cache, int64_t cache_stride_block, int64_t cache_stride_slot,
+                       int64_t cache_stride_head, int64_t num_blocks, const int32_t* block_ids,
+                       int32_t num_block_ids, int32_t seq_len, int32_t num_kv_heads,
+                       int32_t head_size, int32_t block_size, int32_t kv_dtype, void* dst,
+                       void* stream) {
+  if (seq_len < 0 || num_block_ids < 0) return fail(B200ATTN_EINVAL, "negative sizes");
+  if (seq_len == 0) return 0;
+  if (cache == nullptr || block_ids == nullptr || dst == nullptr)
+    return fail(B200ATTN_EINVAL, "null pointer");
+  const int eb = kv_dtype == B200ATTN_KV_FP8_E4M3 ? 1 : 2;
+  if ((head_size * eb) % 16 || block_size <= 0 || num_kv_heads <= 0)
+    return fail(B200ATTN_EINVAL, "rows must be multiples of 16 bytes");
+  if (((cache_stride_slot * eb) % 16) || ((cache_stride_head * eb) % 16) ||
+      ((cache_stride_block * eb) % 16) || (reinterpret_cast<uintptr_t>(cache) % 16) ||
+      (reinterpret_cast<uintptr_t>(dst) % 16))
+    return fail(B200ATTN_EINVAL, "cache/dst must be 16-byte aligned");
+  if (static_cast<int64_t>(num_block_ids) * block_size < seq_len)
+    return fail(B200ATTN_EINVAL, "seq_len %d exceeds %d blocks of %d", seq_len, num_block_ids,
+                block_size);
+  const int sms = cached_num_sms();
+  if (sms <= 0) return cuda_fail(cudaGetLastError(), "device query");
+  GatherParams p;
+  p.cache = static_cast<const uint8_t*>(cache);
+  p.cs_block = cache_stride_block;
+  p.cs_slot = cache_stride_slot;
+  p.cs_head = cache_stride_head;
+  p.num_blocks = num_blocks;
+  p.block_ids = block_ids;
+  p.num_block_ids = num_block_ids;
+  p.seq_len = seq_len;
+  p.num_kv_heads = num_kv_heads;
+  p.head_size = head_size;
+  p.block_size = block_size;
+  p.elem_bytes = eb;
+  p.dst = static_cast<uint8_t*>(dst);
+  cudaError_t e = launch_gather_kv(p, sms, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "gather_kv launch");
+}
+
+}  // extern "C"

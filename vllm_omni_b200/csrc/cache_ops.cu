@@ -1,0 +1,111 @@
+// KV-cache write (reshape_and_cache) and KV gather for sm_100a.
+//
+// Cache write: replaces vLLM `reshape_and_cache_flash`
+// (vllm/v1/attention/ops/triton_reshape_and_cache_flash.py:44-124 restates its semantics:
+//  negative slot skip :46-48, block/offset split :50-51, division by the scale :96,110).
+// Work unit = one (token, kv head, K|V) row of head_size elements; 16 lanes move one
+// 128-element row with 16-byte loads (bf16) and 16- or 8-byte stores (bf16 / e4m3).
+#include <cuda_fp8.h>
+
+#include "kernels.h"
+
+namespace b200 {
+
+template <bool FP8>
+__global__ void __launch_bounds__(256) cache_write_kernel(const CacheWriteParams p) {
+  const int lanes_per_row = p.head_size / 8;  // 8 bf16 = 16 B per lane; 16 for head_size 128
+  const int64_t rows = static_cast<int64_t>(p.num_tokens) * p.num_kv_heads * 2;
+  const int64_t total = rows * lanes_per_row;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % lanes_per_row);
+    int64_t r = i / lanes_per_row;
+    const int is_v = static_cast<int>(r & 1);
+    r >>= 1;
+    const int h = static_cast<int>(r % p.num_kv_heads);
+    const int64_t t = r / p.num_kv_heads;
+    const int64_t slot = __ldg(p.slot_mapping + t);
+    if (slot < 0) continue;  // padding token
+    const int64_t blk = slot / p.block_size;
+    const int off = static_cast<int>(slot % p.block_size);
+    if (blk >= p.num_blocks) continue;  // never write outside the cache
+    const __nv_bfloat16* src = is_v ? p.value + t * p.value_stride_tok + h * p.value_stride_head
+                                    : p.key + t * p.key_stride_tok + h * p.key_stride_head;
+    const int4 v = ldg_nc_v4(src + c * 8);
+    uint8_t* cache = is_v ? p.v_cache : p.k_cache;
+    const int64_t dst_el = blk * p.cs_block + static_cast<int64_t>(off) * p.cs_slot +
+                           static_cast<int64_t>(h) * p.cs_head + c * 8;
+    if constexpr (!FP8) {
+      *reinterpret_cast<int4*>(cache + dst_el * 2) = v;
+    } else {
+      const float scale = __ldg((is_v ? p.v_scale : p.k_scale) + h * p.scale_stride);
+      const __nv_bfloat162* xs = reinterpret_cast<const __nv_bfloat162*>(&v);
+      uint32_t w[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float2 a = __bfloat1622float2(xs[2 * j]);
+        const float2 b = __bfloat1622float2(xs[2 * j + 1]);
+        // IEEE division then RNE + saturate-to-finite e4m3: the same two steps as vLLM's
+        // fp8::scaled_convert (x / scale -> __nv_cvt_float_to_fp8(…, __NV_SATFINITE, __NV_E4M3)).
+        const uint32_t q0 = __nv_cvt_float_to_fp8(__fdiv_rn(a.x, scale), __NV_SATFINITE, __NV_E4M3);
+        const uint32_t q1 = __nv_cvt_float_to_fp8(__fdiv_rn(a.y, scale), __NV_SATFINITE, __NV_E4M3);
+        const uint32_t q2 = __nv_cvt_float_to_fp8(__fdiv_rn(b.x, scale), __NV_SATFINITE, __NV_E4M3);
+        const uint32_t q3 = __nv_cvt_float_to_fp8(__fdiv_rn(b.y, scale), __NV_SATFINITE, __NV_E4M3);
+        w[j] = q0 | (q1 << 8) | (q2 << 16) | (q3 << 24);
+      }
+      *reinterpret_cast<uint2*>(cache + dst_el) = make_uint2(w[0], w[1]);
+    }
+  }
+}
+
+cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms,
+                               cudaStream_t stream) {
+  const int64_t total =
+      static_cast<int64_t>(p.num_tokens) * p.num_kv_heads * 2 * (p.head_size / 8);
+  if (total == 0) return cudaSuccess;
+  const int threads = 256;
+  int64_t blocks = (total + threads - 1) / threads;
+  const int64_t cap = static_cast<int64_t>(num_sms) * 8;  // whole waves of resident CTAs
+  if (blocks > cap) blocks = cap;
+  if (fp8)
+    cache_write_kernel<true><<<static_cast<unsigned>(blocks), threads, 0, stream>>>(p);
+  else
+    cache_write_kernel<false><<<static_cast<unsigned>(blocks), threads, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+// Gather of one request's rows: dst[s, h, :] = cache[block_ids[s / bs], s % bs, h, :], s < seq_len.
+// Device twin of kv_transfer_manager.py:829-846 in the reference.
+__global__ void __launch_bounds__(256) gather_kv_kernel(const GatherParams p) {
+  const int row_bytes = p.head_size * p.elem_bytes;
+  const int chunks = row_bytes / 16;
+  const int64_t total = static_cast<int64_t>(p.seq_len) * p.num_kv_heads * chunks;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % chunks);
+    int64_t r = i / chunks;
+    const int h = static_cast<int>(r % p.num_kv_heads);
+    const int64_t s = r / p.num_kv_heads;
+    const int page = static_cast<int>(s / p.block_size);
+    if (page >= p.num_block_ids) continue;
+    const int64_t blk = __ldg(p.block_ids + page);
+    if (blk < 0 || blk >= p.num_blocks) continue;
+    const int64_t src_el = blk * p.cs_block + (s % p.block_size) * p.cs_slot +
+                           static_cast<int64_t>(h) * p.cs_head;
+    const int4 v = ldg_nc_v4(p.cache + src_el * p.elem_bytes + c * 16);
+    *reinterpret_cast<int4*>(p.dst + (s * p.num_kv_heads + h) * row_bytes + c * 16) = v;
+  }
+}
+
+cudaError_t launch_gather_kv(const GatherParams& p, int num_sms, cudaStream_t stream) {
+  const int64_t total = static_cast<int64_t>(p.seq_len) * p.num_kv_heads *
+                        (p.head_size * p.elem_bytes / 16);
+  if (total == 0) return cudaSuccess;
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = static_cast<int64_t>(num_sms) * 8;
+  if (blocks > cap) blocks = cap;
+  gather_kv_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace b200

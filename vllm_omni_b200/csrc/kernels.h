@@ -1,0 +1,54 @@
+// Internal launcher declarations shared by api.cu and the kernel translation units.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "decode_common.cuh"
+
+namespace b200 {
+
+// coordinate order of the 4-D KV tensor maps: which of (slot, head, block) is tensor-map
+// dimension 1, 2, 3 (dimension 0 is always head_size). Values: 0 = slot, 1 = head, 2 = block.
+struct CoordPerm {
+  int32_t dim1, dim2, dim3;
+};
+
+cudaError_t launch_decode_tma(const CUtensorMap& tm_k, const CUtensorMap& tm_v, CoordPerm perm,
+                              const DecodeParams& p, int grid, cudaStream_t stream);
+cudaError_t launch_decode_cpasync(const DecodeParams& p, cudaStream_t stream);
+size_t decode_tma_smem_bytes();
+size_t decode_cpasync_smem_bytes();
+
+cudaError_t launch_lse_reduce(__nv_bfloat16* out, int64_t out_stride_tok, float* lse,
+                              const int32_t* seq_lens, int batch, int num_q_heads, int num_splits,
+                              int tiles_per_split, const float* part_o, const float* part_lse,
+                              bool pdl, cudaStream_t stream);
+
+struct CacheWriteParams {
+  const __nv_bfloat16* key;
+  const __nv_bfloat16* value;
+  int64_t key_stride_tok, key_stride_head, value_stride_tok, value_stride_head;
+  uint8_t* k_cache;
+  uint8_t* v_cache;
+  int64_t cs_block, cs_slot, cs_head;
+  const int64_t* slot_mapping;
+  int32_t num_tokens, num_kv_heads, head_size, block_size;
+  int64_t num_blocks;
+  const float* k_scale;
+  const float* v_scale;
+  int32_t scale_stride;
+};
+cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms, cudaStream_t stream);
+
+struct GatherParams {
+  const uint8_t* cache;
+  int64_t cs_block, cs_slot, cs_head;  // elements
+  int64_t num_blocks;
+  const int32_t* block_ids;
+  int32_t num_block_ids, seq_len, num_kv_heads, head_size, block_size, elem_bytes;
+  uint8_t* dst;
+};
+cudaError_t launch_gather_kv(const GatherParams& p, int num_sms, cudaStream_t stream);
+
+}  // namespace b200
