@@ -1,0 +1,248 @@
+"""GPU parity: split-K paged decode through the C ABI vs the fp32 oracle.
+
+Tolerance (north_star): bf16 KV within 2e-3 relative of the fp32 SDPA oracle. The bound is applied
+to `excess_rel_err` = max(|x - ref| - half_ulp_bf16(ref)) / max|ref| — arithmetic error beyond the
+mandatory rounding of the bf16 output — and to the relative L2 error of the whole tensor.
+"""
+import math
+
+import pytest
+import torch
+
+from oracle import c_oracle, oracle
+from tests.helpers import cache_to_dev, excess_rel_err, make_case, rel_l2, to_dev
+from vllm_omni_b200 import _lib, layout, ops, workloads
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-3
+VARIANTS = [ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
+
+
+def run_device(c, variant=ops.VARIANT_AUTO, num_splits=0, want_lse=True, cache_dev=None, q_dev=None):
+    cache = cache_to_dev(c.kv_cache) if cache_dev is None else cache_dev
+    q = c.q.cuda() if q_dev is None else q_dev
+    B, hq, d = q.shape
+    lse = torch.full((B, hq), 123.0, dtype=torch.float32, device="cuda") if want_lse else None
+    out = torch.full((B, hq, d), 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.paged_decode(q, cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), c.max_seq_len,
+                     c.scale, out=out, lse=lse, kv_cache_dtype=c.kv_cache_dtype,
+                     k_scale=to_dev(c.k_scale), v_scale=to_dev(c.v_scale), num_splits=num_splits,
+                     variant=variant)
+    torch.cuda.synchronize()
+    return out, lse
+
+
+def check(c, out, lse, tol=TOL):
+    ref, ref_lse = c_oracle.paged_decode(c.q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens,
+                                         c.scale, c.fp8, c.k_scale, c.v_scale)
+    assert torch.isfinite(out.float()).all(), "non-finite output"
+    e, l2 = excess_rel_err(out, ref), rel_l2(out, ref)
+    assert e <= tol, f"excess rel err {e:.3e} > {tol}"
+    assert l2 <= tol, f"rel L2 err {l2:.3e} > {tol}"
+    if lse is not None:
+        got = lse.cpu()
+        fin = torch.isfinite(ref_lse)
+        assert torch.equal(torch.isfinite(got), fin)
+        assert torch.allclose(got[fin], ref_lse[fin], atol=2e-3, rtol=1e-4)
+    return e, l2
+
+
+LENS = [[1], [15], [16], [17], [31, 32, 33], [1, 100, 257, 64], [5, 0, 48, 0], [300, 129, 2, 511]]
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("lens", LENS)
+def test_decode_vs_oracle_small(lib, lens, variant):
+    c = make_case(lens, hq=8, hkv=1, seed=sum(lens))
+    for splits in (1, 0, 3):
+        out, lse = run_device(c, variant, splits)
+        check(c, out, lse)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+@pytest.mark.parametrize("hq,hkv", [(32, 4), (28, 4), (16, 2), (4, 1), (4, 4), (16, 1), (24, 2)])
+def test_decode_gqa_group_shapes(lib, hq, hkv, variant):
+    """G = 8 (Qwen3-Omni), 7 (Qwen2.5-Omni-7B), 4 (TP8 shard), 1 (MHA), 16 and 12 (two head sub-groups)."""
+    c = make_case([200, 77, 16], hq=hq, hkv=hkv, seed=hq * 10 + hkv)
+    out, lse = run_device(c, variant, 0)
+    check(c, out, lse)
+    out, lse = run_device(c, variant, 4)
+    check(c, out, lse)
+
+
+@pytest.mark.parametrize("bs", [32, 64, 128])
+def test_decode_larger_block_sizes(lib, bs):
+    c = make_case([bs + 3, 5 * bs, 17], hq=8, hkv=2, bs=bs, seed=bs)
+    for variant in VARIANTS:
+        out, lse = run_device(c, variant, 0)
+        check(c, out, lse)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_masked_tail_never_leaks_garbage(lib, variant):
+    """Unused slots of the last page (and unused pages) hold NaN bit patterns."""
+    c = make_case([1, 17, 45, 130], hq=8, hkv=2, seed=5, garbage_fill=True)
+    for splits in (1, 2):
+        out, lse = run_device(c, variant, splits)
+        check(c, out, lse)
+
+
+def test_forced_split_counts_agree(lib):
+    c = make_case([1000, 513, 64, 2048], hq=8, hkv=2, seed=8)
+    base, _ = run_device(c, ops.VARIANT_TMA, 1)
+    check(c, base, None)
+    for s in (2, 5, 16, 64, 128):
+        out, lse = run_device(c, ops.VARIANT_TMA, s)
+        check(c, out, lse)
+        assert rel_l2(out, base) < 6e-3  # two bf16 roundings of the same value
+
+
+def test_large_magnitude_scores_are_stable(lib):
+    """Softmax with |scale*q.k| up to ~50: the online max must keep exp() in range."""
+    c = make_case([300, 40], hq=8, hkv=2, seed=12, q_std=6.0, kv_std=3.0)
+    for variant in VARIANTS:
+        out, lse = run_device(c, variant, 3)
+        check(c, out, lse)
+
+
+def test_strided_q_and_out(lib):
+    """q is a slice of the fused qkv output; out rows may be strided too."""
+    c = make_case([90, 33], hq=8, hkv=2, seed=6)
+    qkv = torch.zeros(2, (8 + 4) * 128, dtype=torch.bfloat16, device="cuda")
+    qkv[:, : 8 * 128] = c.q.cuda().view(2, -1)
+    q = qkv[:, : 8 * 128].view(2, 8, 128)
+    assert q.stride(0) == 12 * 128
+    cache = cache_to_dev(c.kv_cache)
+    big = torch.zeros(2, 2, 8, 128, dtype=torch.bfloat16, device="cuda")
+    out = big[:, 1]
+    ops.paged_decode(q, cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), c.max_seq_len,
+                     c.scale, out=out)
+    check(c, out, None)
+    assert torch.count_nonzero(big[:, 0]) == 0
+
+
+def test_nhd_physical_layout_also_works(lib):
+    """The ABI is stride-generic: vLLM's default NHD order (slot stride > head stride) gives the
+    same result as the backend's own HND-paired order."""
+    c = make_case([100, 37], hq=8, hkv=2, seed=3)
+    nhd = torch.zeros(2, c.num_blocks, 16, 2, 128, dtype=torch.bfloat16, device="cuda")
+    nhd.copy_(c.kv_cache)
+    for variant in VARIANTS:
+        out, lse = run_device(c, variant, 2, cache_dev=nhd)
+        check(c, out, lse)
+
+
+def test_max_seq_len_hint_may_be_too_small(lib):
+    """max_seq_len only steers the split heuristic; the last split extends to the true length."""
+    c = make_case([700, 300], hq=8, hkv=2, seed=4)
+    cache = cache_to_dev(c.kv_cache)
+    out = torch.empty(2, 8, 128, dtype=torch.bfloat16, device="cuda")
+    ops.paged_decode(c.q.cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), 256,
+                     c.scale, out=out, num_splits=2)
+    check(c, out, None)
+
+
+@pytest.mark.parametrize("name,batch", [("cfg1", 1), ("cfg2", 4), ("cfg3", 3)])
+def test_named_shapes_full_context(lib, name, batch):
+    """BASELINE.json shapes at their full context length, batch reduced so the oracle runs in seconds."""
+    wl = workloads.WORKLOADS[name]
+    c = make_case([wl.ctx] * (batch - 1) + [wl.ctx - 5], hq=wl.total_q_heads, hkv=wl.total_kv_heads,
+                  seed={"cfg1": 101, "cfg2": 102, "cfg3": 103}[name])
+    for variant in VARIANTS:
+        out, lse = run_device(c, variant, 0)
+        e, l2 = check(c, out, lse)
+        print(f"{name} variant={variant} excess_rel_err={e:.2e} rel_l2={l2:.2e}")
+
+
+def test_abi_errors_surface_as_exceptions(lib):
+    c = make_case([100], hq=8, hkv=2, seed=1)
+    cache = cache_to_dev(c.kv_cache)
+    q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
+    tiny = ops.DecodeWorkspace("cuda", 256)
+    tiny.ensure = lambda n: None  # defeat the auto-grow: the C side must refuse
+    with pytest.raises(_lib.B200AttnError, match="EWORKSPACE"):
+        ops.paged_decode(q, cache[0], cache[1], bt, sl, 100, c.scale, num_splits=4, workspace=tiny)
+    bad = torch.zeros(2, 4, 16, 2, 64, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises((_lib.B200AttnError, ValueError)):
+        ops.paged_decode(torch.zeros(1, 8, 64, dtype=torch.bfloat16, device="cuda"), bad[0], bad[1], bt, sl,
+                         100, c.scale)
+    # the heuristic never exceeds what a caller-provided workspace can hold
+    small = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(1, 8, 128, 2))
+    small.ensure = lambda n: None
+    out = ops.paged_decode(q, cache[0], cache[1], bt, sl, 100000, c.scale, num_splits=0, workspace=small)
+    check(c, out, None)
+
+
+def test_cuda_graph_capture_and_replay(lib):
+    """Write + decode captured once; replays follow the DEVICE seq_lens/block_table/slot_mapping."""
+    c = make_case([130, 64, 257], hq=8, hkv=2, seed=21)
+    cache = cache_to_dev(c.kv_cache)
+    q = c.q.cuda()
+    bt, sl = c.block_table.cuda(), c.seq_lens.cuda()
+    out = torch.zeros(3, 8, 128, dtype=torch.bfloat16, device="cuda")
+    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(3, 8, 128, 4))
+    new_k = torch.zeros(3, 2, 128, dtype=torch.bfloat16, device="cuda")
+    slots = torch.full((3,), -1, dtype=torch.int64, device="cuda")
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        ops.reshape_and_cache(new_k, new_k, cache[0], cache[1], slots)
+        ops.paged_decode(q, cache[0], cache[1], bt, sl, 4096, c.scale, out=out, num_splits=4, workspace=ws)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        ops.reshape_and_cache(new_k, new_k, cache[0], cache[1], slots)
+        ops.paged_decode(q, cache[0], cache[1], bt, sl, 4096, c.scale, out=out, num_splits=4, workspace=ws)
+    g.replay()
+    torch.cuda.synchronize()
+    check(c, out, None)
+    # shorten the sequences on the device only and replay
+    c2 = make_case([130, 64, 257], hq=8, hkv=2, seed=21)
+    c2.seq_lens = torch.tensor([100, 1, 200], dtype=torch.int32)
+    sl.copy_(c2.seq_lens.cuda())
+    g.replay()
+    torch.cuda.synchronize()
+    check(c2, out, None)
+
+
+@pytest.mark.parametrize("ragged", [False, True])
+def test_full_size_properties_cfg3(lib, ragged):
+    """BASELINE cfg3 at full size (B=64, ctx 4096, 32q/4kv): properties that need no full oracle run."""
+    wl = workloads.WORKLOADS["cfg3"]
+    inp = workloads.make_decode_inputs(wl, "cuda", ragged=ragged)
+    cache = inp.kv_caches[0]
+    k_cache, v_cache = cache[0], cache[1]
+    ops.reshape_and_cache(inp.new_k, inp.new_v, k_cache, v_cache, inp.slot_mapping)
+    outs = {}
+    for variant in VARIANTS:
+        for s in (0, 1):
+            lse = torch.empty(wl.batch, wl.total_q_heads, dtype=torch.float32, device="cuda")
+            outs[(variant, s)] = (ops.paged_decode(inp.q, k_cache, v_cache, inp.block_table, inp.seq_lens,
+                                                   inp.max_seq_len, inp.softmax_scale, lse=lse,
+                                                   num_splits=s, variant=variant), lse)
+    torch.cuda.synchronize()
+    base, base_lse = outs[(ops.VARIANT_TMA, 0)]
+    assert torch.isfinite(base.float()).all()
+    # (1) the two staging variants agree (different warp counts => different merge order)
+    assert rel_l2(outs[(ops.VARIANT_CPASYNC, 0)][0], base) < 3e-3
+    assert torch.allclose(outs[(ops.VARIANT_CPASYNC, 0)][1], base_lse, atol=2e-3)
+    # (2) split count does not change the result beyond bf16 rounding
+    assert rel_l2(outs[(ops.VARIANT_TMA, 1)][0], base) < 6e-3
+    assert torch.allclose(outs[(ops.VARIANT_TMA, 1)][1], base_lse, atol=2e-3)
+    # (3) oracle on a sample of sequences (first, last, one in the middle)
+    kc, vc = k_cache.cpu(), v_cache.cpu()
+    for b in (0, 31, 63):
+        S = int(inp.seq_lens[b])
+        bt_row = inp.block_table[b:b + 1].cpu()
+        ref, ref_lse = c_oracle.paged_decode(inp.q[b:b + 1].cpu(), kc, vc, bt_row,
+                                             torch.tensor([S], dtype=torch.int32), inp.softmax_scale)
+        assert excess_rel_err(base[b:b + 1], ref) <= TOL and rel_l2(base[b:b + 1], ref) <= TOL
+        assert torch.allclose(base_lse[b:b + 1].cpu(), ref_lse, atol=2e-3)
+    # (4) physical placement does not matter: same tokens under a contiguous block table
+    inp2 = workloads.make_decode_inputs(wl, "cuda", ragged=ragged, contiguous_blocks=True)
+    c2 = inp2.kv_caches[0]
+    ops.reshape_and_cache(inp2.new_k, inp2.new_v, c2[0], c2[1], inp2.slot_mapping)
+    out2 = ops.paged_decode(inp2.q, c2[0], c2[1], inp2.block_table, inp2.seq_lens, inp2.max_seq_len,
+                            inp2.softmax_scale)
+    assert not torch.equal(inp.block_table, inp2.block_table)
+    assert torch.equal(out2, base)
