@@ -5,7 +5,7 @@ import pytest
 import torch
 
 from oracle import c_oracle
-from tests.helpers import excess_rel_err, make_case, rel_l2
+from tests.helpers import excess_rel_err, kernel_rel_l2, make_case, rel_l2
 from vllm_omni_b200 import layout, ops
 
 pytestmark = pytest.mark.gpu
@@ -64,7 +64,7 @@ def test_impl_write_then_decode_step(lib, be, fp8):
     ref, _ = c_oracle.paged_decode(c.q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, c.scale,
                                    fp8, c.k_scale, c.v_scale)
     got = output[:B].view(B, hq, d)
-    assert excess_rel_err(got, ref) <= 2e-3 and rel_l2(got, ref) <= 2e-3
+    assert excess_rel_err(got, ref) <= 2e-3 and kernel_rel_l2(got, ref) <= 2e-3
     assert torch.all(output[B:] == 9.0)  # padded rows are not touched
     # the cache now equals the oracle-written cache bit for bit
     assert torch.equal(kv.cpu().view(torch.int16), c.kv_cache.view(torch.int16))
