@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: global batch = workload batch x N (per-GPU KV bytes fixed up to the "
                          "KV-head count); strong: global batch fixed")
-    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 TMA, 2 cp.async")
+    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 TMA, 2 cp.async, 3 stream")
     ap.add_argument("--splits", type=int, default=0, help="0 = heuristic")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -302,7 +302,8 @@ def run_b200(args, wl):
     peak, peak_src = peaks()
     achieved = kv_bytes / (kern_avg_ms * 1e-3) / 1e9
     roofline = {
-        "bound": "hbm", "kernel": "paged_decode_tma_kernel" if args.variant in (0, 1) else "paged_decode_cpasync_kernel",
+        "bound": "hbm", "kernel": {0: "paged_decode_tma_kernel", 1: "paged_decode_tma_kernel", 2: "paged_decode_cpasync_kernel",
+                                   3: "paged_decode_stream_kernel"}[args.variant],
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
         "peak_source": peak_src, "algorithmic_bytes_per_launch": kv_bytes,
         "kernel_avg_us": kern_avg_ms * 1e3, "kernel_median_us": statistics.median(kern_ms) * 1e3,

@@ -57,6 +57,7 @@ extern "C" {
 #define B200ATTN_VARIANT_AUTO 0
 #define B200ATTN_VARIANT_TMA 1      /* persistent, TMA-staged pages, mbarrier ring       */
 #define B200ATTN_VARIANT_CPASYNC 2  /* one CTA per work item, cp.async-staged pages      */
+#define B200ATTN_VARIANT_STREAM 3   /* persistent, per-warp cp.async rings across items  */
 
 B200ATTN_API int b200attn_abi_version(void);
 B200ATTN_API const char* b200attn_last_error(void); /* host string, thread-local */

@@ -17,7 +17,7 @@ from vllm_omni_b200 import _lib, layout, ops, workloads
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-3
-VARIANTS = [ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
+VARIANTS = [ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
 
 
 def run_device(c, variant=ops.VARIANT_AUTO, num_splits=0, want_lse=True, cache_dev=None, q_dev=None):

@@ -18,6 +18,7 @@ KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0
 VARIANT_TMA = 1
 VARIANT_CPASYNC = 2
+VARIANT_STREAM = 3
 
 ERRORS = {1: "EINVAL", 2: "EUNSUPPORTED", 3: "EWORKSPACE", 4: "EDRIVER"}
 

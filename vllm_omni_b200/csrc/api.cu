@@ -388,6 +388,8 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       e = launch_decode_tma(tm_k, *mv, pk, p, grid, stream);
     } else if (variant == B200ATTN_VARIANT_CPASYNC) {
       e = launch_decode_cpasync(p, stream);
+    } else if (variant == B200ATTN_VARIANT_STREAM) {
+      e = launch_decode_stream(p, static_cast<int>(items < sms ? items : sms), stream);
     } else {
       return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
     }

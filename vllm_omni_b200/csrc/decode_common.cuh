@@ -58,16 +58,17 @@ struct WorkItem {
 
 // item index -> (b, kvh, split, sub); sub (head sub-group) is fastest so CTAs that re-read the
 // same pages run next to each other in time.
-__device__ __forceinline__ WorkItem decode_item(const DecodeParams& p, int item) {
-  WorkItem w;
+__device__ __forceinline__ void item_coords(const DecodeParams& p, int item, WorkItem& w) {
   w.sub = item % p.subgroups;
   int r = item / p.subgroups;
   w.split = r % p.num_splits;
   r /= p.num_splits;
   w.kvh = r % p.num_kv_heads;
   w.b = r / p.num_kv_heads;
-  w.seq_len = __ldg(p.seq_lens + w.b);
-  if (w.seq_len < 0) w.seq_len = 0;
+}
+// Tile range of the item once the sequence length is known.
+__device__ __forceinline__ void item_finish(const DecodeParams& p, int seq_len, WorkItem& w) {
+  w.seq_len = seq_len < 0 ? 0 : seq_len;
   const int tiles_total = (w.seq_len + kTileTokens - 1) / kTileTokens;
   w.tile_begin = w.split * p.tiles_per_split;
   // the last split extends to the end of the sequence, so a sequence longer than the host's
@@ -77,6 +78,11 @@ __device__ __forceinline__ WorkItem decode_item(const DecodeParams& p, int item)
   if (w.tile_begin > w.tile_end) w.tile_begin = w.tile_end;
   int as = (tiles_total + p.tiles_per_split - 1) / p.tiles_per_split;
   w.actual_splits = max(1, min(as, p.num_splits));
+}
+__device__ __forceinline__ WorkItem decode_item(const DecodeParams& p, int item) {
+  WorkItem w;
+  item_coords(p, item, w);
+  item_finish(p, __ldg(p.seq_lens + w.b), w);
   return w;
 }
 

@@ -17,6 +17,8 @@ struct CoordPerm {
 cudaError_t launch_decode_tma(const CUtensorMap& tm_k, const CUtensorMap& tm_v, CoordPerm perm,
                               const DecodeParams& p, int grid, cudaStream_t stream);
 cudaError_t launch_decode_cpasync(const DecodeParams& p, cudaStream_t stream);
+cudaError_t launch_decode_stream(const DecodeParams& p, int grid, cudaStream_t stream);
+size_t decode_stream_smem_bytes();
 size_t decode_tma_smem_bytes();
 size_t decode_cpasync_smem_bytes();
 

@@ -9,7 +9,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from ._lib import KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC, VARIANT_TMA, check  # noqa: F401
+from ._lib import KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC, VARIANT_STREAM, VARIANT_TMA, check  # noqa: F401
 
 _FP8_NAMES = ("fp8", "fp8_e4m3")
 
