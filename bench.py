@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: global batch = workload batch x N (per-GPU KV bytes fixed up to the "
                          "KV-head count); strong: global batch fixed")
-    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 TMA, 2 cp.async, 3 stream")
+    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 TMA, 2 cp.async, 3 stream, 4 stream-K")
     ap.add_argument("--splits", type=int, default=0, help="0 = heuristic")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -245,7 +245,10 @@ def run_b200(args, wl):
     B, hq, hkv, d = global_batch, sh.num_q_heads, sh.num_kv_heads, wl.head_size
     caches = [ops.split_kv_cache(c) for c in inp.kv_caches]
     out = torch.empty(B, hq, d, dtype=torch.bfloat16, device="cuda")
-    splits = args.splits or ops.decode_num_splits(B, hq, hkv, inp.max_seq_len)
+    # schedule: stream-K (no split count) unless a split count or a fixed-split variant is asked for
+    streamk = args.variant == ops.VARIANT_STREAMK or (args.variant == ops.VARIANT_AUTO and args.splits == 0)
+    variant = ops.VARIANT_STREAMK if streamk else (args.variant or ops.VARIANT_STREAM)
+    splits = 0 if streamk else (args.splits or ops.decode_num_splits(B, hq, hkv, inp.max_seq_len))
     ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, hq, d, max(splits, 1)))
     hidden = torch.zeros(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")  # o_proj output stand-in
     if world > 1:
@@ -258,11 +261,11 @@ def run_b200(args, wl):
             ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
                              inp.softmax_scale, out=out, kv_cache_dtype=wl.kv_cache_dtype,
                              k_scale=inp.k_scale, v_scale=inp.v_scale, num_splits=splits,
-                             variant=args.variant, workspace=ws)
+                             variant=variant, workspace=ws)
             if world > 1:
                 dist.all_reduce(hidden)  # the only collective next to the path: o_proj's row-parallel sum
 
-    launches_per_step = L * (2 + (1 if splits > 1 else 0))
+    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0))
     for _ in range(max(args.warmup, 3)):
         step()
     barrier(world)
@@ -291,24 +294,25 @@ def run_b200(args, wl):
             ops.paged_decode_partial(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
                                      inp.softmax_scale, out, max(splits, 1), ws,
                                      kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
-                                     v_scale=inp.v_scale, variant=args.variant)
+                                     v_scale=inp.v_scale, variant=variant)
             evs[i][1].record()
             i += 1
-            if splits > 1:
-                ops.lse_reduce(out, inp.seq_lens, inp.max_seq_len, splits, ws)
+            if splits > 1 or streamk:
+                ops.lse_reduce(out, inp.seq_lens, inp.max_seq_len, max(splits, 1), ws, num_kv_heads=hkv,
+                               variant=variant)
     torch.cuda.synchronize()
     kern_ms = [a.elapsed_time(b) for a, b in evs]
     kern_avg_ms = sum(kern_ms) / len(kern_ms)
     peak, peak_src = peaks()
     achieved = kv_bytes / (kern_avg_ms * 1e-3) / 1e9
     roofline = {
-        "bound": "hbm", "kernel": {0: "paged_decode_tma_kernel", 1: "paged_decode_tma_kernel", 2: "paged_decode_cpasync_kernel",
-                                   3: "paged_decode_stream_kernel"}[args.variant],
+        "bound": "hbm", "kernel": {1: "paged_decode_tma_kernel", 2: "paged_decode_cpasync_kernel",
+                                   3: "paged_decode_stream_kernel", 4: "paged_decode_streamk_kernel"}[variant],
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
         "peak_source": peak_src, "algorithmic_bytes_per_launch": kv_bytes,
         "kernel_avg_us": kern_avg_ms * 1e3, "kernel_median_us": statistics.median(kern_ms) * 1e3,
         "kernel_share_of_step": kern_avg_ms * L / ms_per_step, "frac_of_8TBps": achieved / 8000.0,
-        "step_gbs_per_gpu": kv_bytes * L / (ms_per_step * 1e-3) / 1e9, "num_splits": splits,
+        "step_gbs_per_gpu": kv_bytes * L / (ms_per_step * 1e-3) / 1e9, "num_splits": splits, "schedule": "stream-K" if streamk else "fixed-split",
     }
 
     # ---- end to end through the plugin with host buffers (H2D + D2H inside the timed region) ----

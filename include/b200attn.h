@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 3
+#define B200ATTN_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -58,6 +58,7 @@ extern "C" {
 #define B200ATTN_VARIANT_TMA 1      /* persistent, TMA-staged pages, mbarrier ring       */
 #define B200ATTN_VARIANT_CPASYNC 2  /* one CTA per work item, cp.async-staged pages      */
 #define B200ATTN_VARIANT_STREAM 3   /* persistent, per-warp cp.async rings across items  */
+#define B200ATTN_VARIANT_STREAMK 4  /* persistent, equal tile chunks per warp (default)  */
 
 B200ATTN_API int b200attn_abi_version(void);
 B200ATTN_API const char* b200attn_last_error(void); /* host string, thread-local */
@@ -120,8 +121,14 @@ B200ATTN_API size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t n
  * S_b == 0 => out row = 0, lse = -inf.
  *
  * Two launches: the split-K partial kernel (online softmax per KV range, fp32 partial
- * outputs + LSE into `workspace`) and the LSE-reduce kernel. Sequences that fit in one
- * split are written to `out` directly by the first kernel.
+ * outputs + LSE into `workspace`) and the LSE-reduce kernel. KV ranges that cover a whole
+ * sequence are written to `out` directly by the first kernel.
+ *
+ * Schedules: with num_splits == 0 and variant AUTO (what the backend uses) the KV tiles of
+ * the whole step are cut into equal contiguous chunks, one per warp of a persistent grid
+ * ("stream-K": no split count, balanced for ragged batches, needs batch <= 2048 and the
+ * workspace of b200attn_decode_workspace_bytes; otherwise the fixed-split schedule is
+ * used). With num_splits >= 1 every sequence is cut into that many equal KV ranges.
  *
  * q:   bf16 [batch, num_q_heads, head_size], token stride given, head stride = head_size
  * out: bf16 [batch, num_q_heads, head_size], token stride given
@@ -129,7 +136,8 @@ B200ATTN_API size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t n
  * seq_lens: i32 [batch] (device; never read on the host)
  * max_seq_len: host upper bound used for the split heuristic only (longer sequences
  *              are still handled correctly: the last split extends to S_b)
- * num_splits: 0 = heuristic, else forced (1 = no split, no reduce launch)
+ * num_splits: 0 = automatic (stream-K, or the split heuristic for the fixed-split variants),
+ *             else forced (1 = no split, no reduce launch)
  * variant: B200ATTN_VARIANT_*
  */
 B200ATTN_API int b200attn_paged_decode(
@@ -149,8 +157,10 @@ B200ATTN_API int b200attn_paged_decode(
 
 /*
  * The two launches of b200attn_paged_decode, exported separately for profiling sweeps.
- * `num_splits` must be >= 1 here. partial writes workspace (and `out` rows whose sequence
- * needs a single split); reduce merges rows that used > 1 split.
+ * `num_splits` must be >= 1 here unless variant is B200ATTN_VARIANT_STREAMK (which ignores it);
+ * AUTO means B200ATTN_VARIANT_STREAM. partial writes workspace (and `out` rows finished by a
+ * single KV range); reduce merges the rows that were cut. Both calls must be given the same
+ * batch, head counts, num_splits, variant and workspace.
  */
 B200ATTN_API int b200attn_paged_decode_partial(
     const void* q, int64_t q_stride_tok,
@@ -170,8 +180,8 @@ B200ATTN_API int b200attn_paged_decode_partial(
 B200ATTN_API int b200attn_lse_reduce(
     void* out, int64_t out_stride_tok, float* lse,
     const int32_t* seq_lens, int32_t batch, int32_t max_seq_len,
-    int32_t num_q_heads, int32_t head_size,
-    int32_t num_splits,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size,
+    int32_t num_splits, int32_t variant,
     const void* workspace, size_t workspace_bytes, void* stream);
 
 /*

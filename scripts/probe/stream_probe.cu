@@ -203,6 +203,56 @@ k_ring(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* p
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// modes 5/6: every warp fills its OWN ring (D slots of one 8 KiB page, one mbarrier per slot) with
+// one bulk op per page issued by its lane 0, waits for the oldest, touches it and re-issues: no
+// producer warp, no empty barriers, no cross-warp handshake.
+//   5: cp.async.bulk 1-D (linear 8 KiB)      6: TMA 4-D tile 64x32x2 box (SWIZZLE_128B)
+// ---------------------------------------------------------------------------------------------
+template <int MODE, int W, int D>
+__global__ void __launch_bounds__(W * 32, 1)
+k_self(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* pages, int npages, int* sink) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + W * D * kPage);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0)
+    for (int s = 0; s < D; ++s) mbar_init(&bars[warp * D + s], 1);
+  fence_barrier_init();
+  __syncthreads();
+  uint8_t* ring = smem + warp * D * kPage;
+  uint64_t* bar = bars + warp * D;
+  const int gw = blockIdx.x * W + warp, nw = gridDim.x * W;
+  const int nst = (npages - gw + nw - 1) / nw;
+  const uint64_t pol = l2_policy_evict_first();
+  // page ids of the next 32 stages, one per lane
+  int ids = (lane < nst) ? pages[gw + lane * nw] : 0;
+  auto issue = [&](int s) {
+    if (s < nst) {
+      if ((s & 31) == 0 && s > 0) ids = (s + lane < nst) ? pages[gw + (s + lane) * nw] : 0;
+      const int pg = __shfl_sync(0xffffffffu, ids, s & 31);
+      if (lane == 0) {
+        const int slot = s % D;
+        mbar_arrive_expect_tx(&bar[slot], kPage);
+        if (MODE == 5)
+          bulk_copy_1d(ring + slot * kPage, base + static_cast<int64_t>(pg) * kPage, kPage, &bar[slot], pol);
+        else
+          tma_load_4d(ring + slot * kPage, &tm, &bar[slot], 0, 0, 0, pg, pol);
+      }
+    }
+  };
+  for (int s = 0; s < D; ++s) issue(s);
+  int acc = 0;
+  for (int s = 0; s < nst; ++s) {
+    const int slot = s % D;
+    mbar_wait_dbg(&bar[slot], (s / D) & 1, 2, s);
+    acc ^= *reinterpret_cast<const int*>(ring + slot * kPage + lane * 16);
+    __syncwarp();
+    issue(s + D);
+  }
+  if (acc == 0x12345678) *sink = acc;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -321,5 +371,20 @@ int main(int argc, char** argv) {
   RING(4, 8, 8, 2, tm4);
   RING(4, 8, 24, 1, tm4);
   RING(4, 4, 4, 4, tm4);
+#define SELF(MODE, W, D, TM)                                                                      \
+  {                                                                                               \
+    auto k = k_self<MODE, W, D>;                                                                  \
+    const int sm = W * D * kPage + W * D * 8 + 1024;                                              \
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));                 \
+    run("self mode=" #MODE " W=" #W " D=" #D, bytes, [&] { k<<<sms, W * 32, sm>>>(TM, base, pg(), npages, sink); }); \
+  }
+  SELF(5, 8, 2, tm4);
+  SELF(5, 8, 3, tm4);
+  SELF(5, 4, 6, tm4);
+  SELF(5, 12, 2, tm4);
+  SELF(6, 8, 2, tm4);
+  SELF(6, 8, 3, tm4);
+  SELF(6, 4, 6, tm4);
+  SELF(6, 12, 2, tm4);
   return 0;
 }

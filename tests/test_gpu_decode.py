@@ -17,7 +17,7 @@ from vllm_omni_b200 import _lib, layout, ops, workloads
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-3
-VARIANTS = [ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
+VARIANTS = [ops.VARIANT_STREAMK, ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
 
 
 def run_device(c, variant=ops.VARIANT_AUTO, num_splits=0, want_lse=True, cache_dev=None, q_dev=None):
@@ -92,10 +92,10 @@ def test_masked_tail_never_leaks_garbage(lib, variant):
 
 def test_forced_split_counts_agree(lib):
     c = make_case([1000, 513, 64, 2048], hq=8, hkv=2, seed=8)
-    base, _ = run_device(c, ops.VARIANT_TMA, 1)
+    base, _ = run_device(c, ops.VARIANT_STREAM, 1)
     check(c, base, None)
     for s in (2, 5, 16, 64, 128):
-        out, lse = run_device(c, ops.VARIANT_TMA, s)
+        out, lse = run_device(c, ops.VARIANT_STREAM, s)
         check(c, out, lse)
         assert rel_l2(out, base) < 6e-3  # two bf16 roundings of the same value
 
@@ -224,14 +224,15 @@ def test_full_size_properties_cfg3(lib, ragged):
                                                    inp.max_seq_len, inp.softmax_scale, lse=lse,
                                                    num_splits=s, variant=variant), lse)
     torch.cuda.synchronize()
-    base, base_lse = outs[(ops.VARIANT_TMA, 0)]
+    base, base_lse = outs[(ops.VARIANT_STREAMK, 0)]
     assert torch.isfinite(base.float()).all()
     # (1) the two staging variants agree (different warp counts => different merge order)
-    assert rel_l2(outs[(ops.VARIANT_CPASYNC, 0)][0], base) < 3e-3
-    assert torch.allclose(outs[(ops.VARIANT_CPASYNC, 0)][1], base_lse, atol=2e-3)
+    for v in VARIANTS[1:]:
+        assert rel_l2(outs[(v, 0)][0], base) < 3e-3
+        assert torch.allclose(outs[(v, 0)][1], base_lse, atol=2e-3)
     # (2) split count does not change the result beyond bf16 rounding
-    assert rel_l2(outs[(ops.VARIANT_TMA, 1)][0], base) < 6e-3
-    assert torch.allclose(outs[(ops.VARIANT_TMA, 1)][1], base_lse, atol=2e-3)
+    assert rel_l2(outs[(ops.VARIANT_STREAM, 1)][0], base) < 6e-3
+    assert torch.allclose(outs[(ops.VARIANT_STREAM, 1)][1], base_lse, atol=2e-3)
     # (3) oracle on a sample of sequences (first, last, one in the middle)
     kc, vc = k_cache.cpu(), v_cache.cpu()
     for b in (0, 31, 63):

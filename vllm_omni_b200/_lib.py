@@ -12,13 +12,14 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 KV_BF16 = 0
 KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0
 VARIANT_TMA = 1
 VARIANT_CPASYNC = 2
 VARIANT_STREAM = 3
+VARIANT_STREAMK = 4
 
 ERRORS = {1: "EINVAL", 2: "EUNSUPPORTED", 3: "EWORKSPACE", 4: "EDRIVER"}
 
@@ -67,7 +68,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200attn_paged_decode": (C.c_int, _DECODE_ARGS),
     "b200attn_paged_decode_partial": (C.c_int, _DECODE_ARGS),
     "b200attn_lse_reduce": (C.c_int, [
-        _vp, _i64, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _sz, _vp]),
+        _vp, _i64, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _sz, _vp]),
     "b200attn_paged_prefill": (C.c_int, [
         _vp, _i64,
         _vp, _vp, *_CACHE_ARGS, _i64,

@@ -142,13 +142,9 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
               fast_build: bool = False) -> B200AttentionMetadata:
         cam = common_attn_metadata
         nd, np_, ndt, npt = split_decodes_and_prefills(cam, decode_threshold=1)
-        splits = 1
-        if nd > 0:
-            splits = ops.decode_num_splits(nd, self.num_heads_q, self.num_heads_kv, cam.max_seq_len,
-                                           self._sms)
-            while splits > 1 and ops.decode_workspace_bytes(
-                    nd, self.num_heads_q, self.head_size, splits) > self.workspace.nbytes:
-                splits -= 1
+        # 0 = the library's default schedule (stream-K: equal KV-tile chunks per warp of a persistent
+        # grid, nothing to choose on the host; falls back to fixed splits sized to the workspace)
+        splits = 0
         pqsl, pmax = None, 0
         if np_ > 0:
             pqsl = cam.query_start_loc[nd:] - ndt

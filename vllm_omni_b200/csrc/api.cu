@@ -151,6 +151,49 @@ int get_kv_map(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, 
   return 0;
 }
 
+// 5-D tensor map of one cache tensor for the stream-K kernel, valid for ANY cache strides:
+//   dim0 = d_lo (64 elements = 128 B, the swizzle span)   dim1 = slot   (stride cs_slot)
+//   dim2 = d_hi (2, stride 64 elements)                   dim3 = head   (stride cs_head)
+//   dim4 = block (stride cs_block)
+// box = 64 x 16 x 2 x 1 x 1: one 16-token x 128-dim tile per op, landing as two 2 KiB halves of
+// SWIZZLE_128B rows — the layout the math reads with ldmatrix.
+thread_local KvMapEntry g_maps5[kMapCache];
+
+int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv, int32_t bs,
+                const CUtensorMap** out_map) {
+  KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, 0};
+  const size_t slot = (reinterpret_cast<uintptr_t>(ptr) >> 8) % kMapCache;
+  KvMapEntry& e = g_maps5[slot];
+  if (e.valid && e.key == key) {
+    *out_map = &e.map;
+    return 0;
+  }
+  EncodeTiledFn enc = get_encode_fn();
+  if (enc == nullptr) return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled entry point not found");
+  // a size-1 dimension may carry any stride: give it a harmless one
+  const int64_t st_slot = ss * 2;
+  const int64_t st_head = hkv > 1 ? sh * 2 : 256;
+  const int64_t st_block = nb > 1 ? sb * 2 : 256;
+  cuuint64_t gdim[5] = {64, static_cast<cuuint64_t>(bs), 2, static_cast<cuuint64_t>(hkv), static_cast<cuuint64_t>(nb)};
+  cuuint64_t gstr[4] = {static_cast<cuuint64_t>(st_slot), 128, static_cast<cuuint64_t>(st_head),
+                        static_cast<cuuint64_t>(st_block)};
+  cuuint32_t box[5] = {64, static_cast<cuuint32_t>(kTileTokens), 2, 1, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(&e.map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    e.valid = false;
+    return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled (5-D) failed (%d): strides [%lld,128,%lld,%lld] B",
+                static_cast<int>(r), static_cast<long long>(st_slot), static_cast<long long>(st_head),
+                static_cast<long long>(st_block));
+  }
+  e.key = key;
+  e.valid = true;
+  *out_map = &e.map;
+  return 0;
+}
+
 int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64_t ss, int64_t sh,
                      int64_t nb, int32_t hkv, int32_t hd, int32_t bs, int32_t kv_dtype) {
   if (k_cache == nullptr || v_cache == nullptr) return fail(B200ATTN_EINVAL, "null cache pointer");
@@ -168,6 +211,19 @@ int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64
   if ((reinterpret_cast<uintptr_t>(k_cache) % 16) || (reinterpret_cast<uintptr_t>(v_cache) % 16))
     return fail(B200ATTN_EINVAL, "cache pointers must be 16-byte aligned");
   return 0;
+}
+
+// stream-K workspace: 2 partial slots per warp of the persistent grid (O rows then LSE), then the
+// tiles-prefix plan.
+size_t fixed_workspace_bytes(int batch, int num_q_heads, int head_size, int splits) {
+  const size_t rows = static_cast<size_t>(batch) * num_q_heads * splits;
+  return rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
+}
+size_t sk_part_rows(int sms) { return static_cast<size_t>(2) * sms * kSkWarps * kHeadsPerItem; }
+size_t sk_workspace_bytes(int batch, int sms) {
+  const size_t rows = sk_part_rows(sms);
+  return rows * kHeadDim * sizeof(float) + rows * sizeof(float) +
+         ((static_cast<size_t>(batch) + 1 + 3) / 4 * 4) * sizeof(int32_t) + 256;
 }
 
 constexpr int kMaxSplits = 128;
@@ -274,8 +330,13 @@ int32_t b200attn_decode_num_splits(int32_t batch, int32_t num_q_heads, int32_t n
 size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads, int32_t head_size,
                                        int32_t max_splits) {
   if (max_batch <= 0 || num_q_heads <= 0 || head_size <= 0 || max_splits <= 0) return 0;
-  const size_t rows = static_cast<size_t>(max_batch) * num_q_heads * max_splits;
-  return rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
+  const size_t fixed = fixed_workspace_bytes(max_batch, num_q_heads, head_size, max_splits);
+  // the default (stream-K) schedule needs a batch-independent partial area; size for both so
+  // that either schedule can run on a workspace of this size
+  int sms = cached_num_sms();
+  if (sms <= 0) sms = 148;
+  const size_t sk = sk_workspace_bytes(max_batch, sms);
+  return fixed > sk ? fixed : sk;
 }
 
 static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t q_stride_tok,
@@ -305,28 +366,76 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
 
   if (num_splits < 0 || num_splits > kMaxSplits)
     return fail(B200ATTN_EINVAL, "num_splits %d out of [0, %d]", num_splits, kMaxSplits);
-  if (num_splits == 0) {
-    num_splits = b200attn_decode_num_splits(batch, num_q_heads, num_kv_heads, max_seq_len, sms);
-    // never ask for more splits than the caller's workspace can hold
-    while (num_splits > 1 &&
-           b200attn_decode_workspace_bytes(batch, num_q_heads, head_size, num_splits) > workspace_bytes)
-      --num_splits;
+  if (variant < B200ATTN_VARIANT_AUTO || variant > B200ATTN_VARIANT_STREAMK)
+    return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
+  // schedule: stream-K (equal tile chunks per warp, no split count) unless the caller asks for a
+  // fixed split count or a fixed-split kernel
+  bool use_sk = variant == B200ATTN_VARIANT_STREAMK || (variant == B200ATTN_VARIANT_AUTO && num_splits == 0);
+  if (use_sk) {
+    const int tpp = block_size / kTileTokens;
+    const bool fits = batch <= kSkMaxBatch && workspace != nullptr && tpp > 0 && (tpp & (tpp - 1)) == 0 &&
+                      sk_workspace_bytes(batch, sms) <= workspace_bytes &&
+                      (reinterpret_cast<uintptr_t>(workspace) % 16) == 0;
+    if (!fits) {
+      if (variant == B200ATTN_VARIANT_STREAMK)
+        return fail(B200ATTN_EWORKSPACE,
+                    "stream-K needs batch <= %d, block_size = 16 * 2^k and a 16-byte aligned workspace of %zu B (got %zu)",
+                    kSkMaxBatch, sk_workspace_bytes(batch, sms), workspace_bytes);
+      use_sk = false;  // AUTO: fall back to the fixed-split schedule
+    }
   }
+  if (variant == B200ATTN_VARIANT_AUTO || variant == B200ATTN_VARIANT_STREAMK)
+    variant = use_sk ? B200ATTN_VARIANT_STREAMK : B200ATTN_VARIANT_STREAM;
   float* part_o = nullptr;
   float* part_lse = nullptr;
-  if (num_splits > 1) {
-    if (workspace == nullptr ||
-        b200attn_decode_workspace_bytes(batch, num_q_heads, head_size, num_splits) > workspace_bytes)
-      return fail(B200ATTN_EWORKSPACE, "workspace %zu B too small for %d splits (need %zu)",
-                  workspace_bytes, num_splits,
-                  b200attn_decode_workspace_bytes(batch, num_q_heads, head_size, num_splits));
-    if (reinterpret_cast<uintptr_t>(workspace) % 16)
-      return fail(B200ATTN_EINVAL, "workspace must be 16-byte aligned");
-    const size_t rows = static_cast<size_t>(batch) * num_q_heads * num_splits;
+  int32_t* plan_cum = nullptr;
+  if (use_sk) {
+    num_splits = 1;
+    const size_t rows = sk_part_rows(sms);
     part_o = static_cast<float*>(workspace);
-    part_lse = part_o + rows * head_size;
+    part_lse = part_o + rows * kHeadDim;
+    plan_cum = reinterpret_cast<int32_t*>(part_lse + rows);
+  } else {
+    if (num_splits == 0) {
+      num_splits = b200attn_decode_num_splits(batch, num_q_heads, num_kv_heads, max_seq_len, sms);
+      // never ask for more splits than the caller's workspace can hold
+      while (num_splits > 1 &&
+             fixed_workspace_bytes(batch, num_q_heads, head_size, num_splits) > workspace_bytes)
+        --num_splits;
+    }
+    if (num_splits > 1) {
+      if (workspace == nullptr ||
+          fixed_workspace_bytes(batch, num_q_heads, head_size, num_splits) > workspace_bytes)
+        return fail(B200ATTN_EWORKSPACE, "workspace %zu B too small for %d splits (need %zu)",
+                    workspace_bytes, num_splits,
+                    fixed_workspace_bytes(batch, num_q_heads, head_size, num_splits));
+      if (reinterpret_cast<uintptr_t>(workspace) % 16)
+        return fail(B200ATTN_EINVAL, "workspace must be 16-byte aligned");
+      const size_t rows = static_cast<size_t>(batch) * num_q_heads * num_splits;
+      part_o = static_cast<float*>(workspace);
+      part_lse = part_o + rows * head_size;
+    }
   }
   const int tiles_per_split = tiles_per_split_for(max_seq_len, num_splits);
+
+  DecodeParams p{};
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.out_stride_tok = out_stride_tok;
+  p.lse = lse;
+  p.seq_lens = seq_lens;
+  p.batch = batch;
+  p.num_q_heads = num_q_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.group = num_q_heads / num_kv_heads;
+  p.subgroups = (p.group + kHeadsPerItem - 1) / kHeadsPerItem;
+  p.num_splits = num_splits;
+  p.tiles_per_split = tiles_per_split;
+  p.part_o = part_o;
+  p.part_lse = part_lse;
+  p.plan_cum = plan_cum;
+  const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
+  if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
+  p.total_items = static_cast<int32_t>(items);
 
   if (run_partial) {
     if (q == nullptr || block_table == nullptr) return fail(B200ATTN_EINVAL, "null q/block_table");
@@ -338,7 +447,6 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
     const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
     if (fp8) return fail(B200ATTN_EUNSUPPORTED, "fp8 KV decode is not built yet");
-    DecodeParams p;
     p.q = static_cast<const __nv_bfloat16*>(q);
     p.q_stride_tok = q_stride_tok;
     p.k_cache = static_cast<const uint8_t*>(k_cache);
@@ -346,32 +454,23 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     p.cs_block = cache_stride_block;
     p.cs_slot = cache_stride_slot;
     p.cs_head = cache_stride_head;
-    p.out = static_cast<__nv_bfloat16*>(out);
-    p.out_stride_tok = out_stride_tok;
-    p.lse = lse;
     p.block_table = block_table;
     p.bt_stride = block_table_stride;
-    p.seq_lens = seq_lens;
-    p.batch = batch;
-    p.num_q_heads = num_q_heads;
-    p.num_kv_heads = num_kv_heads;
-    p.group = num_q_heads / num_kv_heads;
-    p.subgroups = (p.group + kHeadsPerItem - 1) / kHeadsPerItem;
     p.block_size = block_size;
     p.tiles_per_page = block_size / kTileTokens;
-    p.num_splits = num_splits;
-    p.tiles_per_split = tiles_per_split;
-    const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
-    if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
-    p.total_items = static_cast<int32_t>(items);
+    p.tpp_shift = -1;
+    for (int sh = 0; sh < 16; ++sh)
+      if ((1 << sh) == p.tiles_per_page) p.tpp_shift = sh;
+    p.tpp_mask = p.tiles_per_page - 1;
+    if (variant == B200ATTN_VARIANT_STREAMK && p.tpp_shift < 0) {
+      // block sizes that are not 16 * 2^k go through the fixed-split kernel
+      return fail(B200ATTN_EUNSUPPORTED, "stream-K needs block_size = 16 * 2^k (got %d)", block_size);
+    }
     p.scale_log2 = softmax_scale * kLog2e;
     p.k_scale = k_scale;
     p.v_scale = v_scale;
     p.scale_stride = scale_numel > 1 ? 1 : 0;
-    p.part_o = part_o;
-    p.part_lse = part_lse;
 
-    if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_TMA;
     cudaError_t e;
     if (variant == B200ATTN_VARIANT_TMA) {
       const CUtensorMap *mk = nullptr, *mv = nullptr;
@@ -390,12 +489,26 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       e = launch_decode_cpasync(p, stream);
     } else if (variant == B200ATTN_VARIANT_STREAM) {
       e = launch_decode_stream(p, static_cast<int>(items < sms ? items : sms), stream);
+    } else if (variant == B200ATTN_VARIANT_STREAMK) {
+      const CUtensorMap *mk = nullptr, *mv = nullptr;
+      if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
+                               num_kv_heads, block_size, &mk))
+        return rc;
+      const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
+      if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
+                               num_kv_heads, block_size, &mv))
+        return rc;
+      e = launch_decode_streamk(tm_k, *mv, p, sms, stream);
     } else {
       return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
     }
     if (e != cudaSuccess) return cuda_fail(e, "paged_decode partial launch");
   }
-  if (run_reduce && num_splits > 1) {
+  if (run_reduce && use_sk) {
+    const bool pdl = run_partial && env_flag("B200ATTN_PDL", true);
+    cudaError_t e = launch_streamk_reduce(p, sms, pdl, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "streamk_reduce launch");
+  } else if (run_reduce && num_splits > 1) {
     const bool pdl = run_partial && env_flag("B200ATTN_PDL", true);
     cudaError_t e = launch_lse_reduce(static_cast<__nv_bfloat16*>(out), out_stride_tok, lse, seq_lens,
                                       batch, num_q_heads, num_splits, tiles_per_split, part_o,
@@ -433,7 +546,9 @@ int b200attn_paged_decode_partial(const void* q, int64_t q_stride_tok, const voi
                                   const float* k_scale, const float* v_scale, int32_t scale_numel,
                                   int32_t num_splits, int32_t variant, void* workspace,
                                   size_t workspace_bytes, void* stream) {
-  if (num_splits < 1) return fail(B200ATTN_EINVAL, "partial needs an explicit num_splits >= 1");
+  if (variant != B200ATTN_VARIANT_STREAMK && num_splits < 1)
+    return fail(B200ATTN_EINVAL, "partial needs an explicit num_splits >= 1");
+  if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_STREAM;
   return decode_impl(true, false, q, q_stride_tok, k_cache, v_cache, cache_stride_block,
                      cache_stride_slot, cache_stride_head, num_blocks, out, out_stride_tok, lse,
                      block_table, block_table_stride, seq_lens, batch, max_seq_len, num_q_heads,
@@ -442,13 +557,15 @@ int b200attn_paged_decode_partial(const void* q, int64_t q_stride_tok, const voi
 }
 
 int b200attn_lse_reduce(void* out, int64_t out_stride_tok, float* lse, const int32_t* seq_lens,
-                        int32_t batch, int32_t max_seq_len, int32_t num_q_heads, int32_t head_size,
-                        int32_t num_splits, const void* workspace, size_t workspace_bytes,
-                        void* stream) {
-  if (num_splits < 1) return fail(B200ATTN_EINVAL, "reduce needs an explicit num_splits >= 1");
+                        int32_t batch, int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
+                        int32_t head_size, int32_t num_splits, int32_t variant, const void* workspace,
+                        size_t workspace_bytes, void* stream) {
+  if (variant != B200ATTN_VARIANT_STREAMK && num_splits < 1)
+    return fail(B200ATTN_EINVAL, "reduce needs an explicit num_splits >= 1");
+  if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_STREAM;
   return decode_impl(false, true, nullptr, 0, nullptr, nullptr, 0, 0, 0, 0, out, out_stride_tok, lse,
-                     nullptr, 0, seq_lens, batch, max_seq_len, num_q_heads, num_q_heads, head_size, 16,
-                     1.f, B200ATTN_KV_BF16, nullptr, nullptr, 1, num_splits, 0,
+                     nullptr, 0, seq_lens, batch, max_seq_len, num_q_heads, num_kv_heads, head_size, 16,
+                     1.f, B200ATTN_KV_BF16, nullptr, nullptr, 1, num_splits, variant,
                      const_cast<void*>(workspace), workspace_bytes, stream);
 }
 

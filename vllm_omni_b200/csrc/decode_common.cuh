@@ -18,6 +18,9 @@ namespace b200 {
 constexpr int kHeadDim = 128;      // only head_size 128 is built (all Qwen-Omni AR stages)
 constexpr int kTileTokens = 16;    // one MMA M-tile of KV tokens
 constexpr int kHeadsPerItem = 8;   // query heads packed in one N=8 tile
+constexpr int kSkMaxBatch = 2048;  // stream-K plan (tiles prefix) lives in shared memory
+constexpr int kSkWarps = 8;        // stream-K: warps per CTA, each with its own ring
+constexpr int kSkDepth = 3;        // stream-K: ring stages per warp (8 KiB each)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -38,6 +41,8 @@ struct DecodeParams {
   int32_t subgroups;     // ceil(group / 8): head groups per KV head
   int32_t block_size;
   int32_t tiles_per_page;  // block_size / 16
+  int32_t tpp_shift;       // log2(tiles_per_page) when it is a power of two, else -1
+  int32_t tpp_mask;        // tiles_per_page - 1 (valid with tpp_shift >= 0)
   int32_t num_splits;
   int32_t tiles_per_split;  // multiple of the stage tile count
   int32_t total_items;      // batch * Hkv * num_splits * subgroups
@@ -47,6 +52,7 @@ struct DecodeParams {
   int32_t scale_stride;  // 0 = per-tensor, 1 = per-kv-head
   float* part_o;         // [batch, Hq, num_splits, 128] f32, normalised partial outputs
   float* part_lse;       // [batch, Hq, num_splits] f32, natural log
+  int32_t* plan_cum;     // stream-K only: [batch + 1] exclusive prefix of tiles per sequence
 };
 
 struct WorkItem {

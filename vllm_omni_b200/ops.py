@@ -9,7 +9,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from ._lib import KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC, VARIANT_STREAM, VARIANT_TMA, check  # noqa: F401
+from ._lib import KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check  # noqa: F401
 
 _FP8_NAMES = ("fp8", "fp8_e4m3")
 
@@ -198,7 +198,7 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         return out
     if workspace is None:
         workspace = DecodeWorkspace(q.device)
-    if num_splits != 1:
+    if num_splits != 1 or variant == VARIANT_STREAMK:
         s = num_splits if num_splits > 0 else decode_num_splits(
             batch, hq, k_cache.shape[2], max_seq_len)
         workspace.ensure(decode_workspace_bytes(batch, hq, d, s))
@@ -221,15 +221,16 @@ def paged_decode_partial(q, k_cache, v_cache, block_table, seq_lens, max_seq_len
 
 
 def lse_reduce(out: torch.Tensor, seq_lens: torch.Tensor, max_seq_len: int, num_splits: int,
-               workspace: DecodeWorkspace, lse: torch.Tensor | None = None) -> None:
+               workspace: DecodeWorkspace, lse: torch.Tensor | None = None, num_kv_heads: int | None = None,
+               variant: int = VARIANT_AUTO) -> None:
     """Second launch only (profiling sweeps): merge the per-split partials by their LSE."""
     lib = _lib.load()
     _need_cuda(out, seq_lens, lse)
     batch, hq, d = out.shape
     check("b200attn_lse_reduce", lib.b200attn_lse_reduce(
         out.data_ptr(), out.stride(0), lse.data_ptr() if lse is not None else None,
-        seq_lens.data_ptr(), batch, int(max_seq_len), hq, d, int(num_splits), workspace.ptr,
-        workspace.nbytes, _stream()))
+        seq_lens.data_ptr(), batch, int(max_seq_len), hq, num_kv_heads if num_kv_heads is not None else hq, d,
+        int(num_splits), int(variant), workspace.ptr, workspace.nbytes, _stream()))
 
 
 def paged_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
