@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--contiguous-blocks", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
     return ap.parse_args()
 
 
@@ -266,14 +267,39 @@ def run_b200(args, wl):
                 dist.all_reduce(hidden)  # the only collective next to the path: o_proj's row-parallel sum
 
     launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0))
+
+    def capture(fn):
+        """CUDA-graph the launches of `fn` (how vLLM replays decode steps); None if capture fails."""
+        if args.no_graph:
+            return None
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                fn()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            return g
+        except Exception as ex:  # report, fall back to eager launches
+            print(f"[bench] graph capture failed ({type(ex).__name__}: {ex}); eager launches", file=sys.stderr)
+            torch.cuda.synchronize()
+            return None
+
+    step()  # first call outside capture: lazy init (tensor maps, func attributes, NCCL)
+    torch.cuda.synchronize()
+    g_step = capture(step)
+    run_step = g_step.replay if g_step is not None else step
     for _ in range(max(args.warmup, 3)):
-        step()
+        run_step()
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
         e0.record()
         for _ in range(args.steps):
-            step()
+            run_step()
         e1.record()
         torch.cuda.synchronize()
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
@@ -281,27 +307,43 @@ def run_b200(args, wl):
     ms_per_step = ms_total / args.steps
     value = global_batch / (ms_per_step * 1e-3)
 
-    # ---- roofline of the dominant kernel: per-launch CUDA events around the partial kernel ----
+    # ---- roofline of the dominant kernel: CUDA events around a graph of ONLY its L launches
+    # (one per layer cache, back to back), so the average excludes host launch gaps; the eager
+    # fallback brackets every launch with its own event pair.
     kv_bytes = inp.kv_bytes_per_layer
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-           for _ in range(L * args.steps)]
-    i = 0
-    for _ in range(args.steps):
+
+    def partial_only():
         for kc, vc in caches:
-            ops.reshape_and_cache(inp.new_k, inp.new_v, kc, vc, inp.slot_mapping, wl.kv_cache_dtype,
-                                  inp.k_scale, inp.v_scale)
-            evs[i][0].record()
             ops.paged_decode_partial(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
                                      inp.softmax_scale, out, max(splits, 1), ws,
                                      kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
                                      v_scale=inp.v_scale, variant=variant)
-            evs[i][1].record()
-            i += 1
-            if splits > 1 or streamk:
-                ops.lse_reduce(out, inp.seq_lens, inp.max_seq_len, max(splits, 1), ws, num_kv_heads=hkv,
-                               variant=variant)
-    torch.cuda.synchronize()
-    kern_ms = [a.elapsed_time(b) for a, b in evs]
+
+    g_part = capture(partial_only)
+    kern_ms = []
+    if g_part is not None:
+        for _ in range(3):
+            g_part.replay()
+        for _ in range(args.steps):
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            g_part.replay()
+            b_.record()
+            torch.cuda.synchronize()
+            kern_ms.append(a.elapsed_time(b_) / L)
+    else:
+        for _ in range(args.steps):
+            for kc, vc in caches:
+                a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                ops.paged_decode_partial(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
+                                         inp.softmax_scale, out, max(splits, 1), ws,
+                                         kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
+                                         v_scale=inp.v_scale, variant=variant)
+                b_.record()
+                kern_ms.append((a, b_))
+        torch.cuda.synchronize()
+        kern_ms = [a.elapsed_time(b_) for a, b_ in kern_ms]
     kern_avg_ms = sum(kern_ms) / len(kern_ms)
     peak, peak_src = peaks()
     achieved = kv_bytes / (kern_avg_ms * 1e-3) / 1e9
@@ -312,7 +354,7 @@ def run_b200(args, wl):
         "peak_source": peak_src, "algorithmic_bytes_per_launch": kv_bytes,
         "kernel_avg_us": kern_avg_ms * 1e3, "kernel_median_us": statistics.median(kern_ms) * 1e3,
         "kernel_share_of_step": kern_avg_ms * L / ms_per_step, "frac_of_8TBps": achieved / 8000.0,
-        "step_gbs_per_gpu": kv_bytes * L / (ms_per_step * 1e-3) / 1e9, "num_splits": splits, "schedule": "stream-K" if streamk else "fixed-split",
+        "step_gbs_per_gpu": kv_bytes * L / (ms_per_step * 1e-3) / 1e9, "launch_mode": "cuda-graph replay" if g_step is not None else "eager", "num_splits": splits, "schedule": "stream-K" if streamk else "fixed-split",
     }
 
     # ---- end to end through the plugin with host buffers (H2D + D2H inside the timed region) ----

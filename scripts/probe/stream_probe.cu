@@ -209,7 +209,7 @@ k_ring(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* p
 // producer warp, no empty barriers, no cross-warp handshake.
 //   5: cp.async.bulk 1-D (linear 8 KiB)      6: TMA 4-D tile 64x32x2 box (SWIZZLE_128B)
 // ---------------------------------------------------------------------------------------------
-template <int MODE, int W, int D>
+template <int MODE, int W, int D, int DELAY = 0>
 __global__ void __launch_bounds__(W * 32, 1)
 k_self(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* pages, int npages, int* sink) {
   extern __shared__ uint8_t smem_raw[];
@@ -236,8 +236,12 @@ k_self(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* p
         mbar_arrive_expect_tx(&bar[slot], kPage);
         if (MODE == 5)
           bulk_copy_1d(ring + slot * kPage, base + static_cast<int64_t>(pg) * kPage, kPage, &bar[slot], pol);
-        else
+        else if (MODE == 6)
           tma_load_4d(ring + slot * kPage, &tm, &bar[slot], 0, 0, 0, pg, pol);
+        else {  // 7: two 4 KiB boxes (K rows 0-15, V rows 16-31), as the decode kernel issues them
+          tma_load_4d(ring + slot * kPage, &tm, &bar[slot], 0, 0, 0, pg, pol);
+          tma_load_4d(ring + slot * kPage + 4096, &tm, &bar[slot], 0, 16, 0, pg, pol);
+        }
       }
     }
   };
@@ -247,6 +251,154 @@ k_self(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* p
     const int slot = s % D;
     mbar_wait_dbg(&bar[slot], (s / D) & 1, 2, s);
     acc ^= *reinterpret_cast<const int*>(ring + slot * kPage + lane * 16);
+    if (DELAY > 0) {  // stand-in for the per-tile math of the decode kernel
+      const long long t0 = clock64();
+      while (clock64() - t0 < DELAY) {
+      }
+    }
+    __syncwarp();
+    issue(s + D);
+  }
+  if (acc == 0x12345678) *sink = acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// mode 8: as mode 7 (self-issued 2 x 4 KiB TMA boxes per stage) but the warp consumes whichever
+// slot has landed first (softmax accumulation is order independent inside a work item), so one
+// slow DRAM request does not block the stages behind it.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
+template <int W, int D, int DELAY>
+__global__ void __launch_bounds__(W * 32, 1)
+k_ooo(const __grid_constant__ CUtensorMap tm, const uint8_t* base, const int* pages, int npages, int* sink) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + W * D * kPage);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0)
+    for (int s = 0; s < D; ++s) mbar_init(&bars[warp * D + s], 1);
+  fence_barrier_init();
+  __syncthreads();
+  uint8_t* ring = smem + warp * D * kPage;
+  uint64_t* bar = bars + warp * D;
+  const int gw = blockIdx.x * W + warp, nw = gridDim.x * W;
+  const int nst = (npages - gw + nw - 1) / nw;
+  const uint64_t pol = l2_policy_evict_first();
+  int ids = (lane < nst) ? pages[gw + lane * nw] : 0;
+  int next = 0;            // next stage to issue
+  uint32_t phases = 0;     // bit s = parity slot s waits for
+  uint32_t busy = 0;       // bit s = slot s holds an issued, unconsumed stage
+  auto issue = [&](int slot) {
+    if (next < nst) {
+      if ((next & 31) == 0 && next > 0) ids = (next + lane < nst) ? pages[gw + (next + lane) * nw] : 0;
+      const int pg = __shfl_sync(0xffffffffu, ids, next & 31);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&bar[slot], kPage);
+        tma_load_4d(ring + slot * kPage, &tm, &bar[slot], 0, 0, 0, pg, pol);
+        tma_load_4d(ring + slot * kPage + 4096, &tm, &bar[slot], 0, 16, 0, pg, pol);
+      }
+      busy |= 1u << slot;
+      ++next;
+    }
+  };
+  for (int s = 0; s < D; ++s) issue(s);
+  int acc = 0, oldest = 0;
+  for (int done = 0; done < nst; ++done) {
+    int slot = -1;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      const int s = (oldest + i) % D;
+      if (slot < 0 && ((busy >> s) & 1) && mbar_test(&bar[s], (phases >> s) & 1)) slot = s;
+    }
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot < 0) {  // nothing landed yet: block on the oldest busy slot
+      slot = oldest;
+      while (!((busy >> slot) & 1)) slot = (slot + 1) % D;
+      mbar_wait_dbg(&bar[slot], (phases >> slot) & 1, 3, done);
+    } else {
+      mbar_wait_dbg(&bar[slot], (phases >> slot) & 1, 4, done);  // make it visible to every lane
+    }
+    acc ^= *reinterpret_cast<const int*>(ring + slot * kPage + lane * 16);
+    if (DELAY > 0) {
+      const long long t0 = clock64();
+      while (clock64() - t0 < DELAY) {
+      }
+    }
+    __syncwarp();
+    phases ^= 1u << slot;
+    busy &= ~(1u << slot);
+    if (slot == oldest) oldest = (oldest + 1) % D;
+    issue(slot);
+  }
+  if (acc == 0x12345678) *sink = acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// mode 9: as mode 7, plus an L2 prefetch (cp.async.bulk.prefetch.tensor, no shared memory, no
+// completion) issued PD stages ahead of the shared-memory load: DRAM latency is covered by the
+// L2-resident window, the ring only has to cover the L2 -> SM hop.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* tm, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
+template <int W, int D, int PD, int DELAY>
+__global__ void __launch_bounds__(W * 32, 1)
+k_l2pf(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tm_pf, const uint8_t* base,
+       const int* pages, int npages, int* sink) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + W * D * kPage);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0)
+    for (int s = 0; s < D; ++s) mbar_init(&bars[warp * D + s], 1);
+  fence_barrier_init();
+  __syncthreads();
+  uint8_t* ring = smem + warp * D * kPage;
+  uint64_t* bar = bars + warp * D;
+  const int gw = blockIdx.x * W + warp, nw = gridDim.x * W;
+  const int nst = (npages - gw + nw - 1) / nw;
+  const uint64_t pol = l2_policy_evict_first();
+  auto page_of = [&](int s) { return pages[gw + s * nw]; };  // (probe only: plain dependent load)
+  auto prefetch = [&](int s) {
+    if (s < nst && lane == 0) tma_prefetch_4d(&tm_pf, 0, 0, 0, page_of(s));
+  };
+  auto issue = [&](int s) {
+    if (s < nst && lane == 0) {
+      const int slot = s % D;
+      const int pg = page_of(s);
+      mbar_arrive_expect_tx(&bar[slot], kPage);
+      tma_load_4d(ring + slot * kPage, &tm, &bar[slot], 0, 0, 0, pg, pol);
+      tma_load_4d(ring + slot * kPage + 4096, &tm, &bar[slot], 0, 16, 0, pg, pol);
+    }
+  };
+  for (int s = 0; s < PD; ++s) prefetch(s);
+  for (int s = 0; s < D; ++s) issue(s);
+  int acc = 0;
+  for (int s = 0; s < nst; ++s) {
+    const int slot = s % D;
+    prefetch(s + PD);
+    mbar_wait_dbg(&bar[slot], (s / D) & 1, 5, s);
+    acc ^= *reinterpret_cast<const int*>(ring + slot * kPage + lane * 16);
+    if (DELAY > 0) {
+      const long long t0 = clock64();
+      while (clock64() - t0 < DELAY) {
+      }
+    }
     __syncwarp();
     issue(s + D);
   }
@@ -333,6 +485,16 @@ int main(int argc, char** argv) {
     if (r != CUDA_SUCCESS) printf("encode tm4 failed %d\n", r);
   }
 
+  CUtensorMap tm7;
+  {
+    cuuint64_t gdim[4] = {64, 32, 2, pool_pages};
+    cuuint64_t gstr[3] = {256, 128, 8192};
+    cuuint32_t box[4] = {64, 16, 2, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    CUresult r = enc(&tm7, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, gdim, gstr, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) printf("encode tm7 failed %d\n", r);
+  }
   run("ldg128 U=4, 8 CTA/SM x 256thr", bytes, [&] { k_ldg<4><<<sms * 8, 256>>>(base, pg(), npages, sink); });
   run("ldg128 U=8, 8 CTA/SM x 256thr", bytes, [&] { k_ldg<8><<<sms * 8, 256>>>(base, pg(), npages, sink); });
   run("ldg128 U=16, 4 CTA/SM x 256thr", bytes, [&] { k_ldg<16><<<sms * 4, 256>>>(base, pg(), npages, sink); });
@@ -371,12 +533,13 @@ int main(int argc, char** argv) {
   RING(4, 8, 8, 2, tm4);
   RING(4, 8, 24, 1, tm4);
   RING(4, 4, 4, 4, tm4);
-#define SELF(MODE, W, D, TM)                                                                      \
+#define SELF(MODE, W, D, TM) SELFD(MODE, W, D, 0, TM)
+#define SELFD(MODE, W, D, DELAY, TM)                                                              \
   {                                                                                               \
-    auto k = k_self<MODE, W, D>;                                                                  \
+    auto k = k_self<MODE, W, D, DELAY>;                                                                  \
     const int sm = W * D * kPage + W * D * 8 + 1024;                                              \
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));                 \
-    run("self mode=" #MODE " W=" #W " D=" #D, bytes, [&] { k<<<sms, W * 32, sm>>>(TM, base, pg(), npages, sink); }); \
+    run("self mode=" #MODE " W=" #W " D=" #D " delay=" #DELAY, bytes, [&] { k<<<sms, W * 32, sm>>>(TM, base, pg(), npages, sink); }); \
   }
   SELF(5, 8, 2, tm4);
   SELF(5, 8, 3, tm4);
@@ -386,5 +549,43 @@ int main(int argc, char** argv) {
   SELF(6, 8, 3, tm4);
   SELF(6, 4, 6, tm4);
   SELF(6, 12, 2, tm4);
+  SELFD(7, 8, 3, 0, tm7);
+  SELFD(7, 8, 3, 500, tm7);
+  SELFD(7, 8, 3, 1000, tm7);
+  SELFD(7, 8, 3, 1500, tm7);
+  SELFD(7, 8, 3, 2000, tm7);
+  SELFD(7, 9, 3, 1500, tm7);
+  SELFD(7, 6, 4, 1500, tm7);
+  SELFD(7, 12, 2, 1500, tm7);
+  SELFD(7, 13, 2, 1500, tm7);
+  SELFD(7, 4, 6, 1500, tm7);
+  SELFD(7, 5, 5, 1500, tm7);
+#define OOO(W, D, DELAY)                                                                          \
+  {                                                                                               \
+    auto k = k_ooo<W, D, DELAY>;                                                                  \
+    const int sm = W * D * kPage + W * D * 8 + 1024;                                              \
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));                 \
+    run("ooo W=" #W " D=" #D " delay=" #DELAY, bytes, [&] { k<<<sms, W * 32, sm>>>(tm7, base, pg(), npages, sink); }); \
+  }
+#define L2PF(W, D, PD, DELAY)                                                                     \
+  {                                                                                               \
+    auto k = k_l2pf<W, D, PD, DELAY>;                                                             \
+    const int sm = W * D * kPage + W * D * 8 + 1024;                                              \
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));                 \
+    run("l2pf W=" #W " D=" #D " PD=" #PD " delay=" #DELAY, bytes, [&] { k<<<sms, W * 32, sm>>>(tm7, tm4, base, pg(), npages, sink); }); \
+  }
+  L2PF(8, 3, 6, 0);
+  L2PF(8, 3, 6, 1500);
+  L2PF(8, 3, 10, 1500);
+  L2PF(8, 3, 16, 1500);
+  L2PF(8, 2, 8, 1500);
+  L2PF(12, 2, 8, 1500);
+  L2PF(12, 2, 12, 1500);
+  OOO(8, 3, 0);
+  OOO(8, 3, 1000);
+  OOO(8, 3, 1500);
+  OOO(6, 4, 1500);
+  OOO(4, 6, 1500);
+  OOO(12, 2, 1500);
   return 0;
 }

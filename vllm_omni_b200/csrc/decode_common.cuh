@@ -19,8 +19,8 @@ constexpr int kHeadDim = 128;      // only head_size 128 is built (all Qwen-Omni
 constexpr int kTileTokens = 16;    // one MMA M-tile of KV tokens
 constexpr int kHeadsPerItem = 8;   // query heads packed in one N=8 tile
 constexpr int kSkMaxBatch = 2048;  // stream-K plan (tiles prefix) lives in shared memory
-constexpr int kSkWarps = 8;        // stream-K: warps per CTA, each with its own ring
-constexpr int kSkDepth = 3;        // stream-K: ring stages per warp (8 KiB each)
+constexpr int kSkWarps = 12;       // stream-K: warps per CTA, each with its own ring
+constexpr int kSkDepth = 2;        // stream-K: ring stages per warp (8 KiB each)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
