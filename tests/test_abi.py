@@ -68,10 +68,10 @@ def test_split_heuristic_is_pure_host_arithmetic(lib):
 def test_workspace_bytes_formula(lib):
     f = lib.b200attn_decode_workspace_bytes
     assert f(0, 32, 128, 4) == 0
-    # max(fixed-split need, stream-K need); without a GPU the stream-K part assumes 148 SMs x 8 warps
+    # max(fixed-split need, stream-K need); without a GPU the stream-K part assumes 148 SMs x 12 warps
     rows = 64 * 32 * 8
     fixed = rows * 128 * 4 + rows * 4 + 256
-    sk_rows = 2 * 148 * 8 * 8
+    sk_rows = 2 * 148 * 12 * 8
     sk = sk_rows * 128 * 4 + sk_rows * 4 + ((64 + 1 + 3) // 4 * 4) * 4 + 256
     assert f(64, 32, 128, 8) == max(fixed, sk)
     assert f(1, 8, 128, 1) == sk_rows * 128 * 4 + sk_rows * 4 + 4 * 4 + 256

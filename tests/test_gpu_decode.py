@@ -250,3 +250,56 @@ def test_full_size_properties_cfg3(lib, ragged):
                             inp2.softmax_scale)
     assert not torch.equal(inp.block_table, inp2.block_table)
     assert torch.equal(out2, base)
+
+
+# ------------------------------------------------------------------------------------------------
+# FP8-e4m3 KV cache. Tolerance: the oracle is fed the SAME quantised cache (dequantised with the
+# same scales), so this isolates kernel arithmetic from quantisation error: 2e-3 as for bf16.
+# The quantisation error itself (vs the unquantised history) is reported, not gated: e4m3 keeps
+# 3 mantissa bits, ~2^-4 relative per element.
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("per_head", [True, False])
+@pytest.mark.parametrize("lens", [[1], [16], [17], [31, 32, 33], [5, 0, 48, 0], [300, 129, 2, 511]])
+def test_fp8_decode_vs_oracle_small(lib, lens, per_head):
+    c = make_case(lens, hq=8, hkv=2, seed=sum(lens) + 7, fp8=True, per_head_scale=per_head)
+    out, lse = run_device(c, ops.VARIANT_AUTO, 0)
+    check(c, out, lse)
+
+
+@pytest.mark.parametrize("hq,hkv", [(32, 4), (28, 4), (16, 2), (4, 1), (4, 4), (16, 1), (24, 2)])
+def test_fp8_decode_gqa_group_shapes(lib, hq, hkv):
+    c = make_case([200, 77, 16, 1000], hq=hq, hkv=hkv, seed=hq * 10 + hkv + 1, fp8=True)
+    out, lse = run_device(c, ops.VARIANT_STREAMK, 0)
+    check(c, out, lse)
+
+
+def test_fp8_masked_tail_and_block_sizes(lib):
+    c = make_case([1, 17, 45, 130], hq=8, hkv=2, seed=5, fp8=True, garbage_fill=True)
+    out, lse = run_device(c, ops.VARIANT_AUTO, 0)
+    check(c, out, lse)
+    for bs in (32, 64):
+        c = make_case([bs + 3, 5 * bs, 17], hq=8, hkv=2, bs=bs, seed=bs, fp8=True)
+        out, lse = run_device(c, ops.VARIANT_AUTO, 0)
+        check(c, out, lse)
+
+
+def test_fp8_named_shape_cfg4_full_context(lib):
+    """BASELINE cfg4 (fp8 KV, 8k context, 32q/4kv) with the batch reduced so the oracle runs in seconds."""
+    wl = workloads.WORKLOADS["cfg4"]
+    c = make_case([wl.ctx, wl.ctx - 5], hq=wl.total_q_heads, hkv=wl.total_kv_heads, seed=104, fp8=True)
+    out, lse = run_device(c, ops.VARIANT_AUTO, 0)
+    e, l2 = check(c, out, lse)
+    # reported: distance to the UNQUANTISED attention (quantisation error of the cache itself)
+    nb = c.num_blocks
+    raw = layout.alloc_kv_cache(nb, 16, wl.total_kv_heads, 128, "auto", "cpu")
+    oracle.ref_reshape_and_cache(c.hist_k, c.hist_v, raw[0], raw[1], c.slots, False, None, None)
+    ref_raw, _ = c_oracle.paged_decode(c.q, raw[0], raw[1], c.block_table, c.seq_lens, c.scale)
+    print(f"cfg4 fp8: kernel excess_rel_err={e:.2e} kernel_rel_l2={l2:.2e}; "
+          f"vs unquantised attention rel_l2={rel_l2(out, ref_raw):.3e} (quantisation, not gated)")
+    assert rel_l2(out, ref_raw) < 0.1
+
+
+def test_fp8_rejects_fixed_split_variants(lib):
+    c = make_case([100], hq=8, hkv=2, seed=1, fp8=True)
+    with pytest.raises(_lib.B200AttnError, match="EUNSUPPORTED"):
+        run_device(c, ops.VARIANT_STREAM, 2)

@@ -159,9 +159,9 @@ int get_kv_map(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, 
 // SWIZZLE_128B rows — the layout the math reads with ldmatrix.
 thread_local KvMapEntry g_maps5[kMapCache];
 
-int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv, int32_t bs,
+int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv, int32_t bs, bool fp8,
                 const CUtensorMap** out_map) {
-  KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, 0};
+  KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, fp8 ? 1 : 0};
   const size_t slot = (reinterpret_cast<uintptr_t>(ptr) >> 8) % kMapCache;
   KvMapEntry& e = g_maps5[slot];
   if (e.valid && e.key == key) {
@@ -170,6 +170,28 @@ int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb,
   }
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled entry point not found");
+  if (fp8) {
+    // e4m3 cache: a 128-element row is exactly the 128 B swizzle span -> 4-D map
+    // [128][slot][head][block], box 128 x 16: one 2 KiB tile per op
+    const int64_t f_head = hkv > 1 ? sh : 128, f_block = nb > 1 ? sb : 128;
+    cuuint64_t gdim[4] = {128, static_cast<cuuint64_t>(bs), static_cast<cuuint64_t>(hkv), static_cast<cuuint64_t>(nb)};
+    cuuint64_t gstr[3] = {static_cast<cuuint64_t>(ss), static_cast<cuuint64_t>(f_head), static_cast<cuuint64_t>(f_block)};
+    cuuint32_t box[4] = {128, static_cast<cuuint32_t>(kTileTokens), 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&e.map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      e.valid = false;
+      return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled (fp8 4-D) failed (%d): strides [%lld,%lld,%lld] B",
+                  static_cast<int>(r), static_cast<long long>(ss), static_cast<long long>(f_head),
+                  static_cast<long long>(f_block));
+    }
+    e.key = key;
+    e.valid = true;
+    *out_map = &e.map;
+    return 0;
+  }
   // a size-1 dimension may carry any stride: give it a harmless one
   const int64_t st_slot = ss * 2;
   const int64_t st_head = hkv > 1 ? sh * 2 : 256;
@@ -446,7 +468,15 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     if ((q_stride_tok % 2) || (reinterpret_cast<uintptr_t>(q) % 4))
       return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
     const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
-    if (fp8) return fail(B200ATTN_EUNSUPPORTED, "fp8 KV decode is not built yet");
+    if (fp8) {
+      if (variant != B200ATTN_VARIANT_STREAMK)
+        return fail(B200ATTN_EUNSUPPORTED,
+                    "fp8 KV decode is built for the stream-K schedule only (variant AUTO/STREAMK, num_splits 0, "
+                    "batch <= %d, block_size = 16 * 2^k)", kSkMaxBatch);
+      if (k_scale == nullptr || v_scale == nullptr) return fail(B200ATTN_EINVAL, "fp8 cache needs scales");
+      if (scale_numel != 1 && scale_numel != num_kv_heads)
+        return fail(B200ATTN_EINVAL, "scale_numel %d must be 1 or num_kv_heads", scale_numel);
+    }
     p.q = static_cast<const __nv_bfloat16*>(q);
     p.q_stride_tok = q_stride_tok;
     p.k_cache = static_cast<const uint8_t*>(k_cache);
@@ -492,13 +522,13 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     } else if (variant == B200ATTN_VARIANT_STREAMK) {
       const CUtensorMap *mk = nullptr, *mv = nullptr;
       if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
-                               num_kv_heads, block_size, &mk))
+                               num_kv_heads, block_size, fp8, &mk))
         return rc;
       const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
       if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
-                               num_kv_heads, block_size, &mv))
+                               num_kv_heads, block_size, fp8, &mv))
         return rc;
-      e = launch_decode_streamk(tm_k, *mv, p, sms, stream);
+      e = launch_decode_streamk(tm_k, *mv, p, fp8, sms, stream);
     } else {
       return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
     }

@@ -19,10 +19,10 @@ cudaError_t launch_decode_tma(const CUtensorMap& tm_k, const CUtensorMap& tm_v, 
 cudaError_t launch_decode_cpasync(const DecodeParams& p, cudaStream_t stream);
 cudaError_t launch_decode_stream(const DecodeParams& p, int grid, cudaStream_t stream);
 size_t decode_stream_smem_bytes();
-cudaError_t launch_decode_streamk(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, int grid,
-                                  cudaStream_t stream);
+cudaError_t launch_decode_streamk(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, bool fp8,
+                                  int grid, cudaStream_t stream);
 cudaError_t launch_streamk_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream);
-size_t decode_streamk_smem_bytes();
+size_t decode_streamk_smem_bytes(bool fp8);
 size_t decode_tma_smem_bytes();
 size_t decode_cpasync_smem_bytes();
 
