@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 4
+#define B200ATTN_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -104,6 +104,14 @@ B200ATTN_API int32_t b200attn_decode_num_splits(int32_t batch, int32_t num_q_hea
 /* Bytes of split-K workspace for (max_batch, num_q_heads, head_size, max_splits). */
 B200ATTN_API size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads,
                                        int32_t head_size, int32_t max_splits);
+
+/*
+ * One-time preparation of a decode workspace: zeroes its control words (the first 256 bytes:
+ * the stream-K claim counter and finished-warp counter). Call once after allocating the
+ * workspace (or allocate it zero-filled); the library leaves the control words zero after
+ * every launch, so graphs can be replayed without re-initialising.
+ */
+B200ATTN_API int b200attn_workspace_init(void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * Paged decode attention (query length 1 per sequence). Replaces the decode branch of
@@ -222,6 +230,21 @@ B200ATTN_API int b200attn_gather_kv(
     const int32_t* block_ids, int32_t num_block_ids, int32_t seq_len,
     int32_t num_kv_heads, int32_t head_size, int32_t block_size, int32_t kv_dtype,
     void* dst, void* stream);
+
+/*
+ * Debug aid for profiling the stream-K schedule: when set (thread-local, device pointer to
+ * 3 x 8 bytes per warp of the persistent grid, or NULL to disable), every warp of the next
+ * stream-K decode launches records its {entry, static-chunk end, end} %globaltimer stamps.
+ */
+B200ATTN_API void b200attn_debug_set_trace(void* device_buffer);
+
+/*
+ * The stream-K schedule for `total_tiles` KV tiles on `num_warps` warps (pure host arithmetic,
+ * the same function the kernels evaluate): out5 = {static region S, static tiles per warp,
+ * tiles per dynamic chunk, dynamic chunks, dynamic enabled}. Exported so tests can pin it.
+ */
+B200ATTN_API void b200attn_debug_sk_schedule(int64_t total_tiles, int32_t num_warps, int32_t dyn_shift,
+                                             int64_t* out5);
 
 #ifdef __cplusplus
 }

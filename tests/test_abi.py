@@ -69,12 +69,14 @@ def test_workspace_bytes_formula(lib):
     f = lib.b200attn_decode_workspace_bytes
     assert f(0, 32, 128, 4) == 0
     # max(fixed-split need, stream-K need); without a GPU the stream-K part assumes 148 SMs x 12 warps
+    # layout: 256 B of control words, partial O rows, partial LSEs (+ stream-K: the tiles-prefix plan)
     rows = 64 * 32 * 8
-    fixed = rows * 128 * 4 + rows * 4 + 256
-    sk_rows = 2 * 148 * 12 * 8
-    sk = sk_rows * 128 * 4 + sk_rows * 4 + ((64 + 1 + 3) // 4 * 4) * 4 + 256
+    fixed = 256 + rows * 128 * 4 + rows * 4 + 256
+    # stream-K: two partial slots per chunk; one static chunk per warp (+1), no claimed chunks by default
+    sk_rows = 2 * (148 * 12 + 1) * 8
+    sk = 256 + sk_rows * 128 * 4 + sk_rows * 4 + ((64 + 1 + 3) // 4 * 4) * 4 + 256
     assert f(64, 32, 128, 8) == max(fixed, sk)
-    assert f(1, 8, 128, 1) == sk_rows * 128 * 4 + sk_rows * 4 + 4 * 4 + 256
+    assert f(1, 8, 128, 1) == 256 + sk_rows * 128 * 4 + sk_rows * 4 + 4 * 4 + 256
 
 
 def test_zero_token_calls_are_noops_without_a_gpu(lib):

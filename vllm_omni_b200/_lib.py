@@ -12,7 +12,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 KV_BF16 = 0
 KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0
@@ -65,6 +65,9 @@ SIGNATURES: dict[str, tuple] = {
         _vp, _vp, _i32, _vp]),
     "b200attn_decode_num_splits": (_i32, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
+    "b200attn_workspace_init": (C.c_int, [_vp, _sz, _vp]),
+    "b200attn_debug_set_trace": (None, [_vp]),
+    "b200attn_debug_sk_schedule": (None, [_i64, _i32, _i32, C.POINTER(_i64)]),
     "b200attn_paged_decode": (C.c_int, _DECODE_ARGS),
     "b200attn_paged_decode_partial": (C.c_int, _DECODE_ARGS),
     "b200attn_lse_reduce": (C.c_int, [

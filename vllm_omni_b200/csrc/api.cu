@@ -237,16 +237,35 @@ int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64
 
 // stream-K workspace: 2 partial slots per warp of the persistent grid (O rows then LSE), then the
 // tiles-prefix plan.
+constexpr size_t kWsCtrlBytes = 256;
 size_t fixed_workspace_bytes(int batch, int num_q_heads, int head_size, int splits) {
   const size_t rows = static_cast<size_t>(batch) * num_q_heads * splits;
-  return rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
+  return kWsCtrlBytes + rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
 }
-size_t sk_part_rows(int sms) { return static_cast<size_t>(2) * sms * kSkWarps * kHeadsPerItem; }
+// Workspace layout (both schedules): [0, 256) control words kept zero between launches (stream-K
+// claim counter + finished-warp counter), then the partial O rows, the partial LSEs and (stream-K)
+// the tiles-prefix plan. Stream-K has two partial slots per chunk: one static chunk per warp of the
+// persistent grid plus at most kSkDynPerWarp dynamic chunks per warp.
+// Share of the stream scheduled dynamically (B200ATTN_SK_DYN = shift, share = 1 / 2^shift). Off by
+// default: measured on B200 (profiles/README.md) it evens out the warps' finish times but the kernel
+// is HBM-bound throughout, so the gain (<= 2 %) is smaller than the extra partials cost the reduce.
+int sk_dyn_shift() {
+  const char* v = getenv("B200ATTN_SK_DYN");
+  if (v == nullptr || *v == '\0') return kSkDynShiftDefault;
+  const int x = atoi(v);
+  return x < 0 ? 0 : (x > 8 ? 8 : x);
+}
+size_t sk_part_rows(int sms) {
+  const int per_warp = 1 + (sk_dyn_shift() > 0 ? kSkDynPerWarp : 0);
+  return static_cast<size_t>(2) * (static_cast<size_t>(sms) * kSkWarps * per_warp + 1) * kHeadsPerItem;
+}
 size_t sk_workspace_bytes(int batch, int sms) {
   const size_t rows = sk_part_rows(sms);
-  return rows * kHeadDim * sizeof(float) + rows * sizeof(float) +
+  return kWsCtrlBytes + rows * kHeadDim * sizeof(float) + rows * sizeof(float) +
          ((static_cast<size_t>(batch) + 1 + 3) / 4 * 4) * sizeof(int32_t) + 256;
 }
+
+thread_local unsigned long long* g_trace = nullptr;
 
 constexpr int kMaxSplits = 128;
 constexpr int kMinTilesPerSplit = 8;  // 128 tokens
@@ -317,7 +336,7 @@ int b200attn_reshape_and_cache(const void* key, const void* value, int64_t key_s
   p.k_scale = k_scale;
   p.v_scale = v_scale;
   p.scale_stride = scale_numel > 1 ? 1 : 0;
-  cudaError_t e = launch_cache_write(p, fp8, sms, static_cast<cudaStream_t>(stream));
+  cudaError_t e = launch_cache_write(p, fp8, sms, env_flag("B200ATTN_PDL", true), static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "cache_write launch");
 }
 
@@ -414,7 +433,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   if (use_sk) {
     num_splits = 1;
     const size_t rows = sk_part_rows(sms);
-    part_o = static_cast<float*>(workspace);
+    part_o = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + kWsCtrlBytes);
     part_lse = part_o + rows * kHeadDim;
     plan_cum = reinterpret_cast<int32_t*>(part_lse + rows);
   } else {
@@ -434,7 +453,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       if (reinterpret_cast<uintptr_t>(workspace) % 16)
         return fail(B200ATTN_EINVAL, "workspace must be 16-byte aligned");
       const size_t rows = static_cast<size_t>(batch) * num_q_heads * num_splits;
-      part_o = static_cast<float*>(workspace);
+      part_o = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + kWsCtrlBytes);
       part_lse = part_o + rows * head_size;
     }
   }
@@ -455,6 +474,9 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   p.part_o = part_o;
   p.part_lse = part_lse;
   p.plan_cum = plan_cum;
+  p.sk_ctrl = static_cast<int32_t*>(workspace);
+  p.sk_dyn_shift = use_sk ? sk_dyn_shift() : 0;
+  p.trace = g_trace;
   const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
   if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
   p.total_items = static_cast<int32_t>(items);
@@ -528,7 +550,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
                                num_kv_heads, block_size, fp8, &mv))
         return rc;
-      e = launch_decode_streamk(tm_k, *mv, p, fp8, sms, stream);
+      e = launch_decode_streamk(tm_k, *mv, p, fp8, sms, env_flag("B200ATTN_PDL", true), stream);
     } else {
       return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
     }
@@ -598,6 +620,24 @@ int b200attn_lse_reduce(void* out, int64_t out_stride_tok, float* lse, const int
                      1.f, B200ATTN_KV_BF16, nullptr, nullptr, 1, num_splits, variant,
                      const_cast<void*>(workspace), workspace_bytes, stream);
 }
+
+int b200attn_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {
+  if (workspace == nullptr || workspace_bytes < kWsCtrlBytes)
+    return fail(B200ATTN_EWORKSPACE, "workspace must hold at least %zu bytes", kWsCtrlBytes);
+  cudaError_t e = cudaMemsetAsync(workspace, 0, kWsCtrlBytes, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "workspace_init memset");
+}
+
+void b200attn_debug_sk_schedule(int64_t total_tiles, int32_t num_warps, int32_t dyn_shift, int64_t* out5) {
+  const SkSchedule sc = sk_schedule(total_tiles, num_warps, dyn_shift);
+  out5[0] = sc.S;
+  out5[1] = sc.ts;
+  out5[2] = sc.cd;
+  out5[3] = sc.nd;
+  out5[4] = sc.dyn ? 1 : 0;
+}
+
+void b200attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<unsigned long long*>(device_buffer); }
 
 int b200attn_paged_prefill(const void*, int64_t, const void*, const void*, int64_t, int64_t, int64_t,
                            int64_t, void*, int64_t, const int32_t*, int64_t, const int32_t*,

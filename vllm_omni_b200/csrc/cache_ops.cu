@@ -13,6 +13,11 @@ namespace b200 {
 
 template <bool FP8>
 __global__ void __launch_bounds__(256) cache_write_kernel(const CacheWriteParams p) {
+  // programmatic dependent launch: this grid may be resident before the previous kernel on the
+  // stream has finished; nothing is read or written before the wait, and the kernel after this one
+  // (the decode) may start its own prologue right away
+  griddep_wait();
+  griddep_launch_dependents();
   const int lanes_per_row = p.head_size / 8;  // 8 bf16 = 16 B per lane; 16 for head_size 128
   const int64_t rows = static_cast<int64_t>(p.num_tokens) * p.num_kv_heads * 2;
   const int64_t total = rows * lanes_per_row;
@@ -58,7 +63,7 @@ __global__ void __launch_bounds__(256) cache_write_kernel(const CacheWriteParams
   }
 }
 
-cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms,
+cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms, bool pdl,
                                cudaStream_t stream) {
   const int64_t total =
       static_cast<int64_t>(p.num_tokens) * p.num_kv_heads * 2 * (p.head_size / 8);
@@ -67,11 +72,17 @@ cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms,
   int64_t blocks = (total + threads - 1) / threads;
   const int64_t cap = static_cast<int64_t>(num_sms) * 8;  // whole waves of resident CTAs
   if (blocks > cap) blocks = cap;
-  if (fp8)
-    cache_write_kernel<true><<<static_cast<unsigned>(blocks), threads, 0, stream>>>(p);
-  else
-    cache_write_kernel<false><<<static_cast<unsigned>(blocks), threads, 0, stream>>>(p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(blocks));
+  cfg.blockDim = dim3(threads);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return fp8 ? cudaLaunchKernelEx(&cfg, cache_write_kernel<true>, p)
+             : cudaLaunchKernelEx(&cfg, cache_write_kernel<false>, p);
 }
 
 // Gather of one request's rows: dst[s, h, :] = cache[block_ids[s / bs], s % bs, h, :], s < seq_len.

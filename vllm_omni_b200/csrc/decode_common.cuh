@@ -21,6 +21,9 @@ constexpr int kHeadsPerItem = 8;   // query heads packed in one N=8 tile
 constexpr int kSkMaxBatch = 2048;  // stream-K plan (tiles prefix) lives in shared memory
 constexpr int kSkWarps = 12;       // stream-K: warps per CTA, each with its own ring
 constexpr int kSkDepth = 2;        // stream-K: ring stages per warp (8 KiB each)
+constexpr int kSkDynPerWarp = 4;   // stream-K: dynamic (claimed) chunks per warp on average, at most
+constexpr int kSkClaimLead = 2;    // stream-K: tiles left in the front's chunk when the next one is claimed
+constexpr int kSkDynShiftDefault = 0;  // stream-K: dynamic share of the stream = 1 / 2^shift (0 = all static)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -53,7 +56,41 @@ struct DecodeParams {
   float* part_o;         // [batch, Hq, num_splits, 128] f32, normalised partial outputs
   float* part_lse;       // [batch, Hq, num_splits] f32, natural log
   int32_t* plan_cum;     // stream-K only: [batch + 1] exclusive prefix of tiles per sequence
+  int32_t* sk_ctrl;      // stream-K only: {claim counter, finished-warp counter}, zero between launches
+  int32_t sk_dyn_shift;  // stream-K only: dynamic share of the stream = 1 / 2^shift (0 = all static)
+  unsigned long long* trace;  // debug: per-warp {entry, static end, end} globaltimer stamps, or null
 };
+
+// Stream-K schedule, computed identically by the decode and the reduce kernel from the tile total:
+// the first S tiles are cut into nw static chunks of ts tiles (chunk id = global warp id); the
+// remaining total - S tiles (about tpw >> dyn_shift per warp) are cut into nd dynamic chunks of cd
+// tiles (chunk id = nw + j) that the warps claim from a global counter as they finish — SMs do not
+// stream at equal rates (sm__cycles_active min/avg/max = 111k/140k/151k in the static-only capture),
+// so the tail is balanced at run time.
+struct SkSchedule {
+  int64_t total;  // tiles x head-groups in the step
+  int64_t S;      // static region [0, S)
+  int ts;         // static tiles per warp
+  int cd;         // tiles per dynamic chunk
+  int nd;         // dynamic chunks
+  bool dyn;
+};
+__host__ __device__ __forceinline__ SkSchedule sk_schedule(int64_t total, int nw, int dyn_shift) {
+  SkSchedule sc;
+  sc.total = total;
+  const int64_t tpw64 = (total + nw - 1) / nw;
+  const int tpw = static_cast<int>(tpw64 < 1 ? 1 : tpw64);
+  int dpw = dyn_shift >= 1 ? (tpw >> dyn_shift) : 0;  // dynamic tiles per warp (average)
+  if (dpw < 2) dpw = 0;
+  sc.ts = tpw - dpw;
+  const int64_t s_all = static_cast<int64_t>(nw) * sc.ts;
+  sc.S = s_all < total ? s_all : total;
+  int cd = (dpw + kSkDynPerWarp - 1) / kSkDynPerWarp;
+  sc.cd = cd < 2 ? 2 : cd;
+  sc.nd = static_cast<int>((total - sc.S + sc.cd - 1) / sc.cd);
+  sc.dyn = dpw > 0 && sc.nd > 0;
+  return sc;
+}
 
 struct WorkItem {
   int b, kvh, split, sub;

@@ -20,7 +20,7 @@ cudaError_t launch_decode_cpasync(const DecodeParams& p, cudaStream_t stream);
 cudaError_t launch_decode_stream(const DecodeParams& p, int grid, cudaStream_t stream);
 size_t decode_stream_smem_bytes();
 cudaError_t launch_decode_streamk(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, bool fp8,
-                                  int grid, cudaStream_t stream);
+                                  int grid, bool pdl, cudaStream_t stream);
 cudaError_t launch_streamk_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream);
 size_t decode_streamk_smem_bytes(bool fp8);
 size_t decode_tma_smem_bytes();
@@ -45,7 +45,7 @@ struct CacheWriteParams {
   const float* v_scale;
   int32_t scale_stride;
 };
-cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms, cudaStream_t stream);
+cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms, bool pdl, cudaStream_t stream);
 
 struct GatherParams {
   const uint8_t* cache;

@@ -61,6 +61,29 @@ __device__ __forceinline__ int sk_load_ids(const DecodeParams& p, int b, int n_t
   return (b < p.batch && pg < pages) ? __ldg(p.block_table + static_cast<int64_t>(b) * p.bt_stride + pg) : 0;
 }
 
+// Locate stream position g (in tiles x head-groups, see the file header) -> (sequence, hs, tile).
+__device__ __forceinline__ SkPos sk_locate(const int32_t* cum, int batch, int hs_count, int64_t g) {
+  SkPos o;
+  const int key = static_cast<int>(g / hs_count);  // cum[b] <= key < cum[b+1]
+  int lo_b = 0, hi_b = batch;                      // invariant: cum[lo_b] <= key < cum[hi_b]
+  while (hi_b - lo_b > 1) {
+    const int mid = (lo_b + hi_b) >> 1;
+    if (cum[mid] <= key) lo_b = mid; else hi_b = mid;
+  }
+  o.b = lo_b;
+  o.n = cum[lo_b + 1] - cum[lo_b];
+  const int r = static_cast<int>(g - static_cast<int64_t>(cum[lo_b]) * hs_count);
+  o.hs = r / o.n;
+  o.tile = r % o.n;
+  return o;
+}
+
+__device__ __forceinline__ uint64_t sk_globaltimer() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
 template <int W, int D, bool FP8>
 __global__ void __launch_bounds__(W * 32, 1)
 paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
@@ -72,6 +95,7 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
       *reinterpret_cast<SkSmem<W, D, SB>*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint64_t t_entry = p.trace != nullptr ? sk_globaltimer() : 0;
 
   if (lane == 0) {
 #pragma unroll
@@ -82,6 +106,10 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
       tma_prefetch_desc(&tm_v);
     }
   }
+  // Programmatic dependent launch: everything above overlapped the previous kernel on the stream
+  // (the cache write); nothing it may have produced is read before this point.
+  griddep_wait();
+  griddep_launch_dependents();
   // ---- per-CTA plan: tiles per sequence and their exclusive prefix (batch <= kSkMaxBatch)
   {
     const int per = (p.batch + W * 32 - 1) / (W * 32);
@@ -115,72 +143,94 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
   }
 
   const int hs_count = p.num_kv_heads * p.subgroups;
-  const int64_t total = static_cast<int64_t>(sm.cum[p.batch]) * hs_count;
   const int nw = gridDim.x * W;
-  const int tpw = static_cast<int>(max(static_cast<int64_t>(1), (total + nw - 1) / nw));
+  const SkSchedule sc = sk_schedule(static_cast<int64_t>(sm.cum[p.batch]) * hs_count, nw, p.sk_dyn_shift);
   const int gw = blockIdx.x * W + warp;
-  const int64_t g0 = static_cast<int64_t>(gw) * tpw;
-  if (g0 >= total) return;
-  const int count = static_cast<int>(min(static_cast<int64_t>(tpw), total - g0));
-
-  // ---- locate the chunk start
-  SkPos cs;
-  {
-    const int key = static_cast<int>(g0 / hs_count);  // cum[b] <= key < cum[b+1]
-    int lo_b = 0, hi_b = p.batch;                      // invariant: cum[lo_b] <= key < cum[hi_b]
-    while (hi_b - lo_b > 1) {
-      const int mid = (lo_b + hi_b) >> 1;
-      if (sm.cum[mid] <= key) lo_b = mid; else hi_b = mid;
-    }
-    cs.b = lo_b;
-    cs.n = sm.cum[lo_b + 1] - sm.cum[lo_b];
-    const int r = static_cast<int>(g0 - static_cast<int64_t>(sm.cum[lo_b]) * hs_count);
-    cs.hs = r / cs.n;
-    cs.tile = r % cs.n;
-  }
-  SkPos pf = cs;
 
   const SkLane sl = sk_make_lane(lane);
   const uint32_t ring0 = smem_u32(sm.ring[warp][0]);
-  // prefetch-front state
-  int pf_page0 = (pf.tile >> p.tpp_shift) & ~31;  // block-id window of the item the front is in
-  int ids = sk_load_ids(p, pf.b, pf.n, pf_page0, lane);
-  int pf_kvh = pf.hs / p.subgroups;
   const uint32_t bar0 = smem_u32(&sm.bar[warp][0]);
   const uint64_t pol = l2_policy_evict_first();  // KV pages are streamed once per step
-  int pf_left = count;     // stages the front still has to issue
-  int pf_items_ahead = 0;  // item boundaries crossed by the front and not yet by the math (0 or 1)
-  bool pf_fresh = false;   // the front stands on tile 0 of an item it has not prepared yet
+
+  // ---- chunk bookkeeping. The warp's first chunk is its static one; further chunks are claimed
+  // from the global counter. `nxt_*` is the one chunk the prefetch front may be ahead of the math.
+  bool front_ahead = false;  // the front stands in chunk nxt_*, the math still in the previous one
+  bool pf_done = false;      // no chunk left to claim
+  bool first = true;         // the static chunk has not been handed out yet
+  SkPos nxt_pos{0, 0, 0, 1};
+  int nxt_count = 0, nxt_id = 0;
+  int claim_val = 0;
+  bool claim_out = false;  // an atomic claim is in flight (result in lane 0's claim_val)
+
+  // prefetch-front state
+  SkPos pf{0, 0, 0, 1};
+  int pf_left = 0;         // tiles of the front's chunk still to issue
+  int pf_page0 = 0, ids = 0, pf_kvh = 0;
+  int pf_items_ahead = 0;  // item/chunk starts prepared by the front and not yet taken by the math (0 or 1)
+  bool pf_fresh = false;   // the front stands on a tile whose item it has not prepared yet
   int pslot = 0, pending = 0;
   // math state
-  int cs_left = count, cslot = 0;
+  SkPos cs{0, 0, 0, 1};
+  int cs_left = 0, cslot = 0, cur_id = 0;
   uint32_t cphase = 0;  // parity of the current pass over the ring
-  int seg_start = cs.tile;  // first tile of this warp's segment of the current item
+  int seg_start = 0;    // first tile of this warp's segment of the current item
   uint32_t qf[8][2], qf_n[8][2];
+#pragma unroll
+  for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = qf_n[kk][0] = qf_n[kk][1] = 0u;
   // softmax scale in the log2 domain; fp8: times the K dequantisation scale of the item's kv head
   float scale = p.scale_log2, scale_n = p.scale_log2;
-  {
-    WorkItem w;
-    w.b = cs.b;
-    w.kvh = cs.hs / p.subgroups;
-    w.sub = cs.hs % p.subgroups;
-    if (FP8) {
-      sk_load_q_f16(p, w.b, w.kvh, w.sub, lane, qf);
-      scale = p.scale_log2 * __ldg(p.k_scale + w.kvh * p.scale_stride);
-    } else {
-      load_q_frags(p, w, lane, qf);
-    }
-  }
   WarpState st;
   state_reset(st);
-  const int piece_base = gw * 2;
+  uint64_t t_static_end = 0;
 
-  while (cs_left > 0) {
+  while (true) {
     // ================= keep the ring full (one issue per iteration in steady state) ==========
-    while (pending < D && pf_left > 0) {
+    while (pending < D) {
+      // claim the next dynamic chunk shortly before the front runs out of its current one, so the
+      // atomic's round trip hides behind the tiles still to be issued
+      if (sc.dyn && !first && !claim_out && !pf_done && pf_left <= kSkClaimLead) {
+        if (lane == 0) claim_val = atomicAdd(p.sk_ctrl, 1);
+        claim_out = true;
+      }
+      if (pf_left == 0) {
+        if (pf_done || front_ahead) break;  // one chunk descriptor can be outstanding
+        int64_t g0;
+        int cnt, id;
+        if (first) {
+          first = false;
+          g0 = static_cast<int64_t>(gw) * sc.ts;
+          cnt = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(sc.ts), sc.S - g0)));
+          id = gw;
+          if (cnt == 0) {
+            if (!sc.dyn) pf_done = true;
+            continue;  // nothing static for this warp: go claim (or stop)
+          }
+        } else {
+          if (!sc.dyn) {
+            pf_done = true;
+            break;
+          }
+          const int j = __shfl_sync(0xffffffffu, claim_val, 0);
+          claim_out = false;
+          if (j >= sc.nd) {
+            pf_done = true;
+            break;
+          }
+          g0 = sc.S + static_cast<int64_t>(j) * sc.cd;
+          cnt = static_cast<int>(min(static_cast<int64_t>(sc.cd), sc.total - g0));
+          id = nw + j;
+        }
+        pf = sk_locate(sm.cum, p.batch, hs_count, g0);
+        pf_left = cnt;
+        nxt_pos = pf;
+        nxt_count = cnt;
+        nxt_id = id;
+        front_ahead = true;
+        pf_fresh = true;
+      }
       if (pf_fresh) {
-        // the front stands on the first tile of an item it has not prepared yet; qf_n can hold one
-        // prepared item, so the front never runs two item boundaries ahead of the math
+        // the front stands on the first tile of an item (or chunk) it has not prepared yet; qf_n can
+        // hold one prepared item, so the front never runs two starts ahead of the math
         if (pf_items_ahead == 1) break;
         WorkItem w;
         w.b = pf.b;
@@ -192,8 +242,8 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
         } else {
           load_q_frags(p, w, lane, qf_n);
         }
-        pf_page0 = 0;
-        ids = sk_load_ids(p, pf.b, pf.n, 0, lane);
+        pf_page0 = (pf.tile >> p.tpp_shift) & ~31;
+        ids = sk_load_ids(p, pf.b, pf.n, pf_page0, lane);
         pf_kvh = w.kvh;
         pf_items_ahead = 1;
         pf_fresh = false;
@@ -223,6 +273,25 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
       pf_fresh = (pf.tile == 0);
     }
 
+    if (cs_left == 0) {
+      // the math finished its chunk (the segment was stored with its last tile): take the next one
+      if (!front_ahead) break;  // nothing left
+      if (p.trace != nullptr && cur_id < nw && t_static_end == 0 && nxt_id >= nw) t_static_end = sk_globaltimer();
+      cs = nxt_pos;
+      cs_left = nxt_count;
+      cur_id = nxt_id;
+      seg_start = cs.tile;
+      front_ahead = false;
+#pragma unroll
+      for (int kk = 0; kk < 8; ++kk) {
+        qf[kk][0] = qf_n[kk][0];
+        qf[kk][1] = qf_n[kk][1];
+      }
+      scale = scale_n;
+      pf_items_ahead = 0;
+      continue;
+    }
+
     // ================= math on the oldest stage =================
     mbar_wait(&sm.bar[warp][cslot], cphase);
     const bool item_done = (cs.tile + 1 == cs.n);
@@ -240,13 +309,13 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
     if (item_done || cs_left == 0) {
       // the slot just drained is free: use it to transpose the fragments
       const bool whole = item_done && seg_start == 0;
-      const int piece = piece_base + (seg_start > 0 ? 0 : 1);
+      const int piece = cur_id * 2 + (seg_start > 0 ? 0 : 1);
       sk_store<FP8>(p, st, cs.b, cs.hs, whole, piece, reinterpret_cast<float*>(sm.ring[warp][cslot]), lane);
       fence_proxy_async_smem();  // the slot was written through the generic proxy; TMA refills it next
       __syncwarp();
       state_reset(st);
       seg_start = 0;
-      if (cs_left > 0) {
+      if (cs_left > 0) {  // next item of the same chunk: the front prepared it already
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           qf[kk][0] = qf_n[kk][0];
@@ -262,71 +331,170 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
     }
     sk_advance(sm.cum, p.batch, hs_count, cs);
   }
+
+  // ---- the last warp to finish re-arms the claim counter for the next launch
+  if (sc.dyn && lane == 0) {
+    __threadfence();
+    const int old = atomicAdd(p.sk_ctrl + 1, 1);
+    if (old == nw - 1) {
+      p.sk_ctrl[0] = 0;
+      p.sk_ctrl[1] = 0;
+      __threadfence();
+    }
+  }
+  if (p.trace != nullptr && lane == 0) {
+    const uint64_t t_end = sk_globaltimer();
+    p.trace[gw * 3 + 0] = t_entry;
+    p.trace[gw * 3 + 1] = t_static_end != 0 ? t_static_end : t_end;
+    p.trace[gw * 3 + 2] = t_end;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
-// Merge of the partials left by chunk boundaries. One warp per (sequence, query head) row; rows
-// finished by a single warp were already written by it; rows of empty sequences are zeroed here.
+// Merge of the partials left by chunk boundaries (the separate log-sum-exp reduce kernel). One CTA
+// of 8 warps per (sequence, kv head, head sub-group) item: a partial is one contiguous 4 KiB block
+// (8 heads x 128 floats) plus 8 LSEs, so warp w merges the pieces k = w, w + 8, ... for all 8 heads
+// with 8 independent 512 B loads in flight per piece, and the 8 warps are folded through shared
+// memory. Items finished by a single warp were already written by it; rows of empty sequences are
+// zeroed here.
 // ------------------------------------------------------------------------------------------------
-constexpr int kSkReduceRows = 4;
+constexpr int kSkReduceWarps = 8;
 
-__global__ void __launch_bounds__(kSkReduceRows * 32)
+__global__ void __launch_bounds__(kSkReduceWarps * 32)
 streamk_reduce_kernel(__nv_bfloat16* __restrict__ out, int64_t out_stride_tok, float* __restrict__ lse, int batch,
-                      int num_q_heads, int group, int subgroups, int num_kv_heads, int nw,
+                      int num_q_heads, int group, int subgroups, int num_kv_heads, int nw, int dyn_shift,
                       const float* __restrict__ part_o, const float* __restrict__ part_lse,
                       const int32_t* __restrict__ plan_cum, int pdl) {
-  if (pdl) griddep_wait();
-  const int lane = threadIdx.x & 31;
-  const int64_t row = static_cast<int64_t>(blockIdx.x) * kSkReduceRows + (threadIdx.x >> 5);
-  if (row >= static_cast<int64_t>(batch) * num_q_heads) return;
-  const int b = static_cast<int>(row / num_q_heads);
-  const int h = static_cast<int>(row % num_q_heads);
-  __nv_bfloat16* dst = out + static_cast<int64_t>(b) * out_stride_tok + static_cast<int64_t>(h) * kHeadDim + lane * 4;
+  __shared__ float s_acc[kSkReduceWarps][kHeadsPerItem][kHeadDim];
+  __shared__ float s_max[kSkReduceWarps][kHeadsPerItem];
+  __shared__ float s_den[kSkReduceWarps][kHeadsPerItem];
+  if (pdl) {
+    griddep_wait();
+    griddep_launch_dependents();
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int hs_count = num_kv_heads * subgroups;
+  const int b = blockIdx.x / hs_count, hs = blockIdx.x % hs_count;
+  const int kvh = hs / subgroups, sub = hs % subgroups;
+  const int heads_here = min(kHeadsPerItem, group - sub * kHeadsPerItem);
+  const int h_first = kvh * group + sub * kHeadsPerItem;  // first query head of the item
   const int c0 = plan_cum[b], n = plan_cum[b + 1] - c0;
-  if (n == 0) {  // empty sequence: zero row, LSE = -inf
-    *reinterpret_cast<uint2*>(dst) = make_uint2(0u, 0u);
-    if (lse != nullptr && lane == 0) lse[row] = -CUDART_INF_F;
+  if (n == 0) {  // empty sequence: zero rows, LSE = -inf
+    if (warp < heads_here) {
+      const int h = h_first + warp;
+      *reinterpret_cast<uint2*>(out + static_cast<int64_t>(b) * out_stride_tok + static_cast<int64_t>(h) * kHeadDim +
+                                lane * 4) = make_uint2(0u, 0u);
+      if (lse != nullptr && lane == 0) lse[static_cast<int64_t>(b) * num_q_heads + h] = -CUDART_INF_F;
+    }
     return;
   }
-  const int hs_count = num_kv_heads * subgroups;
-  const int64_t total = static_cast<int64_t>(plan_cum[batch]) * hs_count;
-  const int64_t tpw = max(static_cast<int64_t>(1), (total + nw - 1) / nw);
-  const int hig = h % group;
-  const int hs = (h / group) * subgroups + hig / kHeadsPerItem;
-  const int head = hig % kHeadsPerItem;
-  const int64_t t0 = static_cast<int64_t>(c0) * hs_count + static_cast<int64_t>(hs) * n;
-  const int w0 = static_cast<int>(t0 / tpw), w1 = static_cast<int>((t0 + n - 1) / tpw);
-  if (w0 == w1) return;  // finished by one warp
+  const SkSchedule sc = sk_schedule(static_cast<int64_t>(plan_cum[batch]) * hs_count, nw, dyn_shift);
+  // the item's tiles [t0, t1) in stream order and the chunks that overlap them
+  const int64_t t0 = static_cast<int64_t>(c0) * hs_count + static_cast<int64_t>(hs) * n, t1 = t0 + n;
+  int w0 = 0, ns = 0;  // static chunks w0 .. w0 + ns - 1
+  if (t0 < sc.S) {
+    w0 = static_cast<int>(t0 / sc.ts);
+    ns = static_cast<int>(((t1 < sc.S ? t1 : sc.S) - 1) / sc.ts) - w0 + 1;
+  }
+  int j0 = 0, nj = 0;  // dynamic chunks j0 .. j0 + nj - 1
+  if (t1 > sc.S) {
+    j0 = static_cast<int>(((t0 > sc.S ? t0 : sc.S) - sc.S) / sc.cd);
+    nj = static_cast<int>((t1 - 1 - sc.S) / sc.cd) - j0 + 1;
+  }
+  const int pieces = ns + nj;
+  if (pieces == 1) return;  // finished by one warp
 
-  auto piece_row = [&](int w) -> int64_t {
-    const int slot = 2 * w + ((t0 < static_cast<int64_t>(w) * tpw) ? 0 : 1);
-    return static_cast<int64_t>(slot) * kHeadsPerItem + head;
+  auto piece_slot = [&](int k) -> int64_t {  // k-th overlapping chunk -> its partial slot
+    int cid;
+    int64_t cstart;
+    if (k < ns) {
+      cid = w0 + k;
+      cstart = static_cast<int64_t>(cid) * sc.ts;
+    } else {
+      const int j = j0 + (k - ns);
+      cid = nw + j;
+      cstart = sc.S + static_cast<int64_t>(j) * sc.cd;
+    }
+    return static_cast<int64_t>(2 * cid + (t0 < cstart ? 0 : 1));
   };
-  float mx = -CUDART_INF_F;
-  for (int w = w0 + lane; w <= w1; w += 32) mx = fmaxf(mx, part_lse[piece_row(w)]);
+
+  // ---- pass 1: per-head maximum LSE over the pieces (thread = (piece mod 32, head))
+  {
+    const int hh = threadIdx.x & 7;
+    float mx = -CUDART_INF_F;
+    for (int k = threadIdx.x >> 3; k < pieces; k += kSkReduceWarps * 4)
+      mx = fmaxf(mx, part_lse[piece_slot(k) * kHeadsPerItem + hh]);
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+    if (lane < 8) s_max[warp][lane] = mx;
+  }
+  __syncthreads();
+  float mx[kHeadsPerItem];
 #pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  float denom = 0.f;
-  if (mx != -CUDART_INF_F) {
-    for (int w = w0; w <= w1; ++w) {
-      const int64_t r = piece_row(w);
-      const float ls = part_lse[r];
-      const float wgt = (ls == -CUDART_INF_F) ? 0.f : fast_exp2((ls - mx) * kLog2e);
-      const float4 o = *reinterpret_cast<const float4*>(part_o + r * kHeadDim + lane * 4);
-      acc.x = fmaf(o.x, wgt, acc.x);
-      acc.y = fmaf(o.y, wgt, acc.y);
-      acc.z = fmaf(o.z, wgt, acc.z);
-      acc.w = fmaf(o.w, wgt, acc.w);
-      denom += wgt;
+  for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+    float m = s_max[0][hh];
+#pragma unroll
+    for (int w = 1; w < kSkReduceWarps; ++w) m = fmaxf(m, s_max[w][hh]);
+    mx[hh] = m;
+  }
+  // ---- pass 2: warp w accumulates the pieces k = w, w + 8, ... for all heads
+  float4 acc[kHeadsPerItem];
+  float den[kHeadsPerItem];
+#pragma unroll
+  for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+    acc[hh] = make_float4(0.f, 0.f, 0.f, 0.f);
+    den[hh] = 0.f;
+  }
+  for (int k = warp; k < pieces; k += kSkReduceWarps) {
+    const int64_t r0 = piece_slot(k) * kHeadsPerItem;
+    const float ls = lane < kHeadsPerItem ? part_lse[r0 + lane] : 0.f;
+    float4 o[kHeadsPerItem];
+#pragma unroll
+    for (int hh = 0; hh < kHeadsPerItem; ++hh)
+      o[hh] = *reinterpret_cast<const float4*>(part_o + (r0 + hh) * kHeadDim + lane * 4);
+#pragma unroll
+    for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+      const float l = __shfl_sync(0xffffffffu, ls, hh);
+      const float wgt = (l == -CUDART_INF_F) ? 0.f : fast_exp2((l - mx[hh]) * kLog2e);
+      acc[hh].x = fmaf(o[hh].x, wgt, acc[hh].x);
+      acc[hh].y = fmaf(o[hh].y, wgt, acc[hh].y);
+      acc[hh].z = fmaf(o[hh].z, wgt, acc[hh].z);
+      acc[hh].w = fmaf(o[hh].w, wgt, acc[hh].w);
+      den[hh] += wgt;
     }
   }
-  const float inv = denom > 0.f ? 1.f / denom : 0.f;
-  uint2 pk;
-  pk.x = pack_bf16x2(acc.x * inv, acc.y * inv);
-  pk.y = pack_bf16x2(acc.z * inv, acc.w * inv);
-  *reinterpret_cast<uint2*>(dst) = pk;
-  if (lse != nullptr && lane == 0) lse[row] = denom > 0.f ? mx + logf(denom) : -CUDART_INF_F;
+#pragma unroll
+  for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+    *reinterpret_cast<float4*>(&s_acc[warp][hh][lane * 4]) = acc[hh];
+    if (lane == 0) s_den[warp][hh] = den[hh];
+  }
+  __syncthreads();
+  // ---- fold the 8 warps: warp = head, lane = 4 output columns
+  if (warp < heads_here) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    float dsum = 0.f;
+#pragma unroll
+    for (int w = 0; w < kSkReduceWarps; ++w) {
+      const float4 v = *reinterpret_cast<const float4*>(&s_acc[w][warp][lane * 4]);
+      a.x += v.x;
+      a.y += v.y;
+      a.z += v.z;
+      a.w += v.w;
+      dsum += s_den[w][warp];
+    }
+    float mfin = s_max[0][warp];
+#pragma unroll
+    for (int w = 1; w < kSkReduceWarps; ++w) mfin = fmaxf(mfin, s_max[w][warp]);
+    const float inv = dsum > 0.f ? 1.f / dsum : 0.f;
+    const int h = h_first + warp;
+    uint2 pk;
+    pk.x = pack_bf16x2(a.x * inv, a.y * inv);
+    pk.y = pack_bf16x2(a.z * inv, a.w * inv);
+    *reinterpret_cast<uint2*>(out + static_cast<int64_t>(b) * out_stride_tok + static_cast<int64_t>(h) * kHeadDim +
+                              lane * 4) = pk;
+    if (lse != nullptr && lane == 0)
+      lse[static_cast<int64_t>(b) * num_q_heads + h] = dsum > 0.f ? mfin + logf(dsum) : -CUDART_INF_F;
+  }
 }
 
 constexpr int kSkDepthFp8 = 2 * kSkDepth;  // fp8 stages are half the bytes: twice the ring depth
@@ -338,7 +506,7 @@ size_t decode_streamk_smem_bytes(bool fp8) {
 
 template <typename K>
 static cudaError_t sk_launch(K kern, int* configured_dev, size_t smem, const CUtensorMap& tm_k, const CUtensorMap& tm_v,
-                             const DecodeParams& p, int grid, cudaStream_t stream) {
+                             const DecodeParams& p, int grid, bool pdl, cudaStream_t stream) {
   int dev = 0;
   if (cudaError_t e = cudaGetDevice(&dev)) return e;
   if (dev != *configured_dev) {
@@ -347,25 +515,33 @@ static cudaError_t sk_launch(K kern, int* configured_dev, size_t smem, const CUt
       return e;
     *configured_dev = dev;
   }
-  kern<<<grid, kSkWarps * 32, smem, stream>>>(tm_k, tm_v, p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(kSkWarps * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, tm_k, tm_v, p);
 }
 
 cudaError_t launch_decode_streamk(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, bool fp8,
-                                  int grid, cudaStream_t stream) {
+                                  int grid, bool pdl, cudaStream_t stream) {
   static thread_local int dev_bf16 = -1, dev_fp8 = -1;
   if (fp8)
     return sk_launch(paged_decode_streamk_kernel<kSkWarps, kSkDepthFp8, true>, &dev_fp8,
-                     decode_streamk_smem_bytes(true), tm_k, tm_v, p, grid, stream);
+                     decode_streamk_smem_bytes(true), tm_k, tm_v, p, grid, pdl, stream);
   return sk_launch(paged_decode_streamk_kernel<kSkWarps, kSkDepth, false>, &dev_bf16,
-                   decode_streamk_smem_bytes(false), tm_k, tm_v, p, grid, stream);
+                   decode_streamk_smem_bytes(false), tm_k, tm_v, p, grid, pdl, stream);
 }
 
 cudaError_t launch_streamk_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream) {
-  const int64_t rows = static_cast<int64_t>(p.batch) * p.num_q_heads;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(static_cast<unsigned>((rows + kSkReduceRows - 1) / kSkReduceRows));
-  cfg.blockDim = dim3(kSkReduceRows * 32);
+  cfg.gridDim = dim3(static_cast<unsigned>(p.batch * p.num_kv_heads * p.subgroups));
+  cfg.blockDim = dim3(kSkReduceWarps * 32);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -376,8 +552,9 @@ cudaError_t launch_streamk_reduce(const DecodeParams& p, int grid_decode, bool p
   const int pdl_i = pdl ? 1 : 0;
   const int nw = grid_decode * kSkWarps;
   return cudaLaunchKernelEx(&cfg, streamk_reduce_kernel, p.out, p.out_stride_tok, p.lse, p.batch, p.num_q_heads,
-                            p.group, p.subgroups, p.num_kv_heads, nw, static_cast<const float*>(p.part_o),
-                            static_cast<const float*>(p.part_lse), static_cast<const int32_t*>(p.plan_cum), pdl_i);
+                            p.group, p.subgroups, p.num_kv_heads, nw, p.sk_dyn_shift,
+                            static_cast<const float*>(p.part_o), static_cast<const float*>(p.part_lse),
+                            static_cast<const int32_t*>(p.plan_cum), pdl_i);
 }
 
 }  // namespace b200

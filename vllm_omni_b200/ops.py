@@ -122,17 +122,26 @@ def decode_workspace_bytes(max_batch: int, num_q_heads: int, head_size: int, max
 
 
 class DecodeWorkspace:
-    """Caller-owned split-K scratch (partial outputs + LSE), grown on demand outside graphs."""
+    """Caller-owned split-K scratch (control words, partial outputs + LSE), grown on demand outside
+    graphs. The control words (first 256 bytes) are zeroed once per allocation through
+    `b200attn_workspace_init`; the library keeps them zero between launches."""
 
     def __init__(self, device: torch.device | str = "cuda", nbytes: int = 0):
         self.device = torch.device(device)
-        self.buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
+        self._alloc(max(nbytes, 256))
+
+    def _alloc(self, nbytes: int) -> None:
+        self.buf = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        if self.buf.is_cuda:
+            with torch.cuda.device(self.device):
+                check("b200attn_workspace_init", _lib.load().b200attn_workspace_init(
+                    self.buf.data_ptr(), self.buf.numel(), torch.cuda.current_stream(self.device).cuda_stream))
 
     def ensure(self, nbytes: int) -> None:
         if self.buf.numel() < nbytes:
             if torch.cuda.is_current_stream_capturing():
                 raise RuntimeError("decode workspace too small and cannot grow during graph capture")
-            self.buf = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            self._alloc(nbytes)
 
     @property
     def ptr(self) -> int:
