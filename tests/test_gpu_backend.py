@@ -93,3 +93,51 @@ def test_builder_builds_without_sync_and_sizes_workspace(lib, be):
     assert md.decode_num_splits == 0 and md.workspace is b.workspace
     md2 = b.build_for_cudagraph_capture(cam)
     assert md2.num_decodes == 3
+
+
+@pytest.mark.parametrize("fp8", [False, True])
+def test_mixed_batch_decodes_then_prefills_through_builder_and_impl(lib, be, fp8):
+    """A step with 2 decode requests followed by 2 prefill/extend requests (vLLM orders decodes first,
+    reorder_batch_threshold = 1): metadata from the builder, cache update for all new tokens, one
+    forward() call that routes rows to the decode and the prefill kernels."""
+    from vllm.v1.attention.backend import CommonAttentionMetadata
+    from oracle import oracle
+    hq, hkv, d = 16, 2, 128
+    seq_lens = [200, 33, 150, 64]      # context INCLUDING this step's new tokens
+    q_lens = [1, 1, 70, 64]            # decode, decode, extend (80 cached + 70 new), pure prefill
+    c = make_case(seq_lens, hq=hq, hkv=hkv, seed=23, fp8=fp8)
+    mc = types.SimpleNamespace(get_num_attention_heads=lambda pc: hq, get_num_kv_heads=lambda pc: hkv,
+                               get_head_size=lambda: d, max_model_len=1024)
+    cfg = types.SimpleNamespace(model_config=mc, parallel_config=None,
+                                scheduler_config=types.SimpleNamespace(max_num_seqs=8))
+    b = be.B200AttentionMetadataBuilder(types.SimpleNamespace(block_size=16), ["l0"], cfg, torch.device("cuda"))
+    T = sum(q_lens)
+    qsl_cpu = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32)
+    # new tokens = the last q_len positions of every sequence
+    l64 = c.seq_lens.long()
+    starts = torch.cumsum(l64, 0) - l64
+    new_idx = torch.cat([torch.arange(int(starts[i] + l64[i] - q_lens[i]), int(starts[i] + l64[i])) for i in range(4)])
+    old = torch.ones(int(l64.sum()), dtype=torch.bool)
+    old[new_idx] = False
+    impl = be.B200AttentionImpl(hq, d, c.scale, hkv, None, None, c.kv_cache_dtype)
+    layer = _layer(c.k_scale, c.v_scale)
+    kv = layout.alloc_kv_cache(c.num_blocks, 16, hkv, d, c.kv_cache_dtype, "cuda")
+    impl.do_kv_cache_update(layer, c.hist_k[old].cuda(), c.hist_v[old].cuda(), kv, c.slots[old].cuda())
+    cam = CommonAttentionMetadata(
+        query_start_loc=qsl_cpu.cuda(), query_start_loc_cpu=qsl_cpu, seq_lens=c.seq_lens.cuda(), num_reqs=4,
+        num_actual_tokens=T, max_query_len=max(q_lens), max_seq_len=max(seq_lens),
+        block_table_tensor=c.block_table.cuda(), slot_mapping=c.slots[new_idx].cuda())
+    md = b.build(0, cam)
+    assert (md.num_decodes, md.num_prefills, md.num_decode_tokens, md.num_prefill_tokens) == (2, 2, 2, T - 2)
+    assert md.prefill_max_query_len == 70
+    key, value = c.hist_k[new_idx].cuda(), c.hist_v[new_idx].cuda()
+    impl.do_kv_cache_update(layer, key, value, kv, md.slot_mapping)
+    g = torch.Generator().manual_seed(5)
+    query = torch.randn(T, hq, d, generator=g).to(torch.bfloat16)
+    output = torch.full((T, hq * d), 9.0, dtype=torch.bfloat16, device="cuda")
+    impl.forward(layer, query.cuda(), key, value, kv, md, output)
+    torch.cuda.synchronize()
+    ref = oracle.ref_paged_prefill(query, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl_cpu, c.scale,
+                                   fp8, c.k_scale, c.v_scale)
+    got = output.view(T, hq, d)
+    assert excess_rel_err(got, ref) <= 2e-3 and kernel_rel_l2(got, ref) <= 2e-3

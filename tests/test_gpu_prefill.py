@@ -1,0 +1,127 @@
+"""GPU parity: causal varlen attention over the paged cache (prefill / extend / mixed batches,
+SURVEY §8f row 1) through b200attn_paged_prefill vs the fp32 oracle (`ref_paged_prefill`, the
+causal restatement of vllm/v1/attention/backends/flash_attn.py:758-819). Same 2e-3 bound as decode;
+fp8 caches are compared against the oracle fed the same quantised cache."""
+import pytest
+import torch
+
+from oracle import oracle
+from tests.helpers import cache_to_dev, excess_rel_err, kernel_rel_l2, make_case, to_dev
+from vllm_omni_b200 import ops
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-3
+
+
+def run_prefill(c, q_lens, hq, seed=0, q_std=1.0):
+    g = torch.Generator().manual_seed(seed)
+    T = sum(q_lens)
+    q = (torch.randn(T, hq, 128, generator=g) * q_std).to(torch.bfloat16)
+    qsl = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32)
+    cache = cache_to_dev(c.kv_cache)
+    out = torch.full((T, hq, 128), 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.paged_prefill(q.cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl.cuda(),
+                      max(q_lens), c.scale, out=out, kv_cache_dtype=c.kv_cache_dtype, k_scale=to_dev(c.k_scale),
+                      v_scale=to_dev(c.v_scale))
+    torch.cuda.synchronize()
+    ref = oracle.ref_paged_prefill(q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, c.scale,
+                                   c.fp8, c.k_scale, c.v_scale)
+    return out, ref
+
+
+def check(out, ref):
+    assert torch.isfinite(out.float()).all(), "non-finite output"
+    e, l2 = excess_rel_err(out, ref), kernel_rel_l2(out, ref)
+    assert e <= TOL, f"excess rel err {e:.3e}"
+    assert l2 <= TOL, f"kernel rel L2 {l2:.3e}"
+
+
+CASES = [
+    # (seq_lens, q_lens): pure prefill, extend with context, single-token rows, ragged tails
+    ([16], [16]),
+    ([17], [17]),
+    ([1], [1]),
+    ([33, 64], [5, 1]),
+    ([100, 257, 31], [100, 1, 31]),
+    ([300, 129, 48], [44, 129, 17]),
+    ([1000], [1000]),
+    ([2049, 700], [513, 699]),
+]
+
+
+@pytest.mark.parametrize("fp8", [False, True])
+@pytest.mark.parametrize("seq_lens,q_lens", CASES)
+def test_prefill_vs_oracle(lib, seq_lens, q_lens, fp8):
+    c = make_case(seq_lens, hq=8, hkv=1, seed=sum(seq_lens), fp8=fp8, garbage_fill=True)
+    out, ref = run_prefill(c, q_lens, 8, seed=len(q_lens))
+    check(out, ref)
+
+
+@pytest.mark.parametrize("fp8", [False, True])
+@pytest.mark.parametrize("hq,hkv", [(32, 4), (28, 4), (16, 2), (4, 1), (4, 4), (16, 1), (24, 2)])
+def test_prefill_gqa_group_shapes(lib, hq, hkv, fp8):
+    c = make_case([130, 77, 256], hq=hq, hkv=hkv, seed=hq, fp8=fp8)
+    out, ref = run_prefill(c, [130, 20, 1], hq, seed=hkv)
+    check(out, ref)
+
+
+@pytest.mark.parametrize("bs", [32, 64])
+def test_prefill_larger_block_sizes(lib, bs):
+    c = make_case([200, 65], hq=8, hkv=2, bs=bs, seed=bs)
+    out, ref = run_prefill(c, [200, 3], 8)
+    check(out, ref)
+
+
+def test_prefill_last_row_equals_decode_kernel(lib):
+    """The last query row of every sequence sees the whole context: it must agree with the decode
+    kernel on the same cache (two different kernels, same math)."""
+    c = make_case([333, 64, 1025], hq=16, hkv=2, seed=9)
+    q_lens = [40, 64, 1]
+    out, _ = run_prefill(c, q_lens, 16, seed=3)
+    g = torch.Generator().manual_seed(3)
+    q = torch.randn(sum(q_lens), 16, 128, generator=g).to(torch.bfloat16)
+    last = torch.tensor(q_lens).cumsum(0) - 1
+    cache = cache_to_dev(c.kv_cache)
+    dec = ops.paged_decode(q[last].cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(),
+                           c.max_seq_len, c.scale)
+    torch.cuda.synchronize()
+    assert (out[last.cuda()].float() - dec.float()).abs().max().item() <= 2e-2 * dec.float().abs().max().item()
+
+
+def test_prefill_padded_token_count_and_strided_q(lib):
+    """q may be a slice of a wider fused-qkv tensor and carry padding rows past query_start_loc[-1]."""
+    c = make_case([90, 40], hq=8, hkv=2, seed=5)
+    g = torch.Generator().manual_seed(0)
+    T, pad = 50, 14
+    fused = torch.randn(T + pad, 8 * 128 + 2 * 2 * 128, generator=g).to(torch.bfloat16).cuda()
+    q = fused[:, : 8 * 128].view(T + pad, 8, 128)
+    qsl = torch.tensor([0, 30, 50], dtype=torch.int32)
+    cache = cache_to_dev(c.kv_cache)
+    out = torch.full((T + pad, 8, 128), 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.paged_prefill(q, cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl.cuda(), 30, c.scale, out=out)
+    torch.cuda.synchronize()
+    ref = oracle.ref_paged_prefill(q[:T].cpu(), c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, c.scale)
+    check(out[:T], ref)
+    assert (out[T:].float() == 7.0).all(), "rows past query_start_loc[-1] must not be written"
+
+
+def test_prefill_long_chunk_properties(lib):
+    """An 8k-token chunk against an 8k context (cfg5-style prefix, one kv head group): sampled rows vs
+    the oracle, and chunked == unchunked (two 4k chunks with the second extending the first)."""
+    S = 8192
+    c = make_case([S], hq=8, hkv=1, seed=11)
+    out, _ = run_prefill(c, [S], 8, seed=1)
+    g = torch.Generator().manual_seed(1)
+    q = torch.randn(S, 8, 128, generator=g).to(torch.bfloat16)
+    rows = [0, 15, 16, 4095, 4096, 8191]
+    for r in rows:
+        ref, _ = oracle.ref_paged_decode(q[r:r + 1], c.kv_cache[0], c.kv_cache[1], c.block_table,
+                                         torch.tensor([r + 1], dtype=torch.int32), c.scale)
+        assert excess_rel_err(out[r:r + 1], ref) <= TOL
+    # second half as an extend chunk over the same cache
+    cache = cache_to_dev(c.kv_cache)
+    qsl = torch.tensor([0, S // 2], dtype=torch.int32).cuda()
+    out2 = ops.paged_prefill(q[S // 2:].cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl,
+                             S // 2, c.scale)
+    torch.cuda.synchronize()
+    assert torch.equal(out2, out[S // 2:])

@@ -639,11 +639,70 @@ void b200attn_debug_sk_schedule(int64_t total_tiles, int32_t num_warps, int32_t 
 
 void b200attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<unsigned long long*>(device_buffer); }
 
-int b200attn_paged_prefill(const void*, int64_t, const void*, const void*, int64_t, int64_t, int64_t,
-                           int64_t, void*, int64_t, const int32_t*, int64_t, const int32_t*,
-                           const int32_t*, int32_t, int32_t, int32_t, int32_t, int32_t, int32_t,
-                           int32_t, float, int32_t, const float*, const float*, int32_t, void*) {
-  return fail(B200ATTN_EUNSUPPORTED, "paged prefill is not built yet");
+int b200attn_paged_prefill(const void* q, int64_t q_stride_tok, const void* k_cache, const void* v_cache,
+                           int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+                           int64_t num_blocks, void* out, int64_t out_stride_tok, const int32_t* block_table,
+                           int64_t block_table_stride, const int32_t* seq_lens, const int32_t* query_start_loc,
+                           int32_t batch, int32_t num_tokens, int32_t max_query_len, int32_t num_q_heads,
+                           int32_t num_kv_heads, int32_t head_size, int32_t block_size, float softmax_scale,
+                           int32_t kv_dtype, const float* k_scale, const float* v_scale, int32_t scale_numel,
+                           void* stream) {
+  (void)max_query_len;
+  if (batch < 0 || num_tokens < 0) return fail(B200ATTN_EINVAL, "batch/num_tokens < 0");
+  if (batch == 0 || num_tokens == 0) return 0;
+  if (q == nullptr || out == nullptr || block_table == nullptr || seq_lens == nullptr || query_start_loc == nullptr)
+    return fail(B200ATTN_EINVAL, "null q/out/block_table/seq_lens/query_start_loc");
+  if (num_q_heads <= 0 || num_kv_heads <= 0 || (num_q_heads % num_kv_heads) != 0)
+    return fail(B200ATTN_EINVAL, "num_q_heads %d not a multiple of num_kv_heads %d", num_q_heads, num_kv_heads);
+  if (int rc = check_cache_args(k_cache, v_cache, cache_stride_block, cache_stride_slot, cache_stride_head,
+                                num_blocks, num_kv_heads, head_size, block_size, kv_dtype))
+    return rc;
+  if ((q_stride_tok % 2) || (reinterpret_cast<uintptr_t>(q) % 4))
+    return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
+  if ((out_stride_tok % 4) || (reinterpret_cast<uintptr_t>(out) % 8))
+    return fail(B200ATTN_EINVAL, "out rows must be 8-byte aligned");
+  const int tpp = block_size / kTileTokens;
+  int shift = -1;
+  for (int sh = 0; sh < 16; ++sh)
+    if ((1 << sh) == tpp) shift = sh;
+  if (shift < 0) return fail(B200ATTN_EUNSUPPORTED, "prefill needs block_size = 16 * 2^k (got %d)", block_size);
+  const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
+  if (fp8) {
+    if (k_scale == nullptr || v_scale == nullptr) return fail(B200ATTN_EINVAL, "fp8 cache needs scales");
+    if (scale_numel != 1 && scale_numel != num_kv_heads)
+      return fail(B200ATTN_EINVAL, "scale_numel %d must be 1 or num_kv_heads", scale_numel);
+  }
+  PrefillParams p{};
+  p.q = static_cast<const __nv_bfloat16*>(q);
+  p.q_stride_tok = q_stride_tok;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.out_stride_tok = out_stride_tok;
+  p.block_table = block_table;
+  p.bt_stride = block_table_stride;
+  p.seq_lens = seq_lens;
+  p.query_start_loc = query_start_loc;
+  p.batch = batch;
+  p.num_tokens = num_tokens;
+  p.num_q_heads = num_q_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.group = num_q_heads / num_kv_heads;
+  p.subgroups = (p.group + kHeadsPerItem - 1) / kHeadsPerItem;
+  p.tpp_shift = shift;
+  p.tpp_mask = tpp - 1;
+  p.scale_log2 = softmax_scale * kLog2e;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.scale_stride = scale_numel > 1 ? 1 : 0;
+  const CUtensorMap *mk = nullptr, *mv = nullptr;
+  if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks, num_kv_heads,
+                           block_size, fp8, &mk))
+    return rc;
+  const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
+  if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks, num_kv_heads,
+                           block_size, fp8, &mv))
+    return rc;
+  cudaError_t e = launch_paged_prefill(tm_k, *mv, p, fp8, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "paged_prefill launch");
 }
 
 int b200attn_gather_kv(const void* cache, int64_t cache_stride_block, int64_t cache_stride_slot,

@@ -31,6 +31,27 @@ cudaError_t launch_lse_reduce(__nv_bfloat16* out, int64_t out_stride_tok, float*
                               int tiles_per_split, const float* part_o, const float* part_lse,
                               bool pdl, cudaStream_t stream);
 
+struct PrefillParams {
+  const __nv_bfloat16* q;
+  int64_t q_stride_tok;
+  __nv_bfloat16* out;
+  int64_t out_stride_tok;
+  const int32_t* block_table;
+  int64_t bt_stride;
+  const int32_t* seq_lens;
+  const int32_t* query_start_loc;
+  int32_t batch, num_tokens, num_q_heads, num_kv_heads;
+  int32_t group, subgroups;
+  int32_t tpp_shift, tpp_mask;  // 16-token tiles per page = 2^tpp_shift
+  float scale_log2;
+  const float* k_scale;
+  const float* v_scale;
+  int32_t scale_stride;
+};
+cudaError_t launch_paged_prefill(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const PrefillParams& p, bool fp8,
+                                 cudaStream_t stream);
+size_t prefill_smem_bytes(bool fp8);
+
 struct CacheWriteParams {
   const __nv_bfloat16* key;
   const __nv_bfloat16* value;
