@@ -347,10 +347,14 @@ def run_b200(args, wl):
     kern_avg_ms = sum(kern_ms) / len(kern_ms)
     peak, peak_src = peaks()
     achieved = kv_bytes / (kern_avg_ms * 1e-3) / 1e9
+    traffic = None  # DRAM read+write bytes per launch from the committed ncu --set full capture (N=1 shapes)
+    tj = ROOT / "profiles" / "traffic.json"
+    if world == 1 and not args.ragged and tj.exists():
+        traffic = json.loads(tj.read_text()).get(wl.name, {}).get("dram_bytes_per_launch")
     roofline = {
         "bound": "hbm", "kernel": {1: "paged_decode_tma_kernel", 2: "paged_decode_cpasync_kernel",
                                    3: "paged_decode_stream_kernel", 4: "paged_decode_streamk_kernel"}[variant],
-        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "peak_source": peak_src, "algorithmic_bytes_per_launch": kv_bytes,
         "kernel_avg_us": kern_avg_ms * 1e3, "kernel_median_us": statistics.median(kern_ms) * 1e3,
         "kernel_share_of_step": kern_avg_ms * L / ms_per_step, "frac_of_8TBps": achieved / 8000.0,
