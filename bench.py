@@ -49,6 +49,12 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--contiguous-blocks", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
+    ap.add_argument("--replica-mode", default="split", choices=["split", "replicate"],
+                    help="when tp > KV heads: 'replicate' = every rank of a replica group streams the whole KV "
+                         "head for its own query heads (the reference rule); 'split' = the group splits the "
+                         "batch and exchanges q/out (tp.ReplicaSplit: same results, 1/R of the KV bytes per rank)")
+    ap.add_argument("--total-kv-heads", type=int, default=0, help="override the workload's KV-head count "
+                    "(e.g. 1 with --gpus 2 exercises KV-head replication on two GPUs)")
     return ap.parse_args()
 
 
@@ -226,7 +232,11 @@ def workload_config(wl, args, world, global_batch):
                      f"{wl.total_q_heads}q/{wl.total_kv_heads}kv heads d={wl.head_size}, L={args.layers or wl.num_layers}, "
                      f"{'ragged' if args.ragged else 'uniform'} seq_lens, "
                      f"{'contiguous' if args.contiguous_blocks else 'random-permutation'} block table"),
-        "global_batch": global_batch, "seq_len": wl.ctx, "parallelism": f"tp{world} (KV-head sharding)",
+        "global_batch": global_batch, "seq_len": wl.ctx, "parallelism": (f"tp{world} (KV-head sharding" + (
+            "" if world <= wl.total_kv_heads else
+            f"; {world // wl.total_kv_heads} ranks per KV head, " + (
+                "batch split inside the replica group, q/out exchanged by all-to-all"
+                if args.replica_mode == "split" else "KV head replicated (reference rule)")) + ")"),
         "l2": "inputs larger than L2: every layer streams its own KV cache (no reuse between launches)",
     }
 
@@ -246,11 +256,26 @@ def run_b200(args, wl):
     B, hq, hkv, d = global_batch, sh.num_q_heads, sh.num_kv_heads, wl.head_size
     caches = [ops.split_kv_cache(c) for c in inp.kv_caches]
     out = torch.empty(B, hq, d, dtype=torch.bfloat16, device="cuda")
+    # KV-head replication (tp > KV heads): split the batch inside the replica group unless told otherwise
+    rs = None
+    dq, dout, dbt, dsl, dhq = inp.q, out, inp.block_table, inp.seq_lens, hq   # what the decode kernel sees
+    kv_bytes = inp.kv_bytes_per_layer
+    if sh.kv_replicas > 1 and args.replica_mode == "split":
+        import torch.distributed as dist
+        from vllm_omni_b200 import tp as tpmod
+        groups = [dist.new_group(r) for r in tpmod.ReplicaSplit.groups(world, sh.kv_replicas)]
+        rs = tpmod.ReplicaSplit(sh, groups[rank // sh.kv_replicas])
+        per, b0, b1 = rs.plan(B)
+        dhq = rs.group_q_heads
+        q_grp = torch.zeros(per, dhq, d, dtype=torch.bfloat16, device="cuda")
+        out_grp = torch.zeros(per, dhq, d, dtype=torch.bfloat16, device="cuda")
+        dq, dout, dbt, dsl = q_grp[:b1 - b0], out_grp[:b1 - b0], inp.block_table[b0:b1], inp.seq_lens[b0:b1]
+        kv_bytes = int(inp.seq_lens[b0:b1].sum().item()) * 2 * hkv * d * (1 if wl.fp8 else 2)
     # schedule: stream-K (no split count) unless a split count or a fixed-split variant is asked for
     streamk = args.variant == ops.VARIANT_STREAMK or (args.variant == ops.VARIANT_AUTO and args.splits == 0)
     variant = ops.VARIANT_STREAMK if streamk else (args.variant or ops.VARIANT_STREAM)
     splits = 0 if streamk else (args.splits or ops.decode_num_splits(B, hq, hkv, inp.max_seq_len))
-    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, hq, d, max(splits, 1)))
+    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, dhq, d, max(splits, 1)))
     hidden = torch.zeros(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")  # o_proj output stand-in
     if world > 1:
         import torch.distributed as dist
@@ -259,14 +284,18 @@ def run_b200(args, wl):
         for kc, vc in caches:
             ops.reshape_and_cache(inp.new_k, inp.new_v, kc, vc, inp.slot_mapping, wl.kv_cache_dtype,
                                   inp.k_scale, inp.v_scale)
-            ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
-                             inp.softmax_scale, out=out, kv_cache_dtype=wl.kv_cache_dtype,
+            if rs is not None:
+                rs.gather_q(inp.q, out=q_grp)
+            ops.paged_decode(dq, kc, vc, dbt, dsl, inp.max_seq_len,
+                             inp.softmax_scale, out=dout, kv_cache_dtype=wl.kv_cache_dtype,
                              k_scale=inp.k_scale, v_scale=inp.v_scale, num_splits=splits,
                              variant=variant, workspace=ws)
+            if rs is not None:
+                rs.scatter_out(out_grp, B, out=out)
             if world > 1:
                 dist.all_reduce(hidden)  # the only collective next to the path: o_proj's row-parallel sum
 
-    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0))
+    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0))  # our kernels only (not NCCL / copies)
 
     def capture(fn):
         """CUDA-graph the launches of `fn` (how vLLM replays decode steps); None if capture fails."""
@@ -310,12 +339,10 @@ def run_b200(args, wl):
     # ---- roofline of the dominant kernel: CUDA events around a graph of ONLY its L launches
     # (one per layer cache, back to back), so the average excludes host launch gaps; the eager
     # fallback brackets every launch with its own event pair.
-    kv_bytes = inp.kv_bytes_per_layer
-
     def partial_only():
         for kc, vc in caches:
-            ops.paged_decode_partial(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
-                                     inp.softmax_scale, out, max(splits, 1), ws,
+            ops.paged_decode_partial(dq, kc, vc, dbt, dsl, inp.max_seq_len,
+                                     inp.softmax_scale, dout, max(splits, 1), ws,
                                      kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
                                      v_scale=inp.v_scale, variant=variant)
 
@@ -336,8 +363,8 @@ def run_b200(args, wl):
             for kc, vc in caches:
                 a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
-                ops.paged_decode_partial(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len,
-                                         inp.softmax_scale, out, max(splits, 1), ws,
+                ops.paged_decode_partial(dq, kc, vc, dbt, dsl, inp.max_seq_len,
+                                         inp.softmax_scale, dout, max(splits, 1), ws,
                                          kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
                                          v_scale=inp.v_scale, variant=variant)
                 b_.record()
@@ -365,7 +392,7 @@ def run_b200(args, wl):
     e2e = None
     if not args.no_e2e:
         try:
-            e2e = run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch)
+            e2e = run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs)
         except Exception as ex:  # report, never hide
             e2e = {"value": None, "unit": UNIT, "error": f"{type(ex).__name__}: {ex}"}
 
@@ -385,25 +412,40 @@ def run_b200(args, wl):
             "data": "synthetic", "config": workload_config(wl, args, world, global_batch),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
             "clocks": clk.result, "per_rank": {"q_heads": hq, "kv_heads": hkv, "kv_replicas": sh.kv_replicas,
+                                               "replica_mode": (args.replica_mode if sh.kv_replicas > 1 else None),
+                                               "decode_q_heads": dhq, "decode_batch": int(dq.shape[0]),
                                                "kv_bytes_per_layer": kv_bytes},
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        import torch.distributed as dist
-        dist.destroy_process_group()
+        # Leave without tearing NCCL down: destroying a communicator whose kernels are still referenced
+        # by live CUDA graphs can block forever (seen on the 2-GPU box: the line above was printed and
+        # the ranks never exited). Everything is synchronised and flushed, so exit hard on every rank.
+        barrier(world)
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
-def run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch):
+def run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs=None):
     from vllm_omni_b200 import backend as be
     from vllm_omni_b200.host_runner import HostStepRunner
     impl = be.B200AttentionImpl(hq, d, inp.softmax_scale, hkv, None, None, wl.kv_cache_dtype)
+    if rs is not None:
+        impl.enable_replica_split(rs)
     qsl = torch.arange(B + 1, dtype=torch.int32, device="cuda")
     md = be.B200AttentionMetadata(
         num_actual_tokens=B, max_query_len=1, query_start_loc=qsl, max_seq_len=inp.max_seq_len,
         seq_lens=inp.seq_lens, block_table=inp.block_table, slot_mapping=inp.slot_mapping, num_decodes=B,
         num_decode_tokens=B, num_prefills=0, num_prefill_tokens=0, prefill_query_start_loc=None,
         prefill_max_query_len=0, decode_num_splits=splits, workspace=ws)
-    runner = HostStepRunner(impl, md, inp.kv_caches, B, hq, hkv, d, inp.slot_mapping, inp.k_scale, inp.v_scale)
+    after_layer = None
+    if world > 1:
+        import torch.distributed as dist
+        hidden = torch.zeros(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")
+        after_layer = lambda: dist.all_reduce(hidden)  # noqa: E731 - the o_proj row-parallel sum stand-in
+    runner = HostStepRunner(impl, md, inp.kv_caches, B, hq, hkv, d, inp.slot_mapping, inp.k_scale, inp.v_scale,
+                            after_layer=after_layer)
     qkv_dev = torch.cat([inp.q.reshape(B, -1), inp.new_k.reshape(B, -1), inp.new_v.reshape(B, -1)], dim=1)
     host_qkv = [qkv_dev.cpu().pin_memory() for _ in range(L)]
     host_out = [torch.empty(B, hq * d, dtype=torch.bfloat16).pin_memory() for _ in range(L)]
@@ -426,6 +468,8 @@ def main():
     args = parse_args()
     from vllm_omni_b200 import workloads
     wl = workloads.WORKLOADS[args.workload]
+    if args.total_kv_heads:
+        wl = workloads.scaled(wl, total_kv_heads=args.total_kv_heads)
     if args.impl == "reference":
         run_reference(args, wl)
     else:

@@ -62,3 +62,55 @@ def test_kv_head_sharding_world_size_2(total_q, total_kv):
         assert p.exitcode == 0
     assert same, "gathered per-rank outputs differ from the single-rank run"
     assert err < 1e-3
+
+
+def _split_worker(rank: int, world: int, port: int, batch: int, q_out):
+    """tp = 2 over ONE KV head (replicated): batch split inside the replica group vs plain replication."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(1)
+        total_q, total_kv = 8, 1
+        lens = [33, 100, 7, 64, 1][:batch]
+        c = make_case(lens, hq=total_q, hkv=total_kv, seed=3)
+        sh = tp.shard_heads(total_q, total_kv, world, rank)
+        assert sh.kv_replicas == 2 and sh.num_kv_heads == 1
+        groups = [dist.new_group(r) for r in tp.ReplicaSplit.groups(world, sh.kv_replicas)]
+        rs = tp.ReplicaSplit(sh, groups[rank // sh.kv_replicas])
+        per, b0, b1 = rs.plan(batch)
+        qs = slice(sh.q_head_start, sh.q_head_start + sh.num_q_heads)
+        q_rank = c.q[:, qs].contiguous()
+        # reference rule: every rank reads the whole KV head for its own heads
+        rep, _ = oracle.ref_paged_decode(q_rank, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, c.scale)
+        # split: all heads of the group, local sequences only
+        q_grp = rs.gather_q(q_rank)
+        n = b1 - b0
+        assert q_grp.shape == (per, total_q, 128)
+        assert torch.equal(q_grp[:n], c.q[b0:b1])
+        out_local = torch.zeros(per, total_q, 128)
+        if n > 0:
+            o, _ = oracle.ref_paged_decode(q_grp[:n], c.kv_cache[0], c.kv_cache[1], c.block_table[b0:b1],
+                                           c.seq_lens[b0:b1], c.scale)
+            out_local[:n] = o
+        mine = rs.scatter_out(out_local, batch)
+        q_out.put((rank, bool(torch.equal(mine, rep)), tuple(mine.shape)))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("batch", [4, 5, 1])  # even split, padded split, fewer sequences than ranks
+def test_replica_group_batch_split_equals_replication(batch):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_split_worker, args=(r, 2, port, batch, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, same, shape in res:
+        assert same, f"rank {rank}: batch-split output differs from the replicated run"
+        assert shape == (batch, 4, 128)

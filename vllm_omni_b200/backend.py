@@ -202,6 +202,14 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         if unsupported:
             raise NotImplementedError(f"B200AttentionImpl does not support: {', '.join(unsupported)}")
         self._kv_code = ops.kv_dtype_code(kv_cache_dtype)
+        # optional: batch split inside a KV-head replica group (tp > total_kv_heads), see tp.ReplicaSplit
+        self.replica_split = None
+        self._split_ws: ops.DecodeWorkspace | None = None
+
+    def enable_replica_split(self, replica_split) -> None:
+        """Serve decode rows with the batch split over the ranks that replicate this KV head instead of
+        every rank streaming the whole head (tp.ReplicaSplit; identical results, 1/R of the KV bytes)."""
+        self.replica_split = replica_split
 
     # ------------------------------------------------------------------ cache write
     def do_kv_cache_update(self, layer, key: torch.Tensor, value: torch.Tensor,
@@ -230,7 +238,21 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         k_scale = getattr(layer, "_k_scale", None)
         v_scale = getattr(layer, "_v_scale", None)
         nd, ndt = md.num_decodes, md.num_decode_tokens
-        if nd > 0:
+        if nd > 0 and self.replica_split is not None:
+            rs = self.replica_split
+            per, b0, b1 = rs.plan(nd)
+            q_grp = rs.gather_q(q[:ndt])
+            out_grp = torch.zeros_like(q_grp) if b1 - b0 < per else torch.empty_like(q_grp)
+            if b1 > b0:
+                if self._split_ws is None:  # sized for the group's head count, batch-independent (stream-K)
+                    self._split_ws = ops.DecodeWorkspace(q.device, ops.decode_workspace_bytes(
+                        per, rs.group_q_heads, self.head_size, 1))
+                ops.paged_decode(q_grp[:b1 - b0], k_cache, v_cache, md.block_table[b0:b1], md.seq_lens[b0:b1],
+                                 md.max_seq_len, self.scale, out=out_grp[:b1 - b0], kv_cache_dtype=self._kv_code,
+                                 k_scale=k_scale, v_scale=v_scale, num_splits=md.decode_num_splits,
+                                 workspace=self._split_ws)
+            rs.scatter_out(out_grp, nd, out=out[:ndt])
+        elif nd > 0:
             ops.paged_decode(q[:ndt], k_cache, v_cache, md.block_table, md.seq_lens, md.max_seq_len,
                              self.scale, out=out[:ndt], kv_cache_dtype=self._kv_code,
                              k_scale=k_scale, v_scale=v_scale, num_splits=md.decode_num_splits,

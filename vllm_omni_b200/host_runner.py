@@ -17,9 +17,10 @@ import torch
 class HostStepRunner:
     def __init__(self, impl, metadata, kv_caches: list[torch.Tensor], batch: int, num_q_heads: int,
                  num_kv_heads: int, head_size: int, slot_mapping: torch.Tensor,
-                 k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None):
+                 k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None, after_layer=None):
         dev = kv_caches[0].device
         self.impl, self.md, self.kv_caches, self.slot_mapping = impl, metadata, kv_caches, slot_mapping
+        self.after_layer = after_layer  # e.g. the o_proj all-reduce of a tensor-parallel layer
         one = torch.ones(1, dtype=torch.float32, device=dev)
         self.layer = types.SimpleNamespace(_k_scale=one if k_scale is None else k_scale,
                                            _v_scale=one if v_scale is None else v_scale)
@@ -63,6 +64,8 @@ class HostStepRunner:
             k, v = k.view(B, hkv, d), v.view(B, hkv, d)
             self.impl.do_kv_cache_update(self.layer, k, v, self.kv_caches[l], self.slot_mapping)
             self.impl.forward(self.layer, q.view(B, hq, d), k, v, self.kv_caches[l], self.md, self.dev_out[b])
+            if self.after_layer is not None:
+                self.after_layer()
             in_free[b].record(cur)
             out_ready[b].record(cur)
             with torch.cuda.stream(self.s_out):

@@ -52,3 +52,77 @@ def shard_scales(scales, shard: HeadShard):
     if scales is None or scales.numel() == 1:
         return scales
     return scales[shard.kv_head_start: shard.kv_head_start + shard.num_kv_heads].contiguous()
+
+
+class ReplicaSplit:
+    """Batch split inside a KV-head replica group (tp > total_kv_heads).
+
+    The reference rule replicates a KV head on R = tp / total_kv_heads ranks; each of them then
+    streams the SAME KV pages of every sequence for its own 1/R of the head group, so the step's
+    dominant cost (KV bytes read) is paid R times. The R ranks hold identical caches, so instead each
+    rank can serve ALL query heads of the group for 1/R of the sequences: per-rank KV bytes drop by R
+    and the group exchanges only queries and outputs (B x Hq_rank x d bf16 each way — 0.4 % of the KV
+    bytes at cfg3). Results are identical head for head; the o_proj input layout is unchanged.
+
+    Plumbing is two `all_to_all_single` calls on the replica group (NCCL over NVLink on GPUs, gloo in
+    the CPU tests): `gather_q` before the decode, `scatter_out` after it.
+    """
+
+    def __init__(self, shard: HeadShard, group=None):
+        import torch.distributed as dist  # local: tp.py stays importable without torch.distributed use
+
+        self.dist = dist
+        self.R = shard.kv_replicas
+        self.index = shard.rank % self.R          # position inside the replica group
+        self.group = group
+        self.hq = shard.num_q_heads
+
+    @staticmethod
+    def groups(tp_size: int, kv_replicas: int):
+        """Rank lists of all replica groups (every rank must create every group, in this order)."""
+        return [list(range(g * kv_replicas, (g + 1) * kv_replicas)) for g in range(tp_size // kv_replicas)]
+
+    @property
+    def group_q_heads(self) -> int:
+        return self.R * self.hq
+
+    def plan(self, batch: int) -> tuple[int, int, int]:
+        """(sequences per rank incl. padding, first local sequence, one past the last local sequence)."""
+        per = -(-batch // self.R)
+        b0 = min(batch, self.index * per)
+        return per, b0, min(batch, b0 + per)
+
+    def _pad(self, x, rows: int):
+        import torch
+        if x.shape[0] == rows:
+            return x
+        pad = torch.zeros((rows - x.shape[0], *x.shape[1:]), dtype=x.dtype, device=x.device)
+        return torch.cat([x, pad])
+
+    def gather_q(self, q, out=None):
+        """q [B, Hq_rank, d] of this rank -> [per, R * Hq_rank, d]: all heads of the group for the
+        local sequences [b0, b1) (rows past b1 - b0 are padding)."""
+        import torch
+        per, _, _ = self.plan(q.shape[0])
+        send = self._pad(q, self.R * per).contiguous()
+        recv = torch.empty_like(send)             # [R, per, hq, d]: chunk i = peer i's heads, my sequences
+        self.dist.all_to_all_single(recv, send, group=self.group)
+        d = q.shape[-1]
+        res = recv.view(self.R, per, self.hq, d).permute(1, 0, 2, 3).reshape(per, self.R * self.hq, d)
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res.contiguous()
+
+    def scatter_out(self, out_local, batch: int, out=None):
+        """out_local [per, R * Hq_rank, d] -> [B, Hq_rank, d]: this rank's heads for every sequence."""
+        import torch
+        per, d = out_local.shape[0], out_local.shape[-1]
+        send = out_local.view(per, self.R, self.hq, d).permute(1, 0, 2, 3).contiguous()
+        recv = torch.empty_like(send)             # chunk i = peer i's sequences, my heads
+        self.dist.all_to_all_single(recv, send, group=self.group)
+        res = recv.view(self.R * per, self.hq, d)[:batch]
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
