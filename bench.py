@@ -116,6 +116,15 @@ class ClockSampler:
                            "reasons": sorted(reasons), "samples": len(sm)}
 
 
+T0 = time.perf_counter()
+
+
+def log(msg: str) -> None:
+    """Progress on stderr (rank 0): a hung run shows where it stopped."""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"[bench +{time.perf_counter() - T0:6.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
 def dist_setup(n_gpus: int):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -317,9 +326,12 @@ def run_b200(args, wl):
             torch.cuda.synchronize()
             return None
 
+    log(f"inputs ready: tp{world} rank{rank} Hq={hq} Hkv={hkv} replicas={sh.kv_replicas} L={L} B={B}")
     step()  # first call outside capture: lazy init (tensor maps, func attributes, NCCL)
     torch.cuda.synchronize()
+    log("first step done")
     g_step = capture(step)
+    log(f"step {'captured' if g_step is not None else 'NOT captured (eager)'}")
     run_step = g_step.replay if g_step is not None else step
     for _ in range(max(args.warmup, 3)):
         run_step()
@@ -333,6 +345,7 @@ def run_b200(args, wl):
         torch.cuda.synchronize()
     ms_total = max_over_ranks(e0.elapsed_time(e1), world)
     barrier(world)
+    log(f"timed region done: {ms_total / args.steps:.3f} ms/step")
     ms_per_step = ms_total / args.steps
     value = global_batch / (ms_per_step * 1e-3)
 
@@ -372,6 +385,7 @@ def run_b200(args, wl):
         torch.cuda.synchronize()
         kern_ms = [a.elapsed_time(b_) for a, b_ in kern_ms]
     kern_avg_ms = sum(kern_ms) / len(kern_ms)
+    log(f"kernel-only timing done: {kern_avg_ms * 1e3:.1f} us/launch")
     peak, peak_src = peaks()
     achieved = kv_bytes / (kern_avg_ms * 1e-3) / 1e9
     traffic = None  # DRAM read+write bytes per launch from the committed ncu --set full capture (N=1 shapes)
@@ -396,6 +410,7 @@ def run_b200(args, wl):
         except Exception as ex:  # report, never hide
             e2e = {"value": None, "unit": UNIT, "error": f"{type(ex).__name__}: {ex}"}
 
+    log("e2e leg done")
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n_seqs = min(wl.batch, 8)
