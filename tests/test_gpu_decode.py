@@ -309,15 +309,14 @@ def test_fp8_rejects_fixed_split_variants(lib):
 # Opt-in dynamic tail of the stream-K schedule (B200ATTN_SK_DYN = shift): the last 1 / 2^shift of
 # the tile stream is claimed in small chunks from a global counter. Same results, more partials.
 # ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("shift", ["1", "3"])
-@pytest.mark.parametrize("fp8", [False, True])
+@pytest.mark.parametrize("shift,fp8", [("1", False), ("1", True), ("3", False)])
 def test_streamk_dynamic_tail_matches_oracle(lib, monkeypatch, shift, fp8):
     monkeypatch.setenv("B200ATTN_SK_DYN", shift)
     # the dynamic share needs >= 2 tiles per warp: >= 16 (shift 3) / 4 (shift 1) tiles per warp overall,
     # i.e. >= 28k / 7k KV tiles on 148 x 12 warps
     big = [60000, 50000, 40000, 33333, 30000, 20001, 0, 17]
     medium = [9000, 1, 8191, 4096, 20000, 16000, 333]
-    for lens in ([big] if shift == "3" else [big, medium]):
+    for lens in ([big] if shift == "3" else [medium]):
         c = make_case(lens, hq=16, hkv=2, seed=len(lens), fp8=fp8)
         for _ in range(2):  # second launch: the claim counter must have been re-armed by the first
             out, lse = run_device(c, variant=ops.VARIANT_STREAMK)

@@ -106,9 +106,10 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
       tma_prefetch_desc(&tm_v);
     }
   }
-  // Programmatic dependent launch: everything above overlapped the previous kernel on the stream
-  // (the cache write); nothing it may have produced is read before this point.
-  griddep_wait();
+  // Programmatic dependent launch. Only this library's own kernels release their dependents early
+  // (cache write, decode, reduce) and none of them writes seq_lens, the block table or q, so the
+  // plan below may overlap the previous kernel; griddepcontrol.wait comes right before the first
+  // access to what they DO write — the KV cache, the workspace plan and the output.
   griddep_launch_dependents();
   // ---- per-CTA plan: tiles per sequence and their exclusive prefix (batch <= kSkMaxBatch)
   {
@@ -137,7 +138,8 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
     }
     if (threadIdx.x == W * 32 - 1) sm.cum[p.batch] = base + incl;
     __syncthreads();
-    if (blockIdx.x == 0) {  // the reduce kernel reads the same plan
+    if (blockIdx.x == 0) {  // the reduce kernel reads the same plan (a previous reduce may still be reading it)
+      griddep_wait();
       for (int i = threadIdx.x; i <= p.batch; i += W * 32) p.plan_cum[i] = sm.cum[i];
     }
   }
@@ -157,6 +159,7 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
   bool front_ahead = false;  // the front stands in chunk nxt_*, the math still in the previous one
   bool pf_done = false;      // no chunk left to claim
   bool first = true;         // the static chunk has not been handed out yet
+  bool waited = false;       // griddepcontrol.wait executed
   SkPos nxt_pos{0, 0, 0, 1};
   int nxt_count = 0, nxt_id = 0;
   int claim_val = 0;
@@ -232,6 +235,10 @@ paged_decode_streamk_kernel(const __grid_constant__ CUtensorMap tm_k, const __gr
         // the front stands on the first tile of an item (or chunk) it has not prepared yet; qf_n can
         // hold one prepared item, so the front never runs two starts ahead of the math
         if (pf_items_ahead == 1) break;
+        if (!waited) {  // first touch of q / the KV cache: the previous kernel must be complete
+          griddep_wait();
+          waited = true;
+        }
         WorkItem w;
         w.b = pf.b;
         w.kvh = pf.hs / p.subgroups;
@@ -418,32 +425,15 @@ streamk_reduce_kernel(__nv_bfloat16* __restrict__ out, int64_t out_stride_tok, f
     return static_cast<int64_t>(2 * cid + (t0 < cstart ? 0 : 1));
   };
 
-  // ---- pass 1: per-head maximum LSE over the pieces (thread = (piece mod 32, head))
-  {
-    const int hh = threadIdx.x & 7;
-    float mx = -CUDART_INF_F;
-    for (int k = threadIdx.x >> 3; k < pieces; k += kSkReduceWarps * 4)
-      mx = fmaxf(mx, part_lse[piece_slot(k) * kHeadsPerItem + hh]);
-    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-    if (lane < 8) s_max[warp][lane] = mx;
-  }
-  __syncthreads();
-  float mx[kHeadsPerItem];
-#pragma unroll
-  for (int hh = 0; hh < kHeadsPerItem; ++hh) {
-    float m = s_max[0][hh];
-#pragma unroll
-    for (int w = 1; w < kSkReduceWarps; ++w) m = fmaxf(m, s_max[w][hh]);
-    mx[hh] = m;
-  }
-  // ---- pass 2: warp w accumulates the pieces k = w, w + 8, ... for all heads
+  // ---- one pass: warp w folds the pieces k = w, w + 8, ... of all heads with a running reference
+  // (LSE and O of a piece are loaded together: one L2 round trip per piece instead of two)
   float4 acc[kHeadsPerItem];
-  float den[kHeadsPerItem];
+  float den[kHeadsPerItem], m[kHeadsPerItem];
 #pragma unroll
   for (int hh = 0; hh < kHeadsPerItem; ++hh) {
     acc[hh] = make_float4(0.f, 0.f, 0.f, 0.f);
     den[hh] = 0.f;
+    m[hh] = -CUDART_INF_F;
   }
   for (int k = warp; k < pieces; k += kSkReduceWarps) {
     const int64_t r0 = piece_slot(k) * kHeadsPerItem;
@@ -455,36 +445,45 @@ streamk_reduce_kernel(__nv_bfloat16* __restrict__ out, int64_t out_stride_tok, f
 #pragma unroll
     for (int hh = 0; hh < kHeadsPerItem; ++hh) {
       const float l = __shfl_sync(0xffffffffu, ls, hh);
-      const float wgt = (l == -CUDART_INF_F) ? 0.f : fast_exp2((l - mx[hh]) * kLog2e);
-      acc[hh].x = fmaf(o[hh].x, wgt, acc[hh].x);
-      acc[hh].y = fmaf(o[hh].y, wgt, acc[hh].y);
-      acc[hh].z = fmaf(o[hh].z, wgt, acc[hh].z);
-      acc[hh].w = fmaf(o[hh].w, wgt, acc[hh].w);
-      den[hh] += wgt;
+      if (l == -CUDART_INF_F) continue;  // empty partial
+      const float mn = fmaxf(m[hh], l);
+      const float a = fast_exp2((m[hh] - mn) * kLog2e);  // 0 when m = -inf
+      const float wgt = fast_exp2((l - mn) * kLog2e);
+      acc[hh].x = fmaf(o[hh].x, wgt, acc[hh].x * a);
+      acc[hh].y = fmaf(o[hh].y, wgt, acc[hh].y * a);
+      acc[hh].z = fmaf(o[hh].z, wgt, acc[hh].z * a);
+      acc[hh].w = fmaf(o[hh].w, wgt, acc[hh].w * a);
+      den[hh] = fmaf(den[hh], a, wgt);
+      m[hh] = mn;
     }
   }
 #pragma unroll
   for (int hh = 0; hh < kHeadsPerItem; ++hh) {
     *reinterpret_cast<float4*>(&s_acc[warp][hh][lane * 4]) = acc[hh];
-    if (lane == 0) s_den[warp][hh] = den[hh];
+    if (lane == 0) {
+      s_den[warp][hh] = den[hh];
+      s_max[warp][hh] = m[hh];
+    }
   }
   __syncthreads();
   // ---- fold the 8 warps: warp = head, lane = 4 output columns
   if (warp < heads_here) {
+    float mfin = s_max[0][warp];
+#pragma unroll
+    for (int w = 1; w < kSkReduceWarps; ++w) mfin = fmaxf(mfin, s_max[w][warp]);
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
     float dsum = 0.f;
 #pragma unroll
     for (int w = 0; w < kSkReduceWarps; ++w) {
+      const float mw = s_max[w][warp];
+      const float sc_w = (mw == -CUDART_INF_F) ? 0.f : fast_exp2((mw - mfin) * kLog2e);
       const float4 v = *reinterpret_cast<const float4*>(&s_acc[w][warp][lane * 4]);
-      a.x += v.x;
-      a.y += v.y;
-      a.z += v.z;
-      a.w += v.w;
-      dsum += s_den[w][warp];
+      a.x = fmaf(v.x, sc_w, a.x);
+      a.y = fmaf(v.y, sc_w, a.y);
+      a.z = fmaf(v.z, sc_w, a.z);
+      a.w = fmaf(v.w, sc_w, a.w);
+      dsum = fmaf(s_den[w][warp], sc_w, dsum);
     }
-    float mfin = s_max[0][warp];
-#pragma unroll
-    for (int w = 1; w < kSkReduceWarps; ++w) mfin = fmaxf(mfin, s_max[w][warp]);
     const float inv = dsum > 0.f ? 1.f / dsum : 0.f;
     const int h = h_first + warp;
     uint2 pk;
