@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 5
+#define B200ATTN_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -89,6 +89,41 @@ B200ATTN_API int b200attn_reshape_and_cache(
     void* k_cache, void* v_cache,
     int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
     const int64_t* slot_mapping, int32_t num_tokens,
+    int32_t num_kv_heads, int32_t head_size, int32_t block_size, int64_t num_blocks,
+    int32_t kv_dtype,
+    const float* k_scale, const float* v_scale, int32_t scale_numel,
+    void* stream);
+
+/*
+ * Fused rotary embedding + KV-cache write. Replaces the two launches the reference's attention
+ * layers issue before every attention call — `q, k = self.rotary_emb(positions, q, k)`
+ * (vllm_omni/model_executor/models/qwen2_5_omni/qwen2_old.py:151-153; vLLM
+ * model_executor/layers/rotary_embedding/{base,mrope}.py) and the cache write above — behind vLLM's hook
+ * AttentionImpl.do_rope_and_kv_cache_update (vllm/v1/attention/backend.py:815-840).
+ *
+ * For every token t < num_tokens, q head and k head: the first rot_dim elements are rotated IN PLACE
+ * in bf16 arithmetic (every product and sum rounded to bf16, as torch computes on bf16 tensors):
+ *     o1 = x1 * cos - x2 * sin,  o2 = x2 * cos + x1 * sin
+ *     NeoX (is_neox != 0): (x1, x2) = (x[p], x[p + rot_dim/2]); GPT-J: (x[2p], x[2p+1]); p < rot_dim/2
+ *     cos = cos_sin_cache[pos, p], sin = cos_sin_cache[pos, rot_dim/2 + p]   (bf16 rows, stride given)
+ * positions: i64 [num_tokens] (pos_rows = 1) or [3, num_tokens] (pos_rows = 3, M-RoPE: pair p takes its
+ * position from row r(p): chunked — r = section index of p in mrope_section (host i32[3]); interleaved —
+ * r = 1 if p % 3 == 1 and p < 3 * section[1], r = 2 if p % 3 == 2 and p < 3 * section[2], else 0).
+ * Then, for t < num_slot_tokens with slot_mapping[t] >= 0, the rotated key row and the value row are
+ * written to the cache exactly as b200attn_reshape_and_cache would (bf16 bit copy / e4m3 of x / scale).
+ */
+B200ATTN_API int b200attn_rope_and_cache(
+    void* query, int64_t q_stride_tok, int32_t num_q_heads,
+    void* key, const void* value,
+    int64_t key_stride_tok, int64_t key_stride_head,
+    int64_t value_stride_tok, int64_t value_stride_head,
+    const int64_t* positions, int32_t pos_rows, int64_t pos_stride_row,
+    const void* cos_sin_cache, int64_t cos_sin_stride, int64_t max_position,
+    int32_t rot_dim, int32_t is_neox,
+    const int32_t* mrope_section /* host, 3 ints, or NULL */, int32_t mrope_interleaved,
+    void* k_cache, void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    const int64_t* slot_mapping, int32_t num_tokens, int32_t num_slot_tokens,
     int32_t num_kv_heads, int32_t head_size, int32_t block_size, int64_t num_blocks,
     int32_t kv_dtype,
     const float* k_scale, const float* v_scale, int32_t scale_numel,

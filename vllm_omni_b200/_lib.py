@@ -12,7 +12,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 KV_BF16 = 0
 KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0
@@ -62,6 +62,17 @@ SIGNATURES: dict[str, tuple] = {
         _vp, _vp, _i64, _i64, _i64, _i64,
         _vp, _vp, *_CACHE_ARGS,
         _vp, _i32, _i32, _i32, _i32, _i64, _i32,
+        _vp, _vp, _i32, _vp]),
+    "b200attn_rope_and_cache": (C.c_int, [
+        _vp, _i64, _i32,                 # query, token stride, Hq
+        _vp, _vp, _i64, _i64, _i64, _i64,  # key, value, their token/head strides
+        _vp, _i32, _i64,                 # positions, rows (1|3), row stride
+        _vp, _i64, _i64,                 # cos_sin_cache, row stride, max_position
+        _i32, _i32,                      # rot_dim, is_neox
+        C.POINTER(_i32), _i32,           # mrope_section (host), interleaved
+        _vp, _vp, *_CACHE_ARGS,          # caches + strides
+        _vp, _i32, _i32,                 # slot_mapping, num_tokens, num_slot_tokens
+        _i32, _i32, _i32, _i64, _i32,    # Hkv, d, block_size, num_blocks, kv_dtype
         _vp, _vp, _i32, _vp]),
     "b200attn_decode_num_splits": (_i32, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),

@@ -222,6 +222,34 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         ops.reshape_and_cache(key, value, k_cache, v_cache, slot_mapping, self._kv_code,
                               getattr(layer, "_k_scale", None), getattr(layer, "_v_scale", None))
 
+    # ------------------------------------------------------------------ fused RoPE + cache write
+    def fused_rope_kvcache_supported(self) -> bool:
+        """vLLM's RopeKVCacheFusionPass may replace rotary_emb + unified_kv_cache_update by one call of
+        do_rope_and_kv_cache_update (vllm/compilation/passes/fusion/rope_kvcache_fusion.py)."""
+        return self.kv_sharing_target_layer_name is None
+
+    def do_rope_and_kv_cache_update(self, layer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                    positions: torch.Tensor, cos_sin_cache: torch.Tensor, is_neox: bool,
+                                    kv_cache: torch.Tensor, layer_slot_mapping: torch.Tensor) -> None:
+        """In-place RoPE on query/key + cache write of (rotated key, value) in ONE launch
+        (vllm/v1/attention/backend.py:823-840). query/key/value may arrive flat ([T, H*d])."""
+        k_cache, v_cache = ops.split_kv_cache(kv_cache)
+        q = query.view(query.shape[0], -1, self.head_size)
+        k = key.view(key.shape[0], -1, self.head_size)
+        v = value.view(value.shape[0], -1, self.head_size)
+        cs = cos_sin_cache if cos_sin_cache.dtype == torch.bfloat16 else self._cos_sin_bf16(cos_sin_cache)
+        ops.rope_and_cache(positions, q, k, v, cs, is_neox, k_cache, v_cache, layer_slot_mapping, self._kv_code,
+                           getattr(layer, "_k_scale", None), getattr(layer, "_v_scale", None))
+
+    def _cos_sin_bf16(self, cos_sin_cache: torch.Tensor) -> torch.Tensor:
+        """vLLM casts the table to the activation dtype on every call (`_match_cos_sin_cache_dtype`);
+        keep one bf16 copy per table instead."""
+        key = (cos_sin_cache.data_ptr(), tuple(cos_sin_cache.shape))
+        cache = self.__dict__.setdefault("_cs_cache", {})
+        if key not in cache:
+            cache[key] = cos_sin_cache.to(torch.bfloat16)
+        return cache[key]
+
     # ------------------------------------------------------------------ attention
     def forward(self, layer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
                 kv_cache: torch.Tensor, attn_metadata: B200AttentionMetadata,

@@ -340,6 +340,86 @@ int b200attn_reshape_and_cache(const void* key, const void* value, int64_t key_s
   return e == cudaSuccess ? 0 : cuda_fail(e, "cache_write launch");
 }
 
+int b200attn_rope_and_cache(void* query, int64_t q_stride_tok, int32_t num_q_heads, void* key, const void* value,
+                            int64_t key_stride_tok, int64_t key_stride_head, int64_t value_stride_tok,
+                            int64_t value_stride_head, const int64_t* positions, int32_t pos_rows,
+                            int64_t pos_stride_row, const void* cos_sin_cache, int64_t cos_sin_stride,
+                            int64_t max_position, int32_t rot_dim, int32_t is_neox, const int32_t* mrope_section,
+                            int32_t mrope_interleaved, void* k_cache, void* v_cache, int64_t cache_stride_block,
+                            int64_t cache_stride_slot, int64_t cache_stride_head, const int64_t* slot_mapping,
+                            int32_t num_tokens, int32_t num_slot_tokens, int32_t num_kv_heads, int32_t head_size,
+                            int32_t block_size, int64_t num_blocks, int32_t kv_dtype, const float* k_scale,
+                            const float* v_scale, int32_t scale_numel, void* stream) {
+  (void)max_position;
+  if (num_tokens < 0 || num_slot_tokens < 0 || num_slot_tokens > num_tokens)
+    return fail(B200ATTN_EINVAL, "need 0 <= num_slot_tokens <= num_tokens");
+  if (num_tokens == 0) return 0;
+  if (query == nullptr || key == nullptr || value == nullptr || positions == nullptr || cos_sin_cache == nullptr ||
+      (num_slot_tokens > 0 && slot_mapping == nullptr))
+    return fail(B200ATTN_EINVAL, "null query/key/value/positions/cos_sin_cache/slot_mapping");
+  if (int rc = check_cache_args(k_cache, v_cache, cache_stride_block, cache_stride_slot, cache_stride_head,
+                                num_blocks, num_kv_heads, head_size, block_size, kv_dtype))
+    return rc;
+  if (num_q_heads <= 0) return fail(B200ATTN_EINVAL, "num_q_heads must be positive");
+  if (rot_dim <= 0 || rot_dim > head_size || (rot_dim % 16) != 0)
+    return fail(B200ATTN_EUNSUPPORTED, "rot_dim %d must be a multiple of 16 in (0, head_size]", rot_dim);
+  if (pos_rows != 1 && pos_rows != 3) return fail(B200ATTN_EINVAL, "positions must be [T] or [3, T]");
+  if (pos_rows == 3) {
+    if (mrope_section == nullptr) return fail(B200ATTN_EINVAL, "M-RoPE positions need mrope_section");
+    if (mrope_section[0] + mrope_section[1] + mrope_section[2] != rot_dim / 2)
+      return fail(B200ATTN_EINVAL, "mrope_section must sum to rot_dim / 2");
+  }
+  if ((q_stride_tok % 8) || (key_stride_tok % 8) || (key_stride_head % 8) || (value_stride_tok % 8) ||
+      (value_stride_head % 8) || (cos_sin_stride % 8) || (reinterpret_cast<uintptr_t>(query) % 16) ||
+      (reinterpret_cast<uintptr_t>(key) % 16) || (reinterpret_cast<uintptr_t>(value) % 16) ||
+      (reinterpret_cast<uintptr_t>(cos_sin_cache) % 16))
+    return fail(B200ATTN_EINVAL, "query/key/value/cos_sin rows must be 16-byte aligned");
+  const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
+  if (fp8) {
+    if (k_scale == nullptr || v_scale == nullptr) return fail(B200ATTN_EINVAL, "fp8 cache needs scales");
+    if (scale_numel != 1 && scale_numel != num_kv_heads)
+      return fail(B200ATTN_EINVAL, "scale_numel %d must be 1 or num_kv_heads", scale_numel);
+  }
+  const int sms = cached_num_sms();
+  if (sms <= 0) return cuda_fail(cudaGetLastError(), "device query");
+  RopeCacheParams p{};
+  p.query = static_cast<__nv_bfloat16*>(query);
+  p.q_stride_tok = q_stride_tok;
+  p.key = static_cast<__nv_bfloat16*>(key);
+  p.value = static_cast<const __nv_bfloat16*>(value);
+  p.key_stride_tok = key_stride_tok;
+  p.key_stride_head = key_stride_head;
+  p.value_stride_tok = value_stride_tok;
+  p.value_stride_head = value_stride_head;
+  p.positions = positions;
+  p.pos_stride_row = pos_stride_row;
+  p.pos_rows = pos_rows;
+  for (int i = 0; i < 3; ++i) p.mrope_section[i] = (pos_rows == 3) ? mrope_section[i] : 0;
+  p.mrope_interleaved = mrope_interleaved;
+  p.cos_sin = static_cast<const __nv_bfloat16*>(cos_sin_cache);
+  p.cos_sin_stride = cos_sin_stride;
+  p.rot_dim = rot_dim;
+  p.is_neox = is_neox;
+  p.k_cache = static_cast<uint8_t*>(k_cache);
+  p.v_cache = static_cast<uint8_t*>(v_cache);
+  p.cs_block = cache_stride_block;
+  p.cs_slot = cache_stride_slot;
+  p.cs_head = cache_stride_head;
+  p.slot_mapping = slot_mapping;
+  p.num_tokens = num_tokens;
+  p.num_slot_tokens = num_slot_tokens;
+  p.num_q_heads = num_q_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.head_size = head_size;
+  p.block_size = block_size;
+  p.num_blocks = num_blocks;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.scale_stride = scale_numel > 1 ? 1 : 0;
+  cudaError_t e = launch_rope_cache(p, fp8, sms, env_flag("B200ATTN_PDL", true), static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "rope_cache launch");
+}
+
 int32_t b200attn_decode_num_splits(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                                    int32_t max_seq_len, int32_t num_sms) {
   if (batch <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || num_sms <= 0) return 1;

@@ -68,6 +68,32 @@ struct CacheWriteParams {
 };
 cudaError_t launch_cache_write(const CacheWriteParams& p, bool fp8, int num_sms, bool pdl, cudaStream_t stream);
 
+struct RopeCacheParams {
+  __nv_bfloat16* query;  // [T, Hq, d], rotated in place
+  int64_t q_stride_tok;
+  __nv_bfloat16* key;    // [T, Hkv, d], rotated in place
+  const __nv_bfloat16* value;
+  int64_t key_stride_tok, key_stride_head, value_stride_tok, value_stride_head;
+  const int64_t* positions;  // [T] or [3, T]
+  int64_t pos_stride_row;
+  int32_t pos_rows;          // 1 = plain RoPE, 3 = M-RoPE
+  int32_t mrope_section[3];
+  int32_t mrope_interleaved;
+  const __nv_bfloat16* cos_sin;  // [max_pos, rot_dim]: cos | sin
+  int64_t cos_sin_stride;
+  int32_t rot_dim, is_neox;
+  uint8_t* k_cache;
+  uint8_t* v_cache;
+  int64_t cs_block, cs_slot, cs_head;
+  const int64_t* slot_mapping;
+  int32_t num_tokens, num_slot_tokens, num_q_heads, num_kv_heads, head_size, block_size;
+  int64_t num_blocks;
+  const float* k_scale;
+  const float* v_scale;
+  int32_t scale_stride;
+};
+cudaError_t launch_rope_cache(const RopeCacheParams& p, bool fp8, int num_sms, bool pdl, cudaStream_t stream);
+
 struct GatherParams {
   const uint8_t* cache;
   int64_t cs_block, cs_slot, cs_head;  // elements

@@ -110,6 +110,62 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Ten
         slot_mapping.data_ptr(), n, hkv, d, bs, nb, code, ks, vs, sn, _stream()))
 
 
+def rope_and_cache(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                   cos_sin_cache: torch.Tensor, is_neox: bool, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                   slot_mapping: torch.Tensor, kv_cache_dtype: str | int = "auto",
+                   k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None,
+                   rot_dim: int | None = None, mrope_section: list[int] | None = None,
+                   mrope_interleaved: bool = False) -> None:
+    """Fused rotary embedding (query and key rotated IN PLACE) + KV-cache write of the rotated key and
+    the value; one launch for what vLLM does as rotary_emb + reshape_and_cache_flash
+    (hook: AttentionImpl.do_rope_and_kv_cache_update, vllm/v1/attention/backend.py:815-840).
+    query [T, Hq, d] / key, value [T, Hkv, d] bf16 (token/head strides free), positions int64 [T] or [3, T]
+    (M-RoPE), cos_sin_cache bf16 [max_pos, rot_dim] = cos | sin, slot_mapping int64 [<= T]."""
+    import ctypes as C
+    lib = _lib.load()
+    _need_cuda(positions, query, key, value, cos_sin_cache, k_cache, v_cache, slot_mapping)
+    code = kv_dtype_code(kv_cache_dtype)
+    fp8 = code == KV_FP8_E4M3
+    for name, x in (("query", query), ("key", key), ("value", value)):
+        if x.dtype != torch.bfloat16 or x.ndim != 3 or x.stride(2) != 1:
+            raise ValueError(f"{name} must be bfloat16 [T, H, d] with contiguous d")
+    if query.stride(1) != query.shape[2]:
+        raise ValueError("query heads must be contiguous")
+    if cos_sin_cache.dtype != torch.bfloat16 or cos_sin_cache.ndim != 2 or cos_sin_cache.stride(1) != 1:
+        raise ValueError("cos_sin_cache must be bfloat16 [max_pos, rot_dim] (cast it once at load time)")
+    if positions.dtype != torch.int64 or positions.ndim not in (1, 2) or positions.stride(-1) != 1:
+        raise ValueError("positions must be int64 [T] or [3, T]")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be contiguous int64")
+    T = positions.shape[-1]
+    if query.shape[0] < T or key.shape[0] < T or value.shape[0] < T or slot_mapping.numel() > T:
+        raise ValueError("token counts of positions / query / key / value / slot_mapping do not agree")
+    rot = int(rot_dim) if rot_dim is not None else cos_sin_cache.shape[1]
+    if fp8 and k_cache.dtype == torch.float8_e4m3fn:
+        k_cache, v_cache = k_cache.view(torch.uint8), v_cache.view(torch.uint8)
+    want = torch.uint8 if fp8 else torch.bfloat16
+    if k_cache.dtype != want or v_cache.dtype != want:
+        raise ValueError(f"cache dtype {k_cache.dtype} does not match kv_cache_dtype")
+    sb, ss, sh = _cache_strides(k_cache, v_cache)
+    nb, bs, hkv, d = k_cache.shape
+    if key.shape[1] != hkv or key.shape[2] != d or value.shape[1:] != key.shape[1:] or query.shape[2] != d:
+        raise ValueError("query/key/value head layout does not match the cache")
+    rows = 1 if positions.ndim == 1 else positions.shape[0]
+    sec = None
+    if rows != 1:
+        if mrope_section is None or len(mrope_section) != 3:
+            raise ValueError("[3, T] positions need mrope_section (3 ints)")
+        sec = (C.c_int32 * 3)(*[int(x) for x in mrope_section])
+    ks, vs, sn = _scales(k_scale, v_scale, fp8)
+    check("b200attn_rope_and_cache", lib.b200attn_rope_and_cache(
+        query.data_ptr(), query.stride(0), query.shape[1], key.data_ptr(), value.data_ptr(), key.stride(0),
+        key.stride(1), value.stride(0), value.stride(1), positions.data_ptr(), rows,
+        positions.stride(0) if rows != 1 else 0, cos_sin_cache.data_ptr(), cos_sin_cache.stride(0),
+        cos_sin_cache.shape[0], rot, 1 if is_neox else 0, sec, 1 if mrope_interleaved else 0,
+        k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, slot_mapping.data_ptr(), T, slot_mapping.numel(),
+        hkv, d, bs, nb, code, ks, vs, sn, _stream()))
+
+
 def decode_num_splits(batch: int, num_q_heads: int, num_kv_heads: int, max_seq_len: int,
                       sms: int | None = None) -> int:
     lib = _lib.load()
