@@ -53,6 +53,9 @@ def parse_args():
                     help="when tp > KV heads: 'replicate' = every rank of a replica group streams the whole KV "
                          "head for its own query heads (the reference rule); 'split' = the group splits the "
                          "batch and exchanges q/out (tp.ReplicaSplit: same results, 1/R of the KV bytes per rank)")
+    ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"],
+                    help="the o_proj row-parallel sum after every layer (N > 1): 'peer' = this repo's peer-memory "
+                         "kernel over NVLink (one-/two-shot, csrc/peer_allreduce.cu), 'nccl' = dist.all_reduce")
     ap.add_argument("--total-kv-heads", type=int, default=0, help="override the workload's KV-head count "
                     "(e.g. 1 with --gpus 2 exercises KV-head replication on two GPUs)")
     return ap.parse_args()
@@ -286,8 +289,30 @@ def run_b200(args, wl):
     splits = 0 if streamk else (args.splits or ops.decode_num_splits(B, hq, hkv, inp.max_seq_len))
     ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, dhq, d, max(splits, 1)))
     hidden = torch.zeros(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")  # o_proj output stand-in
+    ar, ar_note, hidden_out = None, None, None
     if world > 1:
         import torch.distributed as dist
+        ar_note = "nccl all_reduce"
+        if args.allreduce == "peer":
+            from vllm_omni_b200 import peer
+            try:
+                ar = peer.PeerAllReduce.create(max_numel=hidden.numel())
+                hidden = ar.input(hidden.shape)           # o_proj would write its partial sums here
+                hidden.zero_()
+                hidden_out = torch.empty(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")
+                algo = peer.ALGO_NAMES[peer.choose_algo(2 * hidden.numel(), world, ar.has_multicast)]
+                ar_note = f"peer-memory {algo} kernel ({ar.transport} mapping, multicast={ar.has_multicast})"
+            except Exception as ex:  # noqa: BLE001 - say so in the JSON line, never silently
+                ar = None
+                ar_note = f"nccl all_reduce (peer-memory setup failed: {type(ex).__name__}: {str(ex)[:200]})"
+                log(ar_note)
+
+    def o_proj_sum():
+        """The only collective next to the path: o_proj's row-parallel sum of [B, hidden] bf16."""
+        if ar is not None:
+            ar.all_reduce(hidden, out=hidden_out)
+        else:
+            dist.all_reduce(hidden)
 
     def step():
         for kc, vc in caches:
@@ -302,9 +327,10 @@ def run_b200(args, wl):
             if rs is not None:
                 rs.scatter_out(out_grp, B, out=out)
             if world > 1:
-                dist.all_reduce(hidden)  # the only collective next to the path: o_proj's row-parallel sum
+                o_proj_sum()
 
-    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0))  # our kernels only (not NCCL / copies)
+    # our kernels only (not NCCL / copies): cache write + decode (+ reduce) (+ peer all-reduce)
+    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0) + (1 if ar is not None else 0))
 
     def capture(fn):
         """CUDA-graph the launches of `fn` (how vLLM replays decode steps); None if capture fails."""
@@ -406,7 +432,8 @@ def run_b200(args, wl):
     e2e = None
     if not args.no_e2e:
         try:
-            e2e = run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs)
+            e2e = run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs,
+                          o_proj_sum if world > 1 else None)
         except Exception as ex:  # report, never hide
             e2e = {"value": None, "unit": UNIT, "error": f"{type(ex).__name__}: {ex}"}
 
@@ -430,6 +457,7 @@ def run_b200(args, wl):
                                                "replica_mode": (args.replica_mode if sh.kv_replicas > 1 else None),
                                                "decode_q_heads": dhq, "decode_batch": int(dq.shape[0]),
                                                "kv_bytes_per_layer": kv_bytes},
+            "collective": ar_note,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -442,7 +470,7 @@ def run_b200(args, wl):
         os._exit(0)
 
 
-def run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs=None):
+def run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs=None, after_layer=None):
     from vllm_omni_b200 import backend as be
     from vllm_omni_b200.host_runner import HostStepRunner
     impl = be.B200AttentionImpl(hq, d, inp.softmax_scale, hkv, None, None, wl.kv_cache_dtype)
@@ -454,11 +482,6 @@ def run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs
         seq_lens=inp.seq_lens, block_table=inp.block_table, slot_mapping=inp.slot_mapping, num_decodes=B,
         num_decode_tokens=B, num_prefills=0, num_prefill_tokens=0, prefill_query_start_loc=None,
         prefill_max_query_len=0, decode_num_splits=splits, workspace=ws)
-    after_layer = None
-    if world > 1:
-        import torch.distributed as dist
-        hidden = torch.zeros(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")
-        after_layer = lambda: dist.all_reduce(hidden)  # noqa: E731 - the o_proj row-parallel sum stand-in
     runner = HostStepRunner(impl, md, inp.kv_caches, B, hq, hkv, d, inp.slot_mapping, inp.k_scale, inp.v_scale,
                             after_layer=after_layer)
     qkv_dev = torch.cat([inp.q.reshape(B, -1), inp.new_k.reshape(B, -1), inp.new_v.reshape(B, -1)], dim=1)

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 6
+#define B200ATTN_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -265,6 +265,56 @@ B200ATTN_API int b200attn_gather_kv(
     const int32_t* block_ids, int32_t num_block_ids, int32_t seq_len,
     int32_t num_kv_heads, int32_t head_size, int32_t block_size, int32_t kv_dtype,
     void* dst, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Peer-memory all-reduce (sum over ranks, bf16 in / fp32 accumulate in rank order / bf16 out).
+ *
+ * Replaces the collective behind the o_proj row-parallel sum that follows attention:
+ * vllm/distributed/communication_op.py:12 tensor_model_parallel_all_reduce (reached from
+ * RowParallelLinear.forward, called by Qwen2Attention.forward
+ * vllm_omni/model_executor/models/qwen2_5_omni/qwen2_old.py:155 `output, _ = self.o_proj(attn_output)`).
+ * One process per GPU; every rank owns one peer-mapped allocation (same size on every rank) and
+ * passes HOST arrays of `world` device pointers — entry r = rank r's region as mapped into THIS
+ * process. The launch is asynchronous on `stream`, CUDA-graph capturable, and touches no host state.
+ *
+ *   peer_flags[r]   B200ATTN_PEER_FLAG_BYTES of uint32 flag words, zeroed ONCE before the first
+ *                   launch (then a cross-rank barrier); never reset afterwards.
+ *   peer_in[r]      the bf16 input of rank r (16-byte aligned).
+ *   peer_scratch[r] >= ceil(numel/8/world + 1) * 16 bytes, used by TWOSHOT (may be NULL otherwise).
+ *   out             local result. ONESHOT/TWOSHOT: any device pointer that no peer reads (it may
+ *                   not alias peer_in). MULTIMEM: this rank's unicast view of the region `mc_out`
+ *                   multicasts to.
+ *   mc_in / mc_out  multicast addresses of the input / output regions (MULTIMEM) or NULL.
+ *   numel           multiple of 8.  algo: AUTO picks by size (b200attn_peer_allreduce_algo).
+ *   timeout_ns      a flag wait longer than this records {1, block, peer, epoch} in the 4 words after the
+ *                   flag slots and traps the kernel (0 = 10 s). With B200ATTN_PEER_SOFT_TIMEOUT=1 in the
+ *                   environment (tests) the wait is abandoned instead and the result is undefined.
+ * ONESHOT and TWOSHOT are bit-identical on every rank and equal to the sequential fp32 sum in rank
+ * order rounded once to bf16; MULTIMEM leaves the order to the switch (fp32 accumulate).
+ */
+#define B200ATTN_PEER_FLAG_BYTES 8192
+#define B200ATTN_PEER_MAX_RANKS 8
+#define B200ATTN_AR_AUTO 0
+#define B200ATTN_AR_ONESHOT 1
+#define B200ATTN_AR_TWOSHOT 2
+#define B200ATTN_AR_MULTIMEM 3
+/* pure host arithmetic: the schedule AUTO resolves to for `bytes` of input on `world` ranks */
+B200ATTN_API int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast);
+B200ATTN_API int b200attn_peer_allreduce(
+    const void* const* peer_in, void* const* peer_scratch, void* const* peer_flags,
+    void* out, const void* mc_in, void* mc_out,
+    int64_t numel, int32_t world, int32_t rank, int32_t algo, int32_t max_blocks,
+    uint64_t timeout_ns, void* stream);
+
+/*
+ * Peer-mappable allocations through CUDA IPC for hosts without torch symmetric memory:
+ * alloc = cudaMalloc + zero fill + cudaIpcGetMemHandle (64-byte handle to ship to the peers by any
+ * host channel), open = cudaIpcOpenMemHandle with lazy peer access, close / free undo them.
+ */
+B200ATTN_API int b200attn_peer_alloc(size_t bytes, void** ptr, void* handle64);
+B200ATTN_API int b200attn_peer_open(const void* handle64, void** ptr);
+B200ATTN_API int b200attn_peer_close(void* ptr);
+B200ATTN_API int b200attn_peer_free(void* ptr);
 
 /*
  * Debug aid for profiling the stream-K schedule: when set (thread-local, device pointer to

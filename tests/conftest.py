@@ -8,6 +8,9 @@ ROOT = Path(__file__).resolve().parent.parent
 if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
 os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+# the peer all-reduce protocol test runs up to 8 co-operating kernels on 8 streams of one device: give every
+# stream its own hardware queue so none of them is falsely serialised behind a spinning one
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 
 def pytest_configure(config):

@@ -1,0 +1,91 @@
+#!/usr/bin/env python
+"""Golden vectors for the ATTENTION OUTPUT of the path, produced by the reference's own stock code:
+the kernels vLLM's FLASH_ATTN and FLASHINFER backends run for decode (what vllm-omni's AR stages use
+before this repo's backend is registered) and vLLM's `reshape_and_cache_flash` for the slot writes.
+
+Runs on a GPU box with vLLM installed (no /root/reference needed; the arithmetic of this path lives in
+vLLM):
+
+    python tests/golden/gen_vllm_gpu_golden.py gpurun_out/golden     # then copy *.npz to tests/golden/
+
+Each file holds the complete inputs (q, paged cache as written by vLLM's own cache-write kernel, block
+table, seq_lens, scale) and the outputs of every stock kernel that loaded, so the CPU suite can pin the
+oracle (`oracle.ref_paged_decode`, the C oracle) against them without a GPU:
+  out_fa2/out_fa3/out_fa4   vllm.vllm_flash_attn.flash_attn_varlen_func (flash_attn.py:758-819 call shape)
+  out_trtllm                flashinfer trtllm_batch_decode_with_kv_cache (flashinfer.py:1694-1822)
+  cache_vllm                the cache after vLLM's reshape_and_cache_flash (vllm/_custom_ops.py:2591-2610)
+bf16 arrays are stored as their int16 bit patterns.
+"""
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[2]
+sys.path.insert(0, str(ROOT))
+import numpy as np
+import torch
+
+from tests.helpers import make_case
+
+CASES = {
+    # name: (seq_lens, hq, hkv, seed)  — thinker / talker head shapes of SURVEY §8, ragged lengths incl. 1 and
+    # non-multiples of the block size
+    "decode_32q4kv": ([130, 17, 1, 64], 32, 4, 11),
+    "decode_28q4kv": ([96, 33], 28, 4, 12),
+    "decode_16q2kv": ([48, 1, 15, 16, 150], 16, 2, 13),
+}
+
+
+def bits(t: torch.Tensor) -> np.ndarray:
+    return t.detach().cpu().contiguous().view(torch.int16).numpy()
+
+
+def main(out_dir: Path):
+    out_dir.mkdir(parents=True, exist_ok=True)
+    assert torch.cuda.is_available()
+    from vllm import _custom_ops as vops
+    for name, (lens, hq, hkv, seed) in CASES.items():
+        c = make_case(lens, hq=hq, hkv=hkv, seed=seed)
+        d, bs, nb = 128, c.block_size, c.num_blocks
+        # vLLM's own cache write into an NHD cache [2, nb, bs, Hkv, d]
+        kv = torch.zeros(2, nb, bs, hkv, d, dtype=torch.bfloat16, device="cuda")
+        one = torch.ones(1, dtype=torch.float32, device="cuda")
+        vops.reshape_and_cache_flash(c.hist_k.cuda(), c.hist_v.cuda(), kv[0], kv[1], c.slots.cuda(), "auto", one, one)
+        torch.cuda.synchronize()
+        rec = dict(q=bits(c.q), cache_vllm=bits(kv), block_table=c.block_table.numpy(), seq_lens=c.seq_lens.numpy(),
+                   scale=np.float32(c.scale), hq=hq, hkv=hkv, seed=seed)
+        q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
+        B = q.shape[0]
+        cu_q = torch.arange(B + 1, dtype=torch.int32, device="cuda")
+        try:
+            from vllm.vllm_flash_attn import flash_attn_varlen_func
+            for ver in (2, 3, 4):
+                try:
+                    out = torch.empty_like(q)
+                    flash_attn_varlen_func(q, kv[0], kv[1], max_seqlen_q=1, cu_seqlens_q=cu_q,
+                                           max_seqlen_k=c.max_seq_len, seqused_k=sl, softmax_scale=c.scale,
+                                           causal=True, block_table=bt, out=out, fa_version=ver)
+                    torch.cuda.synchronize()
+                    rec[f"out_fa{ver}"] = bits(out)
+                except Exception as e:  # noqa: BLE001
+                    print(f"{name}: flash-attn v{ver} unavailable: {type(e).__name__}: {str(e)[:120]}")
+        except Exception as e:  # noqa: BLE001
+            print(f"{name}: vllm_flash_attn unavailable: {e}")
+        try:
+            import flashinfer
+            ws = torch.zeros(128 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+            k = kv[0].permute(0, 2, 1, 3).contiguous()   # HND
+            v = kv[1].permute(0, 2, 1, 3).contiguous()
+            out = torch.empty_like(q)
+            flashinfer.decode.trtllm_batch_decode_with_kv_cache(q, (k, v), ws, bt, sl, c.max_seq_len,
+                                                                bmm1_scale=c.scale, bmm2_scale=1.0, out=out,
+                                                                kv_layout="HND")
+            torch.cuda.synchronize()
+            rec["out_trtllm"] = bits(out)
+        except Exception as e:  # noqa: BLE001
+            print(f"{name}: flashinfer trtllm-gen unavailable: {type(e).__name__}: {str(e)[:120]}")
+        np.savez_compressed(out_dir / f"vllm_{name}.npz", **rec)
+        print(f"{name}: wrote {sorted(k for k in rec if k.startswith('out_'))}")
+
+
+if __name__ == "__main__":
+    main(Path(sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/golden"))

@@ -1,0 +1,95 @@
+"""GPU: the peer-memory all-reduce kernels against the sequential fp32 oracle, bit for bit.
+
+The cross-rank flag protocol is exercised on ONE device: `PeerAllReduce.local_ranks(world)` builds `world`
+'ranks' whose peer regions are plain allocations on cuda:0, each launched on its own stream, so the
+kernels wait for each other exactly as ranks on different GPUs do. (The real multi-process transports are
+covered by tests/test_gpu_peer_multi.py on a 2-GPU box and by `bench.py --gpus N`.)"""
+import pytest
+import torch
+
+from oracle import oracle
+from vllm_omni_b200 import _lib, peer
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def soft_timeout(monkeypatch):
+    """A wait that times out (co-residency not granted on this device) must fail the test, not kill the context."""
+    monkeypatch.setenv("B200ATTN_PEER_SOFT_TIMEOUT", "1")
+
+
+def run_ranks(ars, xs, algo, repeats=1):
+    streams = [torch.cuda.Stream() for _ in ars]
+    ins = [ar.input(x.shape) for ar, x in zip(ars, xs)]
+    for i, x in zip(ins, xs):
+        i.copy_(x)
+    outs = [torch.full_like(x, float("nan")) for x in xs]
+    torch.cuda.synchronize()
+    for _ in range(repeats):
+        for ar, s, i, o in zip(ars, streams, ins, outs):
+            with torch.cuda.stream(s):
+                ar.all_reduce(i, out=o, algo=algo)
+    torch.cuda.synchronize()
+    return outs
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("algo", [_lib.AR_ONESHOT, _lib.AR_TWOSHOT])
+@pytest.mark.parametrize("numel", [8, 8 * 37, 64 * 2048, 128 * 2048 + 24])
+def test_allreduce_matches_oracle_bit_exact(lib, world, algo, numel):
+    g = torch.Generator().manual_seed(world * 1000 + numel)
+    xs_cpu = [(torch.randn(numel, generator=g) * 3).to(torch.bfloat16) for _ in range(world)]
+    ars = peer.PeerAllReduce.local_ranks(world, numel, timeout_s=5.0, max_blocks=16)
+    outs = run_ranks(ars, [x.cuda() for x in xs_cpu], algo, repeats=3)   # epochs carry over launches
+    ref = oracle.ref_all_reduce_bf16(xs_cpu)
+    for r, o in enumerate(outs):
+        assert torch.equal(o.cpu().view(torch.int16), ref.view(torch.int16)), f"rank {r} differs"
+        assert ars[r].error_words() == [0, 0, 0, 0]
+
+
+def test_allreduce_auto_and_graph_replay(lib):
+    """AUTO schedule inside CUDA graphs (one per rank), replayed: the flag epochs live in device memory."""
+    world, shape = 4, (128, 2048)
+    g = torch.Generator().manual_seed(7)
+    xs_cpu = [torch.randn(shape, generator=g).to(torch.bfloat16) for _ in range(world)]
+    ars = peer.PeerAllReduce.local_ranks(world, shape[0] * shape[1], timeout_s=5.0, max_blocks=16)
+    xs = [x.cuda() for x in xs_cpu]
+    outs = run_ranks(ars, xs, _lib.AR_AUTO)
+    ref = oracle.ref_all_reduce_bf16(xs_cpu)
+    assert all(torch.equal(o.cpu(), ref) for o in outs)
+    assert ars[0].last_algo == peer.choose_algo(2 * xs[0].numel(), world, False) == _lib.AR_TWOSHOT
+    graphs, gouts = [], []
+    for ar in ars:
+        o = torch.empty(shape, dtype=torch.bfloat16, device="cuda")
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            ar.all_reduce(ar.input(shape), out=o)
+        graphs.append(gr)
+        gouts.append(o)
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream() for _ in ars]
+    for it in range(3):
+        for ar, x in zip(ars, xs_cpu):
+            ar.input(shape).copy_((x.float() * (it + 1)).to(torch.bfloat16))
+        torch.cuda.synchronize()
+        for gr, s in zip(graphs, streams):
+            with torch.cuda.stream(s):
+                gr.replay()
+        torch.cuda.synchronize()
+        ref = oracle.ref_all_reduce_bf16([(x.float() * (it + 1)).to(torch.bfloat16) for x in xs_cpu])
+        assert all(torch.equal(o.cpu(), ref) for o in gouts)
+
+
+def test_allreduce_rejects_bad_arguments(lib):
+    ar = peer.PeerAllReduce.local_ranks(1, 64)[0]
+    with pytest.raises(ValueError):
+        ar.all_reduce(torch.zeros(12, dtype=torch.bfloat16, device="cuda"))      # not a multiple of 8
+    with pytest.raises(ValueError):
+        ar.all_reduce(torch.zeros(16, dtype=torch.float16, device="cuda"))
+    with pytest.raises(ValueError):
+        ar.all_reduce(torch.zeros(16, dtype=torch.bfloat16))                     # CPU tensor: no CPU path
+    with pytest.raises(_lib.B200AttnError):
+        ar.all_reduce(ar.input((16,)), out=ar.input((16,)))                      # out aliases the input region
+    with pytest.raises(peer.PeerSetupError):
+        ar.all_reduce(ar.input((16,)), algo=_lib.AR_MULTIMEM)

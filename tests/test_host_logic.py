@@ -148,3 +148,44 @@ def test_impl_rejects_unsupported_features(backend):
     assert impl.forward(None, None, None, None, None, None, out).abs().sum() == 0  # profiling run
     with pytest.raises(NotImplementedError):
         impl.forward(None, None, None, None, None, object(), out, output_scale=torch.ones(1))
+
+
+# ---- peer-memory all-reduce: host arithmetic (no GPU) ----
+def test_peer_allreduce_schedule_choice_and_region_layout(lib, monkeypatch):
+    from vllm_omni_b200 import _lib, peer
+    monkeypatch.delenv("B200ATTN_AR_MULTIMEM", raising=False)
+    # two ranks: the same bytes cross NVLink either way, so never pay the extra barrier
+    assert peer.choose_algo(8 << 20, 2, False) == _lib.AR_ONESHOT
+    for world in (4, 8):
+        assert peer.choose_algo(64 << 10, world, False) == _lib.AR_ONESHOT
+        assert peer.choose_algo(512 << 10, world, False) == _lib.AR_TWOSHOT
+        assert peer.choose_algo(512 << 10, world, True) == _lib.AR_TWOSHOT      # multimem is opt-in
+    monkeypatch.setenv("B200ATTN_AR_MULTIMEM", "1")
+    assert peer.choose_algo(512 << 10, 8, True) == _lib.AR_MULTIMEM
+    assert peer.choose_algo(512 << 10, 8, False) == _lib.AR_TWOSHOT
+    off_in, off_scr, cap, total = peer.region_layout(512 * 2048)
+    assert off_in == _lib.PEER_FLAG_BYTES and off_in % 256 == 0 and off_scr % 256 == 0
+    assert cap >= 512 * 2048 * 2 + 16 and off_scr == off_in + cap and total == off_scr + cap
+
+
+def test_peer_allreduce_api_rejects_bad_arguments_without_a_gpu(lib):
+    import ctypes as C
+    from vllm_omni_b200 import _lib
+    arr = (C.c_void_p * 2)(C.c_void_p(4096), C.c_void_p(8192))
+    f = lib.b200attn_peer_allreduce
+    assert f(arr, arr, arr, 65536, None, None, 64, 3, 0, 1, 0, 0, None) == -2      # world 3 unsupported
+    assert f(arr, arr, arr, 65536, None, None, 12, 2, 0, 1, 0, 0, None) == -1      # numel % 8
+    assert f(arr, arr, arr, 65536, None, None, 64, 2, 2, 1, 0, 0, None) == -1      # rank out of range
+    assert f(arr, arr, arr, 65536, None, None, 64, 2, 0, 3, 0, 0, None) == -1      # multimem without multicast ptrs
+    assert f(arr, arr, arr, 4096, None, None, 64, 2, 0, 1, 0, 0, None) == -1       # out aliases the input
+    assert f(arr, arr, arr, 65536, None, None, 0, 2, 0, 1, 0, 0, None) == 0        # empty: nothing to do
+
+
+def test_oracle_all_reduce_is_sequential_fp32_then_one_rounding():
+    import torch
+    from oracle import oracle
+    a = torch.tensor([1.0, 256.0, -3.0]).to(torch.bfloat16)
+    b = torch.tensor([0.00390625, 1.0, 3.0]).to(torch.bfloat16)       # 2^-8: lost only at the final rounding
+    c = torch.tensor([0.00390625, 1.0, 0.0]).to(torch.bfloat16)
+    out = oracle.ref_all_reduce_bf16([a, b, c])
+    assert out.tolist() == [1.0078125, 258.0, 0.0]                    # 1 + 2^-7 is representable; a bf16 running sum would give 1.0

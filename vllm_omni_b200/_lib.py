@@ -12,7 +12,9 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 6
+ABI_VERSION = 7
+PEER_FLAG_BYTES = 8192
+AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM = 0, 1, 2, 3
 KV_BF16 = 0
 KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0
@@ -95,6 +97,16 @@ SIGNATURES: dict[str, tuple] = {
         _vp, _vp, _i32, _vp]),
     "b200attn_gather_kv": (C.c_int, [
         _vp, *_CACHE_ARGS, _i64, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "b200attn_peer_allreduce_algo": (_i32, [_i64, _i32, _i32]),
+    "b200attn_peer_allreduce": (C.c_int, [
+        C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),   # peer_in, peer_scratch, peer_flags (host arrays)
+        _vp, _vp, _vp,                                    # out, mc_in, mc_out
+        _i64, _i32, _i32, _i32, _i32,                     # numel, world, rank, algo, max_blocks
+        C.c_uint64, _vp]),                                # timeout_ns, stream
+    "b200attn_peer_alloc": (C.c_int, [_sz, C.POINTER(_vp), C.c_char_p]),
+    "b200attn_peer_open": (C.c_int, [C.c_char_p, C.POINTER(_vp)]),
+    "b200attn_peer_close": (C.c_int, [_vp]),
+    "b200attn_peer_free": (C.c_int, [_vp]),
 }
 
 _lib: C.CDLL | None = None

@@ -824,4 +824,109 @@ int b200attn_gather_kv(const void* cache, int64_t cache_stride_block, int64_t ca
   return e == cudaSuccess ? 0 : cuda_fail(e, "gather_kv launch");
 }
 
+// ---------------------------------------------------------------------------------------------
+// peer-memory all-reduce
+// ---------------------------------------------------------------------------------------------
+static_assert(kPeerFlagBytes == B200ATTN_PEER_FLAG_BYTES && kPeerMaxRanks == B200ATTN_PEER_MAX_RANKS &&
+                  (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 4) * 4 <= kPeerFlagBytes, "flag region");
+
+int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast) {
+  // bytes crossing NVLink per rank: ONESHOT (world-1) x bytes, TWOSHOT 2 x (world-1)/world x bytes + one more
+  // flag barrier (~1.5 us): the same at world 2, so ONESHOT there; the crossover sits near 256 KiB at 4 and 8 ranks.
+  if (world <= 2) return B200ATTN_AR_ONESHOT;
+  if (has_multicast && env_flag("B200ATTN_AR_MULTIMEM", false) && bytes >= (64 << 10)) return B200ATTN_AR_MULTIMEM;
+  return bytes <= (256 << 10) ? B200ATTN_AR_ONESHOT : B200ATTN_AR_TWOSHOT;
+}
+
+int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratch, void* const* peer_flags,
+                            void* out, const void* mc_in, void* mc_out, int64_t numel, int32_t world,
+                            int32_t rank, int32_t algo, int32_t max_blocks, uint64_t timeout_ns, void* stream) {
+  if (world != 1 && world != 2 && world != 4 && world != 8)
+    return fail(B200ATTN_EUNSUPPORTED, "world %d (1, 2, 4 or 8 ranks)", world);
+  if (rank < 0 || rank >= world) return fail(B200ATTN_EINVAL, "rank %d of %d", rank, world);
+  if (numel < 0 || numel % 8) return fail(B200ATTN_EINVAL, "numel %lld must be a non-negative multiple of 8", (long long)numel);
+  if (numel == 0) return 0;
+  if (peer_in == nullptr || peer_flags == nullptr || out == nullptr) return fail(B200ATTN_EINVAL, "null pointer");
+  if (algo == B200ATTN_AR_AUTO) algo = b200attn_peer_allreduce_algo(numel * 2, world, mc_in != nullptr && mc_out != nullptr);
+  if (algo < B200ATTN_AR_ONESHOT || algo > B200ATTN_AR_MULTIMEM) return fail(B200ATTN_EINVAL, "algo %d", algo);
+  if (algo == B200ATTN_AR_TWOSHOT && peer_scratch == nullptr) return fail(B200ATTN_EINVAL, "TWOSHOT needs peer_scratch");
+  if (algo == B200ATTN_AR_MULTIMEM && (mc_in == nullptr || mc_out == nullptr))
+    return fail(B200ATTN_EINVAL, "MULTIMEM needs multicast addresses");
+  PeerArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int r = 0; r < world; ++r) {
+    if (peer_in[r] == nullptr || peer_flags[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_in[r]) % 16) ||
+        (reinterpret_cast<uintptr_t>(peer_flags[r]) % 16))
+      return fail(B200ATTN_EINVAL, "peer_in/peer_flags[%d] null or not 16-byte aligned", r);
+    a.in[r] = peer_in[r];
+    a.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
+    if (algo == B200ATTN_AR_TWOSHOT) {
+      if (peer_scratch[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_scratch[r]) % 16))
+        return fail(B200ATTN_EINVAL, "peer_scratch[%d] null or not 16-byte aligned", r);
+      a.scratch[r] = peer_scratch[r];
+    }
+  }
+  if (reinterpret_cast<uintptr_t>(out) % 16) return fail(B200ATTN_EINVAL, "out must be 16-byte aligned");
+  if (algo != B200ATTN_AR_MULTIMEM && out == peer_in[rank]) return fail(B200ATTN_EINVAL, "out may not alias the input region");
+  a.out = out;
+  a.mc_in = mc_in;
+  a.mc_out = mc_out;
+  a.world = world;
+  a.rank = rank;
+  a.timeout_ns = timeout_ns ? timeout_ns : 10000000000ull;
+  a.soft_timeout = env_flag("B200ATTN_PEER_SOFT_TIMEOUT", false) ? 1 : 0;
+  const int64_t n_vec = numel / 8;
+  const int64_t per_rank = algo == B200ATTN_AR_ONESHOT ? n_vec : n_vec - (world - 1) * (n_vec / world);
+  if (max_blocks <= 0) max_blocks = 64;
+  if (max_blocks > kPeerMaxBlocks) max_blocks = kPeerMaxBlocks;
+  int64_t grid = (per_rank + kPeerThreads - 1) / kPeerThreads;
+  if (grid < 1) grid = 1;
+  if (grid > max_blocks) grid = max_blocks;
+  cudaError_t e = launch_peer_allreduce(a, n_vec, algo, static_cast<int>(grid), static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "peer_allreduce launch");
+}
+
+int b200attn_peer_alloc(size_t bytes, void** ptr, void* handle64) {
+  if (ptr == nullptr || handle64 == nullptr || bytes == 0) return fail(B200ATTN_EINVAL, "null pointer / zero size");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc (peer_alloc)");
+  if ((e = cudaMemset(p, 0, bytes)) != cudaSuccess || (e = cudaDeviceSynchronize()) != cudaSuccess) {
+    cudaFree(p);
+    return cuda_fail(e, "cudaMemset (peer_alloc)");
+  }
+  cudaIpcMemHandle_t h;
+  if ((e = cudaIpcGetMemHandle(&h, p)) != cudaSuccess) {
+    cudaFree(p);
+    return cuda_fail(e, "cudaIpcGetMemHandle");
+  }
+  memcpy(handle64, &h, sizeof(h));
+  *ptr = p;
+  return 0;
+}
+
+int b200attn_peer_open(const void* handle64, void** ptr) {
+  if (ptr == nullptr || handle64 == nullptr) return fail(B200ATTN_EINVAL, "null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaIpcOpenMemHandle");
+  *ptr = p;
+  return 0;
+}
+
+int b200attn_peer_close(void* ptr) {
+  if (ptr == nullptr) return 0;
+  cudaError_t e = cudaIpcCloseMemHandle(ptr);
+  return e == cudaSuccess ? 0 : cuda_fail(e, "cudaIpcCloseMemHandle");
+}
+
+int b200attn_peer_free(void* ptr) {
+  if (ptr == nullptr) return 0;
+  cudaError_t e = cudaFree(ptr);
+  return e == cudaSuccess ? 0 : cuda_fail(e, "cudaFree (peer_free)");
+}
+
 }  // extern "C"

@@ -104,4 +104,23 @@ struct GatherParams {
 };
 cudaError_t launch_gather_kv(const GatherParams& p, int num_sms, cudaStream_t stream);
 
+// ---- peer-memory all-reduce (peer_allreduce.cu) ----
+constexpr int kPeerMaxRanks = 8;
+constexpr int kPeerMaxBlocks = 128;   // flag slots exist for this many blocks per launch
+constexpr int kPeerThreads = 512;
+constexpr size_t kPeerFlagBytes = 8192;  // >= (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 4) * 4, 16-byte multiple
+constexpr int kPeerOneShot = 1, kPeerTwoShot = 2, kPeerMultimem = 3;
+struct PeerArgs {
+  const void* in[kPeerMaxRanks];   // every rank's input region (peer-mapped), index = rank
+  void* scratch[kPeerMaxRanks];    // every rank's scratch region (two-shot)
+  uint32_t* flags[kPeerMaxRanks];  // every rank's flag region (kPeerFlagBytes, zeroed once)
+  void* out;                       // local result
+  const void* mc_in;               // multicast view of the input region (multimem) or null
+  void* mc_out;                    // multicast view of the output region (multimem) or null
+  int32_t world, rank;
+  uint64_t timeout_ns;
+  int32_t soft_timeout;            // B200ATTN_PEER_SOFT_TIMEOUT=1 (tests): record + give up instead of trapping
+};
+cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream);
+
 }  // namespace b200

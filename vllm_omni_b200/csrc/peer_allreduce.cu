@@ -1,0 +1,217 @@
+// Peer-memory all-reduce (sum, bf16) over NVLink 5 / NVSwitch for the o_proj row-parallel sum that
+// follows the attention path (north_star: "the downstream o_proj all-reduce"; the reference reaches it
+// through vLLM's RowParallelLinear -> tensor_model_parallel_all_reduce, vllm/distributed/
+// communication_op.py:12, which on NVLink boxes dispatches to custom_all_reduce.cuh or NCCL).
+//
+// One process per GPU. Every rank owns one peer-mapped allocation (torch symmetric memory or
+// cudaIpc, the host layer's business) carved into [flags | input | scratch]; the kernel gets the
+// per-rank base pointers BY VALUE (<= 8 ranks) and never touches the host. Three schedules:
+//
+//   ONESHOT   every rank loads the 16-byte vector of all ranks and sums it in rank order in fp32.
+//             1 NVLink read per element per peer, 2 flag barriers. Best below ~256 KiB x world.
+//   TWOSHOT   reduce-scatter + all-gather inside ONE launch: rank r sums slice r of every peer into its
+//             scratch, a flag barrier publishes it, then every rank copies the other slices. (world-1)/world
+//             x 2 of the bytes cross NVLink instead of (world-1) x.
+//   MULTIMEM  NVLS: `multimem.ld_reduce` on the multicast address lets the NVSwitch add the replicas
+//             (fp32 accumulate), `multimem.st` broadcasts the sum; each rank handles slice r. Needs a
+//             multicast mapping of the allocation.
+//
+// Flag protocol (CUDA-graph safe, nothing is reset between launches): flag words are monotonically
+// increasing launch-local epochs. Block b of rank r owns epoch counter `epoch[b]` in its own flag
+// region; a barrier = bump the epoch, store it into slot [b][r] of every peer's flag region with
+// st.release.sys, spin with ld.acquire.sys on the `world` slots of the own region until each is >= the
+// epoch (wrap-safe signed compare). A peer can be at most one barrier ahead, so >= is sufficient. Same-index
+// blocks pair up across ranks, and both TWOSHOT phases use the same (block, thread) -> element mapping, so a
+// per-block barrier orders exactly the data that block consumes. The sum order is rank 0..world-1 in fp32
+// with one final bf16 rounding, so ONESHOT/TWOSHOT results are bit-identical on every rank and equal to the
+// sequential fp32 oracle. A spin that exceeds `timeout_ns` records the stuck (block, peer) in the flag region
+// and traps: a dead peer fails the launch loudly instead of hanging the box.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kernels.h"
+
+namespace b200 {
+
+namespace {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// flag region layout (uint32 words): [kPeerMaxBlocks][8] arrival slots | [kPeerMaxBlocks] epochs | 4 error words
+__device__ __forceinline__ uint32_t* slot_of(uint32_t* flags, int block, int from_rank) {
+  return flags + block * kPeerMaxRanks + from_rank;
+}
+__device__ __forceinline__ uint32_t* epoch_of(uint32_t* flags, int block) {
+  return flags + kPeerMaxBlocks * kPeerMaxRanks + block;
+}
+__device__ __forceinline__ uint32_t* error_of(uint32_t* flags) {
+  return flags + kPeerMaxBlocks * kPeerMaxRanks + kPeerMaxBlocks;
+}
+
+// Block-wide barrier with the same-index block of every peer. `fence` = the data written before it
+// must be visible to the peers after it (release/acquire at system scope); false = control only.
+__device__ __forceinline__ void peer_barrier(const PeerArgs& a, uint32_t& epoch, bool fence) {
+  __syncthreads();  // every thread of the block has issued (and, with the fence below, published) its stores
+  epoch += 1;
+  const int t = threadIdx.x;
+  if (t < a.world) {
+    if (fence) __threadfence_system();
+    st_release_sys(slot_of(a.flags[t], blockIdx.x, a.rank), epoch);
+    const uint32_t* mine = slot_of(a.flags[a.rank], blockIdx.x, t);
+    const uint64_t t0 = globaltimer_ns();
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+      if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > a.timeout_ns) {
+        uint32_t* e = error_of(a.flags[a.rank]);
+        e[0] = 1u; e[1] = blockIdx.x; e[2] = static_cast<uint32_t>(t); e[3] = epoch;
+        __threadfence_system();
+        if (!a.soft_timeout) __trap();
+        break;  // test mode: give up on this wait, the host reads the error words
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void acc_bf16x8(float (&acc)[8], const uint4& v) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(h[i]);
+    acc[2 * i] += f.x;
+    acc[2 * i + 1] += f.y;
+  }
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float (&acc)[8]) {
+  uint4 v;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(acc[2 * i], acc[2 * i + 1]);
+  return v;
+}
+
+// sum of vector `idx` over all ranks, rank order, fp32, one rounding
+template <int WORLD>
+__device__ __forceinline__ uint4 reduce_vec(const PeerArgs& a, int64_t idx) {
+  uint4 v[WORLD];
+#pragma unroll
+  for (int r = 0; r < WORLD; ++r) v[r] = ld_peer_v4(reinterpret_cast<const uint4*>(a.in[r]) + idx);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int r = 0; r < WORLD; ++r) acc_bf16x8(acc, v[r]);
+  return pack_bf16x8(acc);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// kernels. n_vec = number of 16-byte vectors (8 bf16 each); the host pads numel to a multiple of 8.
+// ---------------------------------------------------------------------------------------------
+template <int WORLD>
+__global__ void __launch_bounds__(kPeerThreads) peer_allreduce_oneshot_kernel(PeerArgs a, int64_t n_vec) {
+  uint32_t epoch = *epoch_of(a.flags[a.rank], blockIdx.x);
+  peer_barrier(a, epoch, /*fence=*/false);  // every peer's producer kernel has finished (stream order + kernel boundary)
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
+  uint4* out = reinterpret_cast<uint4*>(a.out);
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x; i < n_vec; i += stride)
+    out[i] = reduce_vec<WORLD>(a, i);
+  peer_barrier(a, epoch, /*fence=*/false);  // nobody still reads my input when this launch retires
+  if (threadIdx.x == 0) *epoch_of(a.flags[a.rank], blockIdx.x) = epoch;
+}
+
+template <int WORLD>
+__global__ void __launch_bounds__(kPeerThreads) peer_allreduce_twoshot_kernel(PeerArgs a, int64_t n_vec) {
+  uint32_t epoch = *epoch_of(a.flags[a.rank], blockIdx.x);
+  const int64_t part = n_vec / WORLD;                 // slice r = [r*part, (r+1)*part), the last one takes the tail
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
+  const int64_t my_start = a.rank * part;
+  const int64_t my_len = (a.rank == WORLD - 1) ? n_vec - my_start : part;
+  peer_barrier(a, epoch, false);
+  uint4* scratch = reinterpret_cast<uint4*>(a.scratch[a.rank]);
+  for (int64_t j = tid; j < my_len; j += stride) scratch[j] = reduce_vec<WORLD>(a, my_start + j);
+  peer_barrier(a, epoch, /*fence=*/true);             // reduced slices are published
+  uint4* out = reinterpret_cast<uint4*>(a.out);
+  const int64_t longest = n_vec - (WORLD - 1) * part;
+  for (int64_t j = tid; j < longest; j += stride) {
+#pragma unroll
+    for (int i = 0; i < WORLD; ++i) {
+      const int r = (a.rank + i) % WORLD;             // start with the local slice, spread the peers
+      const int64_t len = (r == WORLD - 1) ? longest : part;
+      if (j < len) out[r * part + j] = ld_peer_v4(reinterpret_cast<const uint4*>(a.scratch[r]) + j);
+    }
+  }
+  peer_barrier(a, epoch, false);                      // scratch and input may be overwritten by the next launch
+  if (threadIdx.x == 0) *epoch_of(a.flags[a.rank], blockIdx.x) = epoch;
+}
+
+// NVLS: the switch reduces. mc_in / mc_out are MULTICAST addresses of the input / output regions;
+// the result lands in every rank's output region (a.out must be this rank's unicast view of it).
+__global__ void __launch_bounds__(kPeerThreads) peer_allreduce_multimem_kernel(PeerArgs a, int64_t n_vec) {
+  uint32_t epoch = *epoch_of(a.flags[a.rank], blockIdx.x);
+  const int64_t part = n_vec / a.world;
+  const int64_t my_start = a.rank * part;
+  const int64_t my_len = (a.rank == a.world - 1) ? n_vec - my_start : part;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
+  peer_barrier(a, epoch, false);
+  const uint4* src = reinterpret_cast<const uint4*>(a.mc_in) + my_start;
+  uint4* dst = reinterpret_cast<uint4*>(a.mc_out) + my_start;
+  for (int64_t j = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x; j < my_len; j += stride) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(src + j)
+                 : "memory");
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + j), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+  }
+  peer_barrier(a, epoch, /*fence=*/true);             // every slice has been broadcast
+  if (threadIdx.x == 0) *epoch_of(a.flags[a.rank], blockIdx.x) = epoch;
+}
+
+template <int WORLD>
+static cudaError_t launch_world(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream) {
+  if (algo == kPeerOneShot)
+    peer_allreduce_oneshot_kernel<WORLD><<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
+  else
+    peer_allreduce_twoshot_kernel<WORLD><<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream) {
+  if (algo == kPeerMultimem) {
+    peer_allreduce_multimem_kernel<<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
+    return cudaGetLastError();
+  }
+  switch (a.world) {
+    case 1: return launch_world<1>(a, n_vec, algo, grid, stream);
+    case 2: return launch_world<2>(a, n_vec, algo, grid, stream);
+    case 4: return launch_world<4>(a, n_vec, algo, grid, stream);
+    case 8: return launch_world<8>(a, n_vec, algo, grid, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace b200
