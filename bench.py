@@ -53,6 +53,8 @@ def parse_args():
                     help="when tp > KV heads: 'replicate' = every rank of a replica group streams the whole KV "
                          "head for its own query heads (the reference rule); 'split' = the group splits the "
                          "batch and exchanges q/out (tp.ReplicaSplit: same results, 1/R of the KV bytes per rank)")
+    ap.add_argument("--replica-exchange", default="peer", choices=["peer", "nccl"],
+                    help="q/out exchange of --replica-mode split: this repo's peer-memory kernels or NCCL all_to_all")
     ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"],
                     help="the o_proj row-parallel sum after every layer (N > 1): 'peer' = this repo's peer-memory "
                          "kernel over NVLink (one-/two-shot, csrc/peer_allreduce.cu), 'nccl' = dist.all_reduce")
@@ -269,18 +271,32 @@ def run_b200(args, wl):
     caches = [ops.split_kv_cache(c) for c in inp.kv_caches]
     out = torch.empty(B, hq, d, dtype=torch.bfloat16, device="cuda")
     # KV-head replication (tp > KV heads): split the batch inside the replica group unless told otherwise
-    rs = None
+    rs, ex, ex_note = None, None, None
     dq, dout, dbt, dsl, dhq = inp.q, out, inp.block_table, inp.seq_lens, hq   # what the decode kernel sees
     kv_bytes = inp.kv_bytes_per_layer
     if sh.kv_replicas > 1 and args.replica_mode == "split":
         import torch.distributed as dist
         from vllm_omni_b200 import tp as tpmod
         groups = [dist.new_group(r) for r in tpmod.ReplicaSplit.groups(world, sh.kv_replicas)]
-        rs = tpmod.ReplicaSplit(sh, groups[rank // sh.kv_replicas])
+        my_group = groups[rank // sh.kv_replicas]
+        ex, ex_note = None, "nccl all_to_all"
+        if args.replica_exchange == "peer":
+            from vllm_omni_b200 import peer
+            try:
+                ex = peer.PeerExchange.create(my_group, B, hq, d)
+                ex.q.copy_(inp.q)                     # the qkv projection would write q here
+                ex_note = f"peer-memory gather/scatter kernels ({ex.mem.transport} mapping)"
+            except Exception as exn:  # noqa: BLE001 - reported in the JSON line
+                ex, ex_note = None, f"nccl all_to_all (peer-memory setup failed: {type(exn).__name__}: {str(exn)[:200]})"
+                log(ex_note)
+        rs = tpmod.ReplicaSplit(sh, my_group, exchange=ex)
         per, b0, b1 = rs.plan(B)
         dhq = rs.group_q_heads
-        q_grp = torch.zeros(per, dhq, d, dtype=torch.bfloat16, device="cuda")
-        out_grp = torch.zeros(per, dhq, d, dtype=torch.bfloat16, device="cuda")
+        if ex is not None:
+            q_grp, out_grp, out = ex.q_grp, ex.out_grp, ex.out
+        else:
+            q_grp = torch.zeros(per, dhq, d, dtype=torch.bfloat16, device="cuda")
+            out_grp = torch.zeros(per, dhq, d, dtype=torch.bfloat16, device="cuda")
         dq, dout, dbt, dsl = q_grp[:b1 - b0], out_grp[:b1 - b0], inp.block_table[b0:b1], inp.seq_lens[b0:b1]
         kv_bytes = int(inp.seq_lens[b0:b1].sum().item()) * 2 * hkv * d * (1 if wl.fp8 else 2)
     # schedule: stream-K (no split count) unless a split count or a fixed-split variant is asked for
@@ -302,9 +318,9 @@ def run_b200(args, wl):
                 hidden_out = torch.empty(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")
                 algo = peer.ALGO_NAMES[peer.choose_algo(2 * hidden.numel(), world, ar.has_multicast)]
                 ar_note = f"peer-memory {algo} kernel ({ar.transport} mapping, multicast={ar.has_multicast})"
-            except Exception as ex:  # noqa: BLE001 - say so in the JSON line, never silently
+            except Exception as exc:  # noqa: BLE001 - say so in the JSON line, never silently
                 ar = None
-                ar_note = f"nccl all_reduce (peer-memory setup failed: {type(ex).__name__}: {str(ex)[:200]})"
+                ar_note = f"nccl all_reduce (peer-memory setup failed: {type(exc).__name__}: {str(exc)[:200]})"
                 log(ar_note)
 
     def o_proj_sum():
@@ -319,7 +335,7 @@ def run_b200(args, wl):
             ops.reshape_and_cache(inp.new_k, inp.new_v, kc, vc, inp.slot_mapping, wl.kv_cache_dtype,
                                   inp.k_scale, inp.v_scale)
             if rs is not None:
-                rs.gather_q(inp.q, out=q_grp)
+                rs.gather_q(ex.q if ex is not None else inp.q, out=q_grp)
             ops.paged_decode(dq, kc, vc, dbt, dsl, inp.max_seq_len,
                              inp.softmax_scale, out=dout, kv_cache_dtype=wl.kv_cache_dtype,
                              k_scale=inp.k_scale, v_scale=inp.v_scale, num_splits=splits,
@@ -330,7 +346,8 @@ def run_b200(args, wl):
                 o_proj_sum()
 
     # our kernels only (not NCCL / copies): cache write + decode (+ reduce) (+ peer all-reduce)
-    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0) + (1 if ar is not None else 0))
+    launches_per_step = L * (2 + (1 if (splits > 1 or streamk) else 0) + (1 if ar is not None else 0)
+                             + (2 if ex is not None else 0))
 
     def capture(fn):
         """CUDA-graph the launches of `fn` (how vLLM replays decode steps); None if capture fails."""
@@ -457,7 +474,7 @@ def run_b200(args, wl):
                                                "replica_mode": (args.replica_mode if sh.kv_replicas > 1 else None),
                                                "decode_q_heads": dhq, "decode_batch": int(dq.shape[0]),
                                                "kv_bytes_per_layer": kv_bytes},
-            "collective": ar_note,
+            "collective": ar_note, "replica_exchange": ex_note,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

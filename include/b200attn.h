@@ -307,6 +307,27 @@ B200ATTN_API int b200attn_peer_allreduce(
     uint64_t timeout_ns, void* stream);
 
 /*
+ * Row exchange inside a KV-head replica group (tp > KV heads, vllm_omni_b200.tp.ReplicaSplit) through
+ * peer memory — replaces the two NCCL all_to_all calls around the decode. The reference rule
+ * (qwen2_old.py:98-106) replicates a KV head on R ranks; here each of them serves ALL query heads of the
+ * group for 1/R of the sequences, so q rows are pulled from the peers before the decode and output rows
+ * are pushed back after it.
+ *   peer_rows[g]  rank g's [batch, row_bytes] buffer (its query heads of every sequence: q, or out)
+ *   local_rows    [rows_per_rank, group_size, row_bytes] staging the decode kernel reads / writes
+ *   scatter = 0   gather : local[i][g] = peer_rows[g][first_row + i]  (one flag barrier, then pulls)
+ *   scatter = 1   scatter: peer_rows[g][first_row + i] = local[i][g]  (pushes, then one fenced barrier:
+ *                 when the launch retires on a rank, every peer's rows for it have landed)
+ * i < num_rows <= rows_per_rank; rows_per_rank must be the same on every rank of the group.
+ * gather(l) and scatter(l) must be issued pairwise by every rank of the group (the hazards between
+ * layers are ordered by these two barriers). Flags: a B200ATTN_PEER_FLAG_BYTES region per rank that
+ * no other collective uses.
+ */
+B200ATTN_API int b200attn_peer_exchange(
+    void* const* peer_rows, void* const* peer_flags, void* local_rows,
+    int32_t group_size, int32_t group_rank, int32_t first_row, int32_t num_rows, int32_t rows_per_rank,
+    int64_t row_bytes, int32_t scatter, uint64_t timeout_ns, void* stream);
+
+/*
  * Peer-mappable allocations through CUDA IPC for hosts without torch symmetric memory:
  * alloc = cudaMalloc + zero fill + cudaIpcGetMemHandle (64-byte handle to ship to the peers by any
  * host channel), open = cudaIpcOpenMemHandle with lazy peer access, close / free undo them.

@@ -11,7 +11,7 @@ vLLM):
 Each file holds the complete inputs (q, paged cache as written by vLLM's own cache-write kernel, block
 table, seq_lens, scale) and the outputs of every stock kernel that loaded, so the CPU suite can pin the
 oracle (`oracle.ref_paged_decode`, the C oracle) against them without a GPU:
-  out_fa2/out_fa3/out_fa4   vllm.vllm_flash_attn.flash_attn_varlen_func (flash_attn.py:758-819 call shape)
+  out_fa2                   vllm.vllm_flash_attn.flash_attn_varlen_func (flash_attn.py:758-819 call shape)
   out_trtllm                flashinfer trtllm_batch_decode_with_kv_cache (flashinfer.py:1694-1822)
   cache_vllm                the cache after vLLM's reshape_and_cache_flash (vllm/_custom_ops.py:2591-2610)
 bf16 arrays are stored as their int16 bit patterns.
@@ -58,7 +58,7 @@ def main(out_dir: Path):
         cu_q = torch.arange(B + 1, dtype=torch.int32, device="cuda")
         try:
             from vllm.vllm_flash_attn import flash_attn_varlen_func
-            for ver in (2, 3, 4):
+            for ver in (2,):   # v3 is the Hopper build (fatal 'no kernel image' on sm_100), v4 is not shipped for decode
                 try:
                     out = torch.empty_like(q)
                     flash_attn_varlen_func(q, kv[0], kv[1], max_seqlen_q=1, cu_seqlens_q=cu_q,

@@ -93,3 +93,32 @@ def test_allreduce_rejects_bad_arguments(lib):
         ar.all_reduce(ar.input((16,)), out=ar.input((16,)))                      # out aliases the input region
     with pytest.raises(peer.PeerSetupError):
         ar.all_reduce(ar.input((16,)), algo=_lib.AR_MULTIMEM)
+
+
+@pytest.mark.parametrize("R,batch", [(2, 64), (2, 7), (4, 10), (8, 33)])
+def test_peer_exchange_matches_replica_split_indexing(lib, R, batch):
+    """gather_q / scatter_out through peer memory == the all_to_all semantics of tp.ReplicaSplit
+    (q_grp[i, g*hq + h] = q_g[b0 + i, h]; out_g[b0 + i, h] = out_grp[i, g*hq + h]), bit for bit, ragged tail
+    (batch not divisible by R) included, twice in a row (epochs carry over)."""
+    hq, d = 4, 128
+    g = torch.Generator().manual_seed(R * 100 + batch)
+    qs = [torch.randn(batch, hq, d, generator=g).to(torch.bfloat16) for _ in range(R)]
+    exs = peer.PeerExchange.local_ranks(R, batch, hq, d, timeout_s=5.0)
+    streams = [torch.cuda.Stream() for _ in exs]
+    for ex, q in zip(exs, qs):
+        ex.q.copy_(q.cuda())
+    torch.cuda.synchronize()
+    for it in range(2):
+        for ex, s in zip(exs, streams):
+            with torch.cuda.stream(s):
+                ex.gather_q()
+                ex.out_grp.copy_(ex.q_grp.float().mul(2 + it).to(torch.bfloat16))   # stand-in for the decode
+                ex.scatter_out()
+        torch.cuda.synchronize()
+        for i, ex in enumerate(exs):
+            n = ex.b1 - ex.b0
+            want = torch.stack([q[ex.b0:ex.b1] for q in qs], dim=1).reshape(n, R * hq, d)
+            assert torch.equal(ex.q_grp[:n].cpu(), want), f"gather differs on rank {i}"
+            assert torch.equal(ex.out.cpu(), qs[i].float().mul(2 + it).to(torch.bfloat16)), f"scatter differs on rank {i}"
+            off = (128 * 8 + 128) * 4
+            assert ex.mem.local[off: off + 16].view(torch.int32).tolist() == [0, 0, 0, 0]

@@ -103,6 +103,10 @@ SIGNATURES: dict[str, tuple] = {
         _vp, _vp, _vp,                                    # out, mc_in, mc_out
         _i64, _i32, _i32, _i32, _i32,                     # numel, world, rank, algo, max_blocks
         C.c_uint64, _vp]),                                # timeout_ns, stream
+    "b200attn_peer_exchange": (C.c_int, [
+        C.POINTER(_vp), C.POINTER(_vp), _vp,              # peer_rows, peer_flags (host arrays), local_rows
+        _i32, _i32, _i32, _i32, _i32,                     # group_size, group_rank, first_row, num_rows, rows_per_rank
+        _i64, _i32, C.c_uint64, _vp]),                    # row_bytes, scatter, timeout_ns, stream
     "b200attn_peer_alloc": (C.c_int, [_sz, C.POINTER(_vp), C.c_char_p]),
     "b200attn_peer_open": (C.c_int, [C.c_char_p, C.POINTER(_vp)]),
     "b200attn_peer_close": (C.c_int, [_vp]),

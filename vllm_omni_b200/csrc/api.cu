@@ -859,7 +859,7 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
         (reinterpret_cast<uintptr_t>(peer_flags[r]) % 16))
       return fail(B200ATTN_EINVAL, "peer_in/peer_flags[%d] null or not 16-byte aligned", r);
     a.in[r] = peer_in[r];
-    a.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
+    a.ctl.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
     if (algo == B200ATTN_AR_TWOSHOT) {
       if (peer_scratch[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_scratch[r]) % 16))
         return fail(B200ATTN_EINVAL, "peer_scratch[%d] null or not 16-byte aligned", r);
@@ -871,10 +871,10 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
   a.out = out;
   a.mc_in = mc_in;
   a.mc_out = mc_out;
-  a.world = world;
-  a.rank = rank;
-  a.timeout_ns = timeout_ns ? timeout_ns : 10000000000ull;
-  a.soft_timeout = env_flag("B200ATTN_PEER_SOFT_TIMEOUT", false) ? 1 : 0;
+  a.ctl.world = world;
+  a.ctl.rank = rank;
+  a.ctl.timeout_ns = timeout_ns ? timeout_ns : 10000000000ull;
+  a.ctl.soft_timeout = env_flag("B200ATTN_PEER_SOFT_TIMEOUT", false) ? 1 : 0;
   const int64_t n_vec = numel / 8;
   const int64_t per_rank = algo == B200ATTN_AR_ONESHOT ? n_vec : n_vec - (world - 1) * (n_vec / world);
   if (max_blocks <= 0) max_blocks = 64;
@@ -884,6 +884,41 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
   if (grid > max_blocks) grid = max_blocks;
   cudaError_t e = launch_peer_allreduce(a, n_vec, algo, static_cast<int>(grid), static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "peer_allreduce launch");
+}
+
+int b200attn_peer_exchange(void* const* peer_rows, void* const* peer_flags, void* local_rows, int32_t group_size,
+                           int32_t group_rank, int32_t first_row, int32_t num_rows, int32_t rows_per_rank,
+                           int64_t row_bytes, int32_t scatter, uint64_t timeout_ns, void* stream) {
+  if (group_size < 1 || group_size > kPeerMaxRanks) return fail(B200ATTN_EUNSUPPORTED, "group of %d ranks (1..8)", group_size);
+  if (group_rank < 0 || group_rank >= group_size) return fail(B200ATTN_EINVAL, "rank %d of %d", group_rank, group_size);
+  if (peer_rows == nullptr || peer_flags == nullptr || local_rows == nullptr) return fail(B200ATTN_EINVAL, "null pointer");
+  if (row_bytes <= 0 || row_bytes % 16 || row_bytes / 16 > 0x7fffffff) return fail(B200ATTN_EINVAL, "row_bytes must be a positive multiple of 16");
+  if (first_row < 0 || num_rows < 0 || rows_per_rank < num_rows) return fail(B200ATTN_EINVAL, "bad row range");
+  if (reinterpret_cast<uintptr_t>(local_rows) % 16) return fail(B200ATTN_EINVAL, "local_rows must be 16-byte aligned");
+  PeerExchangeArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int r = 0; r < group_size; ++r) {
+    if (peer_rows[r] == nullptr || peer_flags[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_rows[r]) % 16) ||
+        (reinterpret_cast<uintptr_t>(peer_flags[r]) % 16))
+      return fail(B200ATTN_EINVAL, "peer_rows/peer_flags[%d] null or not 16-byte aligned", r);
+    a.peer_rows[r] = peer_rows[r];
+    a.ctl.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
+  }
+  a.ctl.world = group_size;
+  a.ctl.rank = group_rank;
+  a.ctl.timeout_ns = timeout_ns ? timeout_ns : 10000000000ull;
+  a.ctl.soft_timeout = env_flag("B200ATTN_PEER_SOFT_TIMEOUT", false) ? 1 : 0;
+  a.local_rows = local_rows;
+  a.b0 = first_row;
+  a.nrows = num_rows;
+  a.row_vec = static_cast<int32_t>(row_bytes / 16);
+  // every rank of the group must launch the same grid (the barrier pairs same-index blocks): size it from
+  // rows_per_rank, which is the same everywhere, not from this rank's possibly shorter range
+  int64_t grid = (static_cast<int64_t>(rows_per_rank) * group_size * a.row_vec + kPeerThreads - 1) / kPeerThreads;
+  if (grid < 1) grid = 1;
+  if (grid > 64) grid = 64;
+  cudaError_t e = launch_peer_exchange(a, scatter != 0, static_cast<int>(grid), static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "peer_exchange launch");
 }
 
 int b200attn_peer_alloc(size_t bytes, void** ptr, void* handle64) {

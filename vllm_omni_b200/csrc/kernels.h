@@ -110,17 +110,32 @@ constexpr int kPeerMaxBlocks = 128;   // flag slots exist for this many blocks p
 constexpr int kPeerThreads = 512;
 constexpr size_t kPeerFlagBytes = 8192;  // >= (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 4) * 4, 16-byte multiple
 constexpr int kPeerOneShot = 1, kPeerTwoShot = 2, kPeerMultimem = 3;
-struct PeerArgs {
-  const void* in[kPeerMaxRanks];   // every rank's input region (peer-mapped), index = rank
-  void* scratch[kPeerMaxRanks];    // every rank's scratch region (two-shot)
-  uint32_t* flags[kPeerMaxRanks];  // every rank's flag region (kPeerFlagBytes, zeroed once)
-  void* out;                       // local result
-  const void* mc_in;               // multicast view of the input region (multimem) or null
-  void* mc_out;                    // multicast view of the output region (multimem) or null
+struct PeerCtl {                   // who takes part in a flag barrier
+  uint32_t* flags[kPeerMaxRanks];  // every rank's flag region (kPeerFlagBytes, zeroed once), index = rank
   int32_t world, rank;
   uint64_t timeout_ns;
   int32_t soft_timeout;            // B200ATTN_PEER_SOFT_TIMEOUT=1 (tests): record + give up instead of trapping
 };
+struct PeerArgs {
+  PeerCtl ctl;
+  const void* in[kPeerMaxRanks];   // every rank's input region (peer-mapped), index = rank
+  void* scratch[kPeerMaxRanks];    // every rank's scratch region (two-shot)
+  void* out;                       // local result
+  const void* mc_in;               // multicast view of the input region (multimem) or null
+  void* mc_out;                    // multicast view of the output region (multimem) or null
+};
+// Row exchange inside a KV-head replica group (tp.ReplicaSplit): rank g of the group owns rows
+// [B, row_bytes] (its query heads of every sequence); rank i serves sequences [b0_i, b0_i + per).
+//   gather : local[(s - b0) * R + g] = peer_g[s]   for s in my sequence range   (pull, barrier first)
+//   scatter: peer_g[s] = local[(s - b0) * R + g]                                  (push, barrier last)
+struct PeerExchangeArgs {
+  PeerCtl ctl;
+  void* peer_rows[kPeerMaxRanks];  // every group rank's [B, row_bytes] region (peer-mapped)
+  void* local_rows;                // [per, R, row_bytes] local staging (q_grp / out_grp)
+  int32_t b0, nrows;               // my sequence range [b0, b0 + nrows)
+  int32_t row_vec;                 // row_bytes / 16
+};
+cudaError_t launch_peer_exchange(const PeerExchangeArgs& a, bool scatter, int grid, cudaStream_t stream);
 cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream);
 
 }  // namespace b200

@@ -71,7 +71,7 @@ __device__ __forceinline__ uint32_t* error_of(uint32_t* flags) {
 
 // Block-wide barrier with the same-index block of every peer. `fence` = the data written before it
 // must be visible to the peers after it (release/acquire at system scope); false = control only.
-__device__ __forceinline__ void peer_barrier(const PeerArgs& a, uint32_t& epoch, bool fence) {
+__device__ __forceinline__ void peer_barrier(const PeerCtl& a, uint32_t& epoch, bool fence) {
   __syncthreads();  // every thread of the block has issued (and, with the fence below, published) its stores
   epoch += 1;
   const int t = threadIdx.x;
@@ -130,51 +130,51 @@ __device__ __forceinline__ uint4 reduce_vec(const PeerArgs& a, int64_t idx) {
 // ---------------------------------------------------------------------------------------------
 template <int WORLD>
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_oneshot_kernel(PeerArgs a, int64_t n_vec) {
-  uint32_t epoch = *epoch_of(a.flags[a.rank], blockIdx.x);
-  peer_barrier(a, epoch, /*fence=*/false);  // every peer's producer kernel has finished (stream order + kernel boundary)
+  uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
+  peer_barrier(a.ctl, epoch, /*fence=*/false);  // every peer's producer kernel has finished (stream order + kernel boundary)
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
   uint4* out = reinterpret_cast<uint4*>(a.out);
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x; i < n_vec; i += stride)
     out[i] = reduce_vec<WORLD>(a, i);
-  peer_barrier(a, epoch, /*fence=*/false);  // nobody still reads my input when this launch retires
-  if (threadIdx.x == 0) *epoch_of(a.flags[a.rank], blockIdx.x) = epoch;
+  peer_barrier(a.ctl, epoch, /*fence=*/false);  // nobody still reads my input when this launch retires
+  if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
 }
 
 template <int WORLD>
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_twoshot_kernel(PeerArgs a, int64_t n_vec) {
-  uint32_t epoch = *epoch_of(a.flags[a.rank], blockIdx.x);
+  uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
   const int64_t part = n_vec / WORLD;                 // slice r = [r*part, (r+1)*part), the last one takes the tail
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
-  const int64_t my_start = a.rank * part;
-  const int64_t my_len = (a.rank == WORLD - 1) ? n_vec - my_start : part;
-  peer_barrier(a, epoch, false);
-  uint4* scratch = reinterpret_cast<uint4*>(a.scratch[a.rank]);
+  const int64_t my_start = a.ctl.rank * part;
+  const int64_t my_len = (a.ctl.rank == WORLD - 1) ? n_vec - my_start : part;
+  peer_barrier(a.ctl, epoch, false);
+  uint4* scratch = reinterpret_cast<uint4*>(a.scratch[a.ctl.rank]);
   for (int64_t j = tid; j < my_len; j += stride) scratch[j] = reduce_vec<WORLD>(a, my_start + j);
-  peer_barrier(a, epoch, /*fence=*/true);             // reduced slices are published
+  peer_barrier(a.ctl, epoch, /*fence=*/true);             // reduced slices are published
   uint4* out = reinterpret_cast<uint4*>(a.out);
   const int64_t longest = n_vec - (WORLD - 1) * part;
   for (int64_t j = tid; j < longest; j += stride) {
 #pragma unroll
     for (int i = 0; i < WORLD; ++i) {
-      const int r = (a.rank + i) % WORLD;             // start with the local slice, spread the peers
+      const int r = (a.ctl.rank + i) % WORLD;             // start with the local slice, spread the peers
       const int64_t len = (r == WORLD - 1) ? longest : part;
       if (j < len) out[r * part + j] = ld_peer_v4(reinterpret_cast<const uint4*>(a.scratch[r]) + j);
     }
   }
-  peer_barrier(a, epoch, false);                      // scratch and input may be overwritten by the next launch
-  if (threadIdx.x == 0) *epoch_of(a.flags[a.rank], blockIdx.x) = epoch;
+  peer_barrier(a.ctl, epoch, false);                      // scratch and input may be overwritten by the next launch
+  if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
 }
 
 // NVLS: the switch reduces. mc_in / mc_out are MULTICAST addresses of the input / output regions;
 // the result lands in every rank's output region (a.out must be this rank's unicast view of it).
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_multimem_kernel(PeerArgs a, int64_t n_vec) {
-  uint32_t epoch = *epoch_of(a.flags[a.rank], blockIdx.x);
-  const int64_t part = n_vec / a.world;
-  const int64_t my_start = a.rank * part;
-  const int64_t my_len = (a.rank == a.world - 1) ? n_vec - my_start : part;
+  uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
+  const int64_t part = n_vec / a.ctl.world;
+  const int64_t my_start = a.ctl.rank * part;
+  const int64_t my_len = (a.ctl.rank == a.ctl.world - 1) ? n_vec - my_start : part;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
-  peer_barrier(a, epoch, false);
+  peer_barrier(a.ctl, epoch, false);
   const uint4* src = reinterpret_cast<const uint4*>(a.mc_in) + my_start;
   uint4* dst = reinterpret_cast<uint4*>(a.mc_out) + my_start;
   for (int64_t j = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x; j < my_len; j += stride) {
@@ -187,8 +187,8 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_multimem_kernel(P
                  "r"(v.z), "r"(v.w)
                  : "memory");
   }
-  peer_barrier(a, epoch, /*fence=*/true);             // every slice has been broadcast
-  if (threadIdx.x == 0) *epoch_of(a.flags[a.rank], blockIdx.x) = epoch;
+  peer_barrier(a.ctl, epoch, /*fence=*/true);             // every slice has been broadcast
+  if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
 }
 
 template <int WORLD>
@@ -205,13 +205,54 @@ cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, in
     peer_allreduce_multimem_kernel<<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
     return cudaGetLastError();
   }
-  switch (a.world) {
+  switch (a.ctl.world) {
     case 1: return launch_world<1>(a, n_vec, algo, grid, stream);
     case 2: return launch_world<2>(a, n_vec, algo, grid, stream);
     case 4: return launch_world<4>(a, n_vec, algo, grid, stream);
     case 8: return launch_world<8>(a, n_vec, algo, grid, stream);
     default: return cudaErrorInvalidValue;
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row exchange inside a KV-head replica group (see PeerExchangeArgs in kernels.h): the q rows are
+// PULLED from the peers after one flag barrier (their producers have finished), the output rows are
+// PUSHED into the peers' buffers and published by one fenced barrier. One 16-byte vector per thread
+// and step; vector v of the local staging [nrows][R][row_vec] maps to (i, g, c).
+// ---------------------------------------------------------------------------------------------
+template <bool SCATTER>
+__global__ void __launch_bounds__(kPeerThreads) peer_exchange_kernel(PeerExchangeArgs a) {
+  uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
+  if (!SCATTER) peer_barrier(a.ctl, epoch, /*fence=*/false);
+  const int R = a.ctl.world;
+  const int64_t total = static_cast<int64_t>(a.nrows) * R * a.row_vec;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
+  uint4* local = reinterpret_cast<uint4*>(a.local_rows);
+  for (int64_t v = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x; v < total; v += stride) {
+    const int c = static_cast<int>(v % a.row_vec);
+    const int64_t ig = v / a.row_vec;
+    const int g = static_cast<int>(ig % R);
+    const int64_t i = ig / R;
+    uint4* remote = reinterpret_cast<uint4*>(a.peer_rows[g]) + (a.b0 + i) * a.row_vec + c;
+    if (SCATTER) {
+      const uint4 x = local[v];
+      asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(remote), "r"(x.x), "r"(x.y), "r"(x.z),
+                   "r"(x.w)
+                   : "memory");
+    } else {
+      local[v] = ld_peer_v4(remote);
+    }
+  }
+  if (SCATTER) peer_barrier(a.ctl, epoch, /*fence=*/true);  // my rows have landed in every peer's buffer
+  if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
+}
+
+cudaError_t launch_peer_exchange(const PeerExchangeArgs& a, bool scatter, int grid, cudaStream_t stream) {
+  if (scatter)
+    peer_exchange_kernel<true><<<grid, kPeerThreads, 0, stream>>>(a);
+  else
+    peer_exchange_kernel<false><<<grid, kPeerThreads, 0, stream>>>(a);
+  return cudaGetLastError();
 }
 
 }  // namespace b200

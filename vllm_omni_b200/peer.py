@@ -57,6 +57,86 @@ def _ptr_array(ptrs):
     return (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
 
 
+class PeerMemory:
+    """One peer-mapped allocation per rank of `group`, zero-filled: `local` is this rank's bytes as a
+    uint8 tensor, `base_ptrs[r]` is rank r's allocation as mapped into this process, `multicast_ptr` the
+    multicast mapping of all of them (0 if the fabric has none)."""
+
+    def __init__(self, world, rank, base_ptrs, local, multicast_ptr=0, transport="local", keepalive=None):
+        self.world, self.rank = world, rank
+        self.base_ptrs = [int(p) for p in base_ptrs]
+        self.local = local
+        self.multicast_ptr = int(multicast_ptr or 0)
+        self.transport = transport
+        self._keep = keepalive
+
+    @classmethod
+    def create(cls, group=None, nbytes: int = 0, device=None, transport: str = "auto"):
+        """Collective over `group` (default: WORLD). transport: 'symm' (torch symmetric memory; gives a
+        multicast mapping where the fabric has one), 'ipc' (cudaMalloc + cudaIpc handles) or 'auto'
+        (symm, then ipc). Raises PeerSetupError on every rank if any rank could not map its peers."""
+        import torch.distributed as dist
+        group = group if group is not None else dist.group.WORLD
+        device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        errors = []
+        for tr in (("symm", "ipc") if transport == "auto" else (transport,)):
+            try:
+                mem = (cls._create_symm if tr == "symm" else cls._create_ipc)(group, nbytes, device)
+            except Exception as ex:  # noqa: BLE001 - every rank must take the same branch: vote below
+                mem, err = None, f"{tr}: {type(ex).__name__}: {ex}"
+            else:
+                err = None
+            votes = [None] * dist.get_world_size(group)
+            dist.all_gather_object(votes, err, group=group)
+            if all(v is None for v in votes):
+                torch.cuda.synchronize(device)
+                dist.barrier(group)          # every rank's allocation is zeroed before anyone launches
+                return mem
+            errors.append("; ".join(sorted({v for v in votes if v})))
+        raise PeerSetupError(" | ".join(errors))
+
+    @classmethod
+    def _create_symm(cls, group, nbytes, device):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        t = symm.empty(nbytes, dtype=torch.uint8, device=device)
+        hdl = symm.rendezvous(t, group)
+        t.zero_()
+        mc = int(hdl.multicast_ptr or 0)     # 0 where the fabric / driver offers no multicast object
+        return cls(dist.get_world_size(group), dist.get_rank(group), list(hdl.buffer_ptrs), t,
+                   multicast_ptr=mc, transport="symm", keepalive=(t, hdl))
+
+    @classmethod
+    def _create_ipc(cls, group, nbytes, device):
+        import torch.distributed as dist
+        lib = _lib.load()
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        with torch.cuda.device(device):
+            ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+            _lib.check("b200attn_peer_alloc", lib.b200attn_peer_alloc(nbytes, C.byref(ptr), handle))
+            handles = [None] * world
+            dist.all_gather_object(handles, handle.raw, group=group)
+            ptrs = []
+            for r, h in enumerate(handles):
+                if r == rank:
+                    ptrs.append(ptr.value)
+                    continue
+                p = C.c_void_p()
+                _lib.check("b200attn_peer_open", lib.b200attn_peer_open(C.create_string_buffer(h, 64), C.byref(p)))
+                ptrs.append(p.value)
+            local = torch.as_tensor(_RawCuda(ptr.value, nbytes), device=device)
+        return cls(world, rank, ptrs, local, transport="ipc", keepalive=("ipc", ptr.value))
+
+    @classmethod
+    def local_ranks(cls, world: int, nbytes: int, device="cuda"):
+        """`world` 'ranks' whose peers are plain allocations on ONE device — the protocol test bed: launch
+        each rank's kernels on its own stream and they synchronise with each other exactly as ranks on
+        different GPUs would (needs all the grids co-resident, which these small grids are)."""
+        bufs = [torch.zeros(nbytes, dtype=torch.uint8, device=device) for _ in range(world)]
+        ptrs = [b.data_ptr() for b in bufs]
+        return [cls(world, r, ptrs, bufs[r], transport="local", keepalive=bufs) for r in range(world)]
+
+
 class PeerAllReduce:
     """bf16 sum over the ranks of `group` through peer memory.
 
@@ -69,99 +149,34 @@ class PeerAllReduce:
     rank: fp32 sum in rank order, one rounding to bf16.
     """
 
-    def __init__(self, world: int, rank: int, base_ptrs, max_numel: int, local: torch.Tensor,
-                 multicast_ptr: int = 0, transport: str = "local", keepalive=None,
-                 timeout_s: float = 10.0, max_blocks: int = 0):
-        if world not in (1, 2, 4, 8):
-            raise ValueError(f"world {world}: 1, 2, 4 or 8 ranks")
+    def __init__(self, mem: PeerMemory, max_numel: int, timeout_s: float = 10.0, max_blocks: int = 0):
+        if mem.world not in (1, 2, 4, 8):
+            raise ValueError(f"world {mem.world}: 1, 2, 4 or 8 ranks")
         self.lib = _lib.load()
-        self.world, self.rank, self.max_numel = world, rank, max_numel
+        self.mem = mem
+        self.world, self.rank, self.max_numel = mem.world, mem.rank, max_numel
         self.off_in, self.off_scr, self.cap, self.total = region_layout(max_numel)
-        if local.numel() * local.element_size() < self.total:
+        if mem.local.numel() < self.total:
             raise ValueError("allocation smaller than region_layout(max_numel)")
-        self.local = local.view(torch.uint8) if local.dtype != torch.uint8 else local   # this rank's allocation
-        self.base_ptrs = [int(p) for p in base_ptrs]
-        self.multicast_ptr = int(multicast_ptr or 0)
-        self.transport = transport
+        self.local = mem.local
+        self.base_ptrs = mem.base_ptrs
+        self.multicast_ptr = mem.multicast_ptr
+        self.transport = mem.transport
         self.timeout_ns = int(timeout_s * 1e9)
         self.max_blocks = max_blocks
-        self._keep = keepalive
         self._in = _ptr_array([p + self.off_in for p in self.base_ptrs])
         self._scr = _ptr_array([p + self.off_scr for p in self.base_ptrs])
         self._flags = _ptr_array(self.base_ptrs)
         self._out_default = None
         self.last_algo = None
 
-    # ---- construction -------------------------------------------------------------------------
     @classmethod
     def create(cls, group=None, max_numel: int = 0, device=None, transport: str = "auto", **kw):
-        """Collective over `group` (default: WORLD). transport: 'symm' (torch symmetric memory; gives a
-        multicast mapping where the fabric has one), 'ipc' (cudaMalloc + cudaIpc handles) or 'auto'
-        (symm, then ipc)."""
-        import torch.distributed as dist
-        group = group if group is not None else dist.group.WORLD
-        device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
-        errors = []
-        for tr in (("symm", "ipc") if transport == "auto" else (transport,)):
-            try:
-                ar = (cls._create_symm if tr == "symm" else cls._create_ipc)(group, max_numel, device, **kw)
-            except Exception as ex:  # noqa: BLE001 - every rank must take the same branch: vote below
-                ar, err = None, f"{tr}: {type(ex).__name__}: {ex}"
-            else:
-                err = None
-            votes = [None] * dist.get_world_size(group)
-            dist.all_gather_object(votes, err, group=group)
-            if all(v is None for v in votes):
-                torch.cuda.synchronize(device)
-                dist.barrier(group)          # every rank's flag region is zeroed before anyone launches
-                return ar
-            errors.append("; ".join(sorted({v for v in votes if v})))
-        raise PeerSetupError(" | ".join(errors))
-
-    @classmethod
-    def _create_symm(cls, group, max_numel, device, **kw):
-        import torch.distributed as dist
-        import torch.distributed._symmetric_memory as symm
-        total = region_layout(max_numel)[3]
-        t = symm.empty(total, dtype=torch.uint8, device=device)
-        hdl = symm.rendezvous(t, group)
-        t.zero_()
-        mc = int(hdl.multicast_ptr or 0)     # 0 where the fabric / driver offers no multicast object
-        return cls(dist.get_world_size(group), dist.get_rank(group), list(hdl.buffer_ptrs), max_numel, t,
-                   multicast_ptr=mc, transport="symm", keepalive=(t, hdl), **kw)
-
-    @classmethod
-    def _create_ipc(cls, group, max_numel, device, **kw):
-        import torch.distributed as dist
-        lib = _lib.load()
-        total = region_layout(max_numel)[3]
-        world, rank = dist.get_world_size(group), dist.get_rank(group)
-        with torch.cuda.device(device):
-            ptr, handle = C.c_void_p(), C.create_string_buffer(64)
-            _lib.check("b200attn_peer_alloc", lib.b200attn_peer_alloc(total, C.byref(ptr), handle))
-            handles = [None] * world
-            dist.all_gather_object(handles, handle.raw, group=group)
-            ptrs = []
-            for r, h in enumerate(handles):
-                if r == rank:
-                    ptrs.append(ptr.value)
-                    continue
-                p = C.c_void_p()
-                _lib.check("b200attn_peer_open", lib.b200attn_peer_open(C.create_string_buffer(h, 64), C.byref(p)))
-                ptrs.append(p.value)
-            local = torch.as_tensor(_RawCuda(ptr.value, total), device=device)
-        return cls(world, rank, ptrs, max_numel, local, transport="ipc", keepalive=("ipc", ptr.value), **kw)
+        return cls(PeerMemory.create(group, region_layout(max_numel)[3], device, transport), max_numel, **kw)
 
     @classmethod
     def local_ranks(cls, world: int, max_numel: int, device="cuda", **kw):
-        """`world` instances whose 'peers' are plain allocations on ONE device — the protocol test bed:
-        launch each on its own stream and the kernels synchronise with each other exactly as ranks on
-        different GPUs would (needs all `world` grids co-resident, which small grids are)."""
-        total = region_layout(max_numel)[3]
-        bufs = [torch.zeros(total, dtype=torch.uint8, device=device) for _ in range(world)]
-        ptrs = [b.data_ptr() for b in bufs]
-        return [cls(world, r, ptrs, max_numel, bufs[r], transport="local", keepalive=bufs, **kw)
-                for r in range(world)]
+        return [cls(m, max_numel, **kw) for m in PeerMemory.local_ranks(world, region_layout(max_numel)[3], device)]
 
     # ---- use ----------------------------------------------------------------------------------
     @property
@@ -220,3 +235,65 @@ class PeerAllReduce:
             out.copy_(res)
             return out
         return res
+
+
+class PeerExchange:
+    """q / output row exchange inside a KV-head replica group through peer memory (the device side of
+    `tp.ReplicaSplit`, replacing its two NCCL all_to_all calls): `b200attn_peer_exchange`.
+
+        ex = PeerExchange.create(group, batch, hq_rank, d)
+        ex.q[...]  = this rank's query heads [batch, hq_rank, d]   (the producer writes here)
+        ex.gather_q()        -> ex.q_grp   [per, R * hq_rank, d]: all heads of the group, my sequences
+        decode(ex.q_grp[:n]) -> ex.out_grp [per, R * hq_rank, d]
+        ex.scatter_out()     -> ex.out     [batch, hq_rank, d]: my heads of every sequence
+    """
+
+    def __init__(self, mem: PeerMemory, batch: int, hq: int, d: int, timeout_s: float = 10.0):
+        self.lib = _lib.load()
+        self.mem, self.R, self.index = mem, mem.world, mem.rank
+        self.batch, self.hq, self.d = batch, hq, d
+        self.row_bytes = hq * d * 2
+        self.per = -(-batch // self.R)
+        self.b0 = min(batch, self.index * self.per)
+        self.b1 = min(batch, self.b0 + self.per)
+        off_q, off_out, total = self.layout(batch, hq, d)
+        if mem.local.numel() < total:
+            raise ValueError("allocation smaller than PeerExchange.layout()")
+        nb = batch * self.row_bytes
+        self.q = mem.local[off_q: off_q + nb].view(torch.bfloat16).view(batch, hq, d)
+        self.out = mem.local[off_out: off_out + nb].view(torch.bfloat16).view(batch, hq, d)
+        dev = mem.local.device
+        self.q_grp = torch.zeros(self.per, self.R * hq, d, dtype=torch.bfloat16, device=dev)
+        self.out_grp = torch.zeros(self.per, self.R * hq, d, dtype=torch.bfloat16, device=dev)
+        self._flags = _ptr_array(mem.base_ptrs)
+        self._q = _ptr_array([p + off_q for p in mem.base_ptrs])
+        self._out = _ptr_array([p + off_out for p in mem.base_ptrs])
+        self.timeout_ns = int(timeout_s * 1e9)
+
+    @staticmethod
+    def layout(batch: int, hq: int, d: int) -> tuple[int, int, int]:
+        """(q offset, out offset, total bytes) of one rank's allocation: [flags | q | out]."""
+        nb = -(-(batch * hq * d * 2) // _ALIGN) * _ALIGN
+        return _lib.PEER_FLAG_BYTES, _lib.PEER_FLAG_BYTES + nb, _lib.PEER_FLAG_BYTES + 2 * nb
+
+    @classmethod
+    def create(cls, group, batch: int, hq: int, d: int, device=None, transport: str = "auto", **kw):
+        return cls(PeerMemory.create(group, cls.layout(batch, hq, d)[2], device, transport), batch, hq, d, **kw)
+
+    @classmethod
+    def local_ranks(cls, R: int, batch: int, hq: int, d: int, device="cuda", **kw):
+        return [cls(m, batch, hq, d, **kw) for m in PeerMemory.local_ranks(R, cls.layout(batch, hq, d)[2], device)]
+
+    def _run(self, ptrs, local, scatter: int):
+        stream = torch.cuda.current_stream(local.device).cuda_stream
+        _lib.check("b200attn_peer_exchange", self.lib.b200attn_peer_exchange(
+            ptrs, self._flags, local.data_ptr(), self.R, self.index, self.b0, self.b1 - self.b0, self.per,
+            self.row_bytes, scatter, self.timeout_ns, stream))
+
+    def gather_q(self) -> torch.Tensor:
+        self._run(self._q, self.q_grp, 0)
+        return self.q_grp
+
+    def scatter_out(self) -> torch.Tensor:
+        self._run(self._out, self.out_grp, 1)
+        return self.out

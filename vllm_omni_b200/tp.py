@@ -65,10 +65,12 @@ class ReplicaSplit:
     bytes at cfg3). Results are identical head for head; the o_proj input layout is unchanged.
 
     Plumbing is two `all_to_all_single` calls on the replica group (NCCL over NVLink on GPUs, gloo in
-    the CPU tests): `gather_q` before the decode, `scatter_out` after it.
+    the CPU tests): `gather_q` before the decode, `scatter_out` after it. With `exchange` (a
+    `peer.PeerExchange` over the same group) both become one kernel each of this repo over peer memory
+    (`b200attn_peer_exchange`): same rows, no NCCL, no staging permutes.
     """
 
-    def __init__(self, shard: HeadShard, group=None):
+    def __init__(self, shard: HeadShard, group=None, exchange=None):
         import torch.distributed as dist  # local: tp.py stays importable without torch.distributed use
 
         self.dist = dist
@@ -76,6 +78,7 @@ class ReplicaSplit:
         self.index = shard.rank % self.R          # position inside the replica group
         self.group = group
         self.hq = shard.num_q_heads
+        self.exchange = exchange
 
     @staticmethod
     def groups(tp_size: int, kv_replicas: int):
@@ -104,6 +107,17 @@ class ReplicaSplit:
         local sequences [b0, b1) (rows past b1 - b0 are padding)."""
         import torch
         per, _, _ = self.plan(q.shape[0])
+        ex = self.exchange
+        if ex is not None:
+            if q.shape[0] != ex.batch:
+                raise ValueError(f"exchange was sized for batch {ex.batch}, got {q.shape[0]}")
+            if q.data_ptr() != ex.q.data_ptr():
+                ex.q.copy_(q)
+            res = ex.gather_q()
+            if out is not None and out.data_ptr() != res.data_ptr():
+                out.copy_(res)
+                return out
+            return res
         send = self._pad(q, self.R * per).contiguous()
         recv = torch.empty_like(send)             # [R, per, hq, d]: chunk i = peer i's heads, my sequences
         self.dist.all_to_all_single(recv, send, group=self.group)
@@ -118,6 +132,15 @@ class ReplicaSplit:
         """out_local [per, R * Hq_rank, d] -> [B, Hq_rank, d]: this rank's heads for every sequence."""
         import torch
         per, d = out_local.shape[0], out_local.shape[-1]
+        ex = self.exchange
+        if ex is not None:
+            if out_local.data_ptr() != ex.out_grp.data_ptr():
+                ex.out_grp[:out_local.shape[0]].copy_(out_local)
+            res = ex.scatter_out()
+            if out is not None and out.data_ptr() != res.data_ptr():
+                out.copy_(res)
+                return out
+            return res
         send = out_local.view(per, self.R, self.hq, d).permute(1, 0, 2, 3).contiguous()
         recv = torch.empty_like(send)             # chunk i = peer i's sequences, my heads
         self.dist.all_to_all_single(recv, send, group=self.group)
