@@ -321,3 +321,24 @@ def test_streamk_dynamic_tail_matches_oracle(lib, monkeypatch, shift, fp8):
         for _ in range(2):  # second launch: the claim counter must have been re-armed by the first
             out, lse = run_device(c, variant=ops.VARIANT_STREAMK)
             check(c, out, lse)
+
+
+@pytest.mark.parametrize("name", ["vllm_decode_32q4kv.npz", "vllm_decode_28q4kv.npz", "vllm_decode_16q2kv.npz"])
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_decode_against_vllm_stock_kernel_fixtures(lib, name, variant):
+    """The committed outputs of vLLM's own decode kernels (FlashAttention-2 paged varlen, FlashInfer TRT-LLM-gen;
+    tests/golden/gen_vllm_gpu_golden.py) on the cache vLLM's reshape_and_cache_flash wrote: this kernel must agree
+    with each of them to within two bf16 roundings of the output scale, and with the oracle to 2e-3."""
+    import numpy as np
+    from pathlib import Path
+    z = np.load(Path(__file__).resolve().parent / "golden" / name)
+    c = make_case(z["seq_lens"].tolist(), hq=int(z["hq"]), hkv=int(z["hkv"]), seed=int(z["seed"]))
+    want_cache = torch.from_numpy(z["cache_vllm"].copy()).view(torch.bfloat16)
+    cache = layout.alloc_kv_cache(c.num_blocks, c.block_size, int(z["hkv"]), 128, "auto", "cuda")
+    ops.reshape_and_cache(c.hist_k.cuda(), c.hist_v.cuda(), cache[0], cache[1], c.slots.cuda())
+    assert torch.equal(cache.cpu().view(torch.int16), want_cache.view(torch.int16)), "slot writes differ from vLLM's"
+    out, lse = run_device(c, variant=variant, cache_dev=cache)
+    check(c, out, lse)
+    for key in ("out_fa2", "out_trtllm"):
+        stock = torch.from_numpy(z[key].copy()).view(torch.bfloat16).float()
+        assert float((out.cpu().float() - stock).abs().max()) <= 2 ** -7 * float(stock.abs().max()), key

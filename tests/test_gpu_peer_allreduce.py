@@ -112,7 +112,8 @@ def test_peer_exchange_matches_replica_split_indexing(lib, R, batch):
         for ex, s in zip(exs, streams):
             with torch.cuda.stream(s):
                 ex.gather_q()
-                ex.out_grp.copy_(ex.q_grp.float().mul(2 + it).to(torch.bfloat16))   # stand-in for the decode
+                ex.out_grp.copy_(ex.q_grp)          # stand-in for the decode; in place: a torch allocation here could
+                ex.out_grp.mul_(2 + it)              # block the host behind rank 0's kernel, which waits for rank 1's launch
                 ex.scatter_out()
         torch.cuda.synchronize()
         for i, ex in enumerate(exs):

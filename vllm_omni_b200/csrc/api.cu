@@ -882,7 +882,8 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
   int64_t grid = (per_rank + kPeerThreads - 1) / kPeerThreads;
   if (grid < 1) grid = 1;
   if (grid > max_blocks) grid = max_blocks;
-  cudaError_t e = launch_peer_allreduce(a, n_vec, algo, static_cast<int>(grid), static_cast<cudaStream_t>(stream));
+  cudaError_t e = launch_peer_allreduce(a, n_vec, algo, static_cast<int>(grid), env_flag("B200ATTN_PDL", true),
+                                        static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "peer_allreduce launch");
 }
 
@@ -917,7 +918,8 @@ int b200attn_peer_exchange(void* const* peer_rows, void* const* peer_flags, void
   int64_t grid = (static_cast<int64_t>(rows_per_rank) * group_size * a.row_vec + kPeerThreads - 1) / kPeerThreads;
   if (grid < 1) grid = 1;
   if (grid > 64) grid = 64;
-  cudaError_t e = launch_peer_exchange(a, scatter != 0, static_cast<int>(grid), static_cast<cudaStream_t>(stream));
+  cudaError_t e = launch_peer_exchange(a, scatter != 0, static_cast<int>(grid), env_flag("B200ATTN_PDL", true),
+                                       static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "peer_exchange launch");
 }
 

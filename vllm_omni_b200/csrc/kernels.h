@@ -135,7 +135,7 @@ struct PeerExchangeArgs {
   int32_t b0, nrows;               // my sequence range [b0, b0 + nrows)
   int32_t row_vec;                 // row_bytes / 16
 };
-cudaError_t launch_peer_exchange(const PeerExchangeArgs& a, bool scatter, int grid, cudaStream_t stream);
-cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream);
+cudaError_t launch_peer_exchange(const PeerExchangeArgs& a, bool scatter, int grid, bool pdl, cudaStream_t stream);
+cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, bool pdl, cudaStream_t stream);
 
 }  // namespace b200

@@ -19,7 +19,7 @@
 // Flag protocol (CUDA-graph safe, nothing is reset between launches): flag words are monotonically
 // increasing launch-local epochs. Block b of rank r owns epoch counter `epoch[b]` in its own flag
 // region; a barrier = bump the epoch, store it into slot [b][r] of every peer's flag region with
-// st.release.sys, spin with ld.acquire.sys on the `world` slots of the own region until each is >= the
+// a relaxed system-scope store, spin with relaxed loads on the `world` slots of the own region until each is >= the
 // epoch (wrap-safe signed compare). A peer can be at most one barrier ahead, so >= is sufficient. Same-index
 // blocks pair up across ranks, and both TWOSHOT phases use the same (block, thread) -> element mapping, so a
 // per-block barrier orders exactly the data that block consumes. The sum order is rank 0..world-1 in fp32
@@ -36,14 +36,6 @@ namespace b200 {
 
 namespace {
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
   uint4 v;
   asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -69,19 +61,35 @@ __device__ __forceinline__ uint32_t* error_of(uint32_t* flags) {
   return flags + kPeerMaxBlocks * kPeerMaxRanks + kPeerMaxBlocks;
 }
 
-// Block-wide barrier with the same-index block of every peer. `fence` = the data written before it
-// must be visible to the peers after it (release/acquire at system scope); false = control only.
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Block-wide barrier with the same-index block of every peer.
+//   fence = true : data written by this block before the barrier is visible to the peers after it
+//                  (fence.sys before the flag store = release, fence.sys after the spin = acquire; bar.sync
+//                  makes both cumulative over the block). A system-scope fence drains to NVLink and costs
+//                  microseconds, so it is paid only where a peer consumes what this launch produced.
+//   fence = false: control only, relaxed flag traffic. Enough (a) at kernel start, where the data the peers
+//                  read was completed by an EARLIER kernel of their stream (visible at kernel completion), and
+//                  (b) for "I have finished reading your buffer", where every load's value was consumed
+//                  before the bar.sync below.
 __device__ __forceinline__ void peer_barrier(const PeerCtl& a, uint32_t& epoch, bool fence) {
-  __syncthreads();  // every thread of the block has issued (and, with the fence below, published) its stores
+  __syncthreads();
   epoch += 1;
   const int t = threadIdx.x;
   if (t < a.world) {
     if (fence) __threadfence_system();
-    st_release_sys(slot_of(a.flags[t], blockIdx.x, a.rank), epoch);
+    st_relaxed_sys(slot_of(a.flags[t], blockIdx.x, a.rank), epoch);
     const uint32_t* mine = slot_of(a.flags[a.rank], blockIdx.x, t);
     const uint64_t t0 = globaltimer_ns();
     uint32_t spins = 0;
-    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+    while (static_cast<int32_t>(ld_relaxed_sys(mine) - epoch) < 0) {
       if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > a.timeout_ns) {
         uint32_t* e = error_of(a.flags[a.rank]);
         e[0] = 1u; e[1] = blockIdx.x; e[2] = static_cast<uint32_t>(t); e[3] = epoch;
@@ -90,8 +98,17 @@ __device__ __forceinline__ void peer_barrier(const PeerCtl& a, uint32_t& epoch, 
         break;  // test mode: give up on this wait, the host reads the error words
       }
     }
+    if (fence) __threadfence_system();
   }
   __syncthreads();
+}
+
+// Programmatic dependent launch: these kernels are launched with programmaticStreamSerialization, so their
+// CTAs are scheduled while the previous kernel of the stream drains; nothing may be touched before the wait.
+// Releasing the dependents first is safe because every kernel of this library waits the same way.
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 __device__ __forceinline__ void acc_bf16x8(float (&acc)[8], const uint4& v) {
@@ -130,6 +147,7 @@ __device__ __forceinline__ uint4 reduce_vec(const PeerArgs& a, int64_t idx) {
 // ---------------------------------------------------------------------------------------------
 template <int WORLD>
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_oneshot_kernel(PeerArgs a, int64_t n_vec) {
+  pdl_prologue();
   uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
   peer_barrier(a.ctl, epoch, /*fence=*/false);  // every peer's producer kernel has finished (stream order + kernel boundary)
   const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
@@ -142,6 +160,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_oneshot_kernel(Pe
 
 template <int WORLD>
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_twoshot_kernel(PeerArgs a, int64_t n_vec) {
+  pdl_prologue();
   uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
   const int64_t part = n_vec / WORLD;                 // slice r = [r*part, (r+1)*part), the last one takes the tail
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x;
@@ -169,6 +188,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_twoshot_kernel(Pe
 // NVLS: the switch reduces. mc_in / mc_out are MULTICAST addresses of the input / output regions;
 // the result lands in every rank's output region (a.out must be this rank's unicast view of it).
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_multimem_kernel(PeerArgs a, int64_t n_vec) {
+  pdl_prologue();
   uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
   const int64_t part = n_vec / a.ctl.world;
   const int64_t my_start = a.ctl.rank * part;
@@ -191,25 +211,34 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_multimem_kernel(P
   if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
 }
 
-template <int WORLD>
-static cudaError_t launch_world(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream) {
-  if (algo == kPeerOneShot)
-    peer_allreduce_oneshot_kernel<WORLD><<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
-  else
-    peer_allreduce_twoshot_kernel<WORLD><<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
-  return cudaGetLastError();
+template <typename K, typename... Args>
+static cudaError_t peer_launch(K kern, int grid, bool pdl, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(kPeerThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
-cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, cudaStream_t stream) {
-  if (algo == kPeerMultimem) {
-    peer_allreduce_multimem_kernel<<<grid, kPeerThreads, 0, stream>>>(a, n_vec);
-    return cudaGetLastError();
-  }
+template <int WORLD>
+static cudaError_t launch_world(const PeerArgs& a, int64_t n_vec, int algo, int grid, bool pdl, cudaStream_t stream) {
+  if (algo == kPeerOneShot) return peer_launch(peer_allreduce_oneshot_kernel<WORLD>, grid, pdl, stream, a, n_vec);
+  return peer_launch(peer_allreduce_twoshot_kernel<WORLD>, grid, pdl, stream, a, n_vec);
+}
+
+cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, bool pdl, cudaStream_t stream) {
+  if (algo == kPeerMultimem) return peer_launch(peer_allreduce_multimem_kernel, grid, pdl, stream, a, n_vec);
   switch (a.ctl.world) {
-    case 1: return launch_world<1>(a, n_vec, algo, grid, stream);
-    case 2: return launch_world<2>(a, n_vec, algo, grid, stream);
-    case 4: return launch_world<4>(a, n_vec, algo, grid, stream);
-    case 8: return launch_world<8>(a, n_vec, algo, grid, stream);
+    case 1: return launch_world<1>(a, n_vec, algo, grid, pdl, stream);
+    case 2: return launch_world<2>(a, n_vec, algo, grid, pdl, stream);
+    case 4: return launch_world<4>(a, n_vec, algo, grid, pdl, stream);
+    case 8: return launch_world<8>(a, n_vec, algo, grid, pdl, stream);
     default: return cudaErrorInvalidValue;
   }
 }
@@ -222,6 +251,7 @@ cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, in
 // ---------------------------------------------------------------------------------------------
 template <bool SCATTER>
 __global__ void __launch_bounds__(kPeerThreads) peer_exchange_kernel(PeerExchangeArgs a) {
+  pdl_prologue();
   uint32_t epoch = *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x);
   if (!SCATTER) peer_barrier(a.ctl, epoch, /*fence=*/false);
   const int R = a.ctl.world;
@@ -247,12 +277,9 @@ __global__ void __launch_bounds__(kPeerThreads) peer_exchange_kernel(PeerExchang
   if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
 }
 
-cudaError_t launch_peer_exchange(const PeerExchangeArgs& a, bool scatter, int grid, cudaStream_t stream) {
-  if (scatter)
-    peer_exchange_kernel<true><<<grid, kPeerThreads, 0, stream>>>(a);
-  else
-    peer_exchange_kernel<false><<<grid, kPeerThreads, 0, stream>>>(a);
-  return cudaGetLastError();
+cudaError_t launch_peer_exchange(const PeerExchangeArgs& a, bool scatter, int grid, bool pdl, cudaStream_t stream) {
+  if (scatter) return peer_launch(peer_exchange_kernel<true>, grid, pdl, stream, a);
+  return peer_launch(peer_exchange_kernel<false>, grid, pdl, stream, a);
 }
 
 }  // namespace b200
