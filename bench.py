@@ -316,7 +316,7 @@ def run_b200(args, wl):
                 hidden = ar.input(hidden.shape)           # o_proj would write its partial sums here
                 hidden.zero_()
                 hidden_out = torch.empty(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")
-                algo = peer.ALGO_NAMES[peer.choose_algo(2 * hidden.numel(), world, ar.has_multicast)]
+                algo = peer.ALGO_NAMES[peer.choose_algo(2 * hidden.numel(), world, ar.has_multicast, ar.push_slot_bytes)]
                 ar_note = f"peer-memory {algo} kernel ({ar.transport} mapping, multicast={ar.has_multicast})"
             except Exception as exc:  # noqa: BLE001 - say so in the JSON line, never silently
                 ar = None

@@ -284,12 +284,16 @@ B200ATTN_API int b200attn_gather_kv(
  *   out             local result. ONESHOT/TWOSHOT: any device pointer that no peer reads (it may
  *                   not alias peer_in). MULTIMEM: this rank's unicast view of the region `mc_out`
  *                   multicasts to.
+ *   peer_push[r]    rank r's receive region of the PUSH schedule (or NULL array: PUSH unavailable):
+ *                   3 x world x push_slot_bytes, filled ONCE with the bf16 pattern 0x8000 (-0.0, the
+ *                   "not arrived" sentinel) before the first launch. PUSH reads its input only from
+ *                   peer_in[rank], which may then be ANY local device pointer (no peer mapping needed).
  *   mc_in / mc_out  multicast addresses of the input / output regions (MULTIMEM) or NULL.
  *   numel           multiple of 8.  algo: AUTO picks by size (b200attn_peer_allreduce_algo).
  *   timeout_ns      a flag wait longer than this records {1, block, peer, epoch} in the 4 words after the
  *                   flag slots and traps the kernel (0 = 10 s). With B200ATTN_PEER_SOFT_TIMEOUT=1 in the
  *                   environment (tests) the wait is abandoned instead and the result is undefined.
- * ONESHOT and TWOSHOT are bit-identical on every rank and equal to the sequential fp32 sum in rank
+ * ONESHOT, TWOSHOT and PUSH are bit-identical on every rank and equal to the sequential fp32 sum in rank
  * order rounded once to bf16; MULTIMEM leaves the order to the switch (fp32 accumulate).
  */
 #define B200ATTN_PEER_FLAG_BYTES 8192
@@ -298,10 +302,13 @@ B200ATTN_API int b200attn_gather_kv(
 #define B200ATTN_AR_ONESHOT 1
 #define B200ATTN_AR_TWOSHOT 2
 #define B200ATTN_AR_MULTIMEM 3
+#define B200ATTN_AR_PUSH 4
 /* pure host arithmetic: the schedule AUTO resolves to for `bytes` of input on `world` ranks */
-B200ATTN_API int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast);
+B200ATTN_API int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast,
+                                                  int64_t push_slot_bytes);
 B200ATTN_API int b200attn_peer_allreduce(
     const void* const* peer_in, void* const* peer_scratch, void* const* peer_flags,
+    void* const* peer_push, int64_t push_slot_bytes,
     void* out, const void* mc_in, void* mc_out,
     int64_t numel, int32_t world, int32_t rank, int32_t algo, int32_t max_blocks,
     uint64_t timeout_ns, void* stream);

@@ -23,7 +23,7 @@ from oracle import oracle
 from vllm_omni_b200 import _lib, peer
 
 HIDDEN = 2048
-ROWS = [8, 64, 128, 256, 512, 1024]
+ROWS = [8, 64, 128, 256, 512]
 REPS = 20
 
 
@@ -66,12 +66,14 @@ def main():
             doc["transports"][tr] = {"unavailable": f"{type(e).__name__}: {str(e)[:400]}"}
             continue
         rec = {"multicast": ar.has_multicast, "algos": {}}
-        algos = [_lib.AR_ONESHOT, _lib.AR_TWOSHOT] + ([_lib.AR_MULTIMEM] if ar.has_multicast else [])
+        algos = [_lib.AR_PUSH, _lib.AR_ONESHOT, _lib.AR_TWOSHOT] + ([_lib.AR_MULTIMEM] if ar.has_multicast else [])
         for algo in algos:
             name = peer.ALGO_NAMES[algo]
             arec = {"exact": True, "max_abs_err": 0.0, "us": {}}
             try:
                 for rows in ROWS:
+                    if algo == _lib.AR_PUSH and 2 * rows * HIDDEN > ar.push_slot_bytes:
+                        continue
                     for it in range(2):
                         parts = inputs(world, rows, it)
                         xin = ar.input((rows, HIDDEN))
@@ -91,7 +93,7 @@ def main():
             except Exception as e:  # noqa: BLE001
                 arec["error"] = f"{type(e).__name__}: {str(e)[:400]}"
             rec["algos"][name] = arec
-        rec["auto"] = {str(r): peer.ALGO_NAMES[peer.choose_algo(2 * r * HIDDEN, world, ar.has_multicast)] for r in ROWS}
+        rec["auto"] = {str(r): peer.ALGO_NAMES[peer.choose_algo(2 * r * HIDDEN, world, ar.has_multicast, ar.push_slot_bytes)] for r in ROWS}
         doc["transports"][tr] = rec
     if rank == 0:
         s = json.dumps(doc, indent=1)

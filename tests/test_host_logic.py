@@ -163,6 +163,14 @@ def test_peer_allreduce_schedule_choice_and_region_layout(lib, monkeypatch):
     monkeypatch.setenv("B200ATTN_AR_MULTIMEM", "1")
     assert peer.choose_algo(512 << 10, 8, True) == _lib.AR_MULTIMEM
     assert peer.choose_algo(512 << 10, 8, False) == _lib.AR_TWOSHOT
+    # PUSH (barrier-free) while the posted bytes stay latency-sized and fit the provisioned slot
+    assert peer.choose_algo(512 << 10, 2, False, 512 << 10) == _lib.AR_PUSH
+    assert peer.choose_algo(512 << 10, 2, False, 256 << 10) == _lib.AR_ONESHOT      # slot too small
+    assert peer.choose_algo(128 << 10, 8, False, 1 << 20) == _lib.AR_PUSH
+    assert peer.choose_algo(2 << 20, 8, False, 1 << 20) == _lib.AR_TWOSHOT          # 14 MiB of pushes: bandwidth-bound
+    assert peer.push_layout(128 * 2048, 1) == 0 and peer.push_layout(128 * 2048, 2) == 512 << 10
+    assert peer.push_layout(1 << 22, 8) == peer.PUSH_MAX_BYTES
+    assert peer.region_layout(128 * 2048, 2)[3] == peer.region_layout(128 * 2048)[3] + 3 * 2 * (512 << 10)
     off_in, off_scr, cap, total = peer.region_layout(512 * 2048)
     assert off_in == _lib.PEER_FLAG_BYTES and off_in % 256 == 0 and off_scr % 256 == 0
     assert cap >= 512 * 2048 * 2 + 16 and off_scr == off_in + cap and total == off_scr + cap
@@ -173,12 +181,14 @@ def test_peer_allreduce_api_rejects_bad_arguments_without_a_gpu(lib):
     from vllm_omni_b200 import _lib
     arr = (C.c_void_p * 2)(C.c_void_p(4096), C.c_void_p(8192))
     f = lib.b200attn_peer_allreduce
-    assert f(arr, arr, arr, 65536, None, None, 64, 3, 0, 1, 0, 0, None) == -2      # world 3 unsupported
-    assert f(arr, arr, arr, 65536, None, None, 12, 2, 0, 1, 0, 0, None) == -1      # numel % 8
-    assert f(arr, arr, arr, 65536, None, None, 64, 2, 2, 1, 0, 0, None) == -1      # rank out of range
-    assert f(arr, arr, arr, 65536, None, None, 64, 2, 0, 3, 0, 0, None) == -1      # multimem without multicast ptrs
-    assert f(arr, arr, arr, 4096, None, None, 64, 2, 0, 1, 0, 0, None) == -1       # out aliases the input
-    assert f(arr, arr, arr, 65536, None, None, 0, 2, 0, 1, 0, 0, None) == 0        # empty: nothing to do
+    assert f(arr, arr, arr, None, 0, 65536, None, None, 64, 3, 0, 1, 0, 0, None) == -2      # world 3 unsupported
+    assert f(arr, arr, arr, None, 0, 65536, None, None, 12, 2, 0, 1, 0, 0, None) == -1      # numel % 8
+    assert f(arr, arr, arr, None, 0, 65536, None, None, 64, 2, 2, 1, 0, 0, None) == -1      # rank out of range
+    assert f(arr, arr, arr, None, 0, 65536, None, None, 64, 2, 0, 3, 0, 0, None) == -1      # multimem without multicast ptrs
+    assert f(arr, arr, arr, None, 0, 4096, None, None, 64, 2, 0, 1, 0, 0, None) == -1       # out aliases the input
+    assert f(arr, arr, arr, None, 0, 65536, None, None, 0, 2, 0, 1, 0, 0, None) == 0        # empty: nothing to do
+    assert f(arr, arr, arr, None, 0, 65536, None, None, 64, 2, 0, 4, 0, 0, None) == -1      # PUSH without receive buffers
+    assert f(arr, arr, arr, arr, 64, 65536, None, None, 64, 2, 0, 4, 0, 0, None) == -1      # PUSH slot smaller than the message
 
 
 def test_oracle_all_reduce_is_sequential_fp32_then_one_rounding():

@@ -14,7 +14,7 @@ LIB_PATH = PKG_DIR / "libb200attn.so"
 
 ABI_VERSION = 7
 PEER_FLAG_BYTES = 8192
-AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM = 0, 1, 2, 3
+AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH = 0, 1, 2, 3, 4
 KV_BF16 = 0
 KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0
@@ -97,9 +97,10 @@ SIGNATURES: dict[str, tuple] = {
         _vp, _vp, _i32, _vp]),
     "b200attn_gather_kv": (C.c_int, [
         _vp, *_CACHE_ARGS, _i64, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
-    "b200attn_peer_allreduce_algo": (_i32, [_i64, _i32, _i32]),
+    "b200attn_peer_allreduce_algo": (_i32, [_i64, _i32, _i32, _i64]),
     "b200attn_peer_allreduce": (C.c_int, [
         C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),   # peer_in, peer_scratch, peer_flags (host arrays)
+        C.POINTER(_vp), _i64,                             # peer_push (host array or NULL), push_slot_bytes
         _vp, _vp, _vp,                                    # out, mc_in, mc_out
         _i64, _i32, _i32, _i32, _i32,                     # numel, world, rank, algo, max_blocks
         C.c_uint64, _vp]),                                # timeout_ns, stream

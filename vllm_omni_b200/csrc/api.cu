@@ -828,35 +828,47 @@ int b200attn_gather_kv(const void* cache, int64_t cache_stride_block, int64_t ca
 // peer-memory all-reduce
 // ---------------------------------------------------------------------------------------------
 static_assert(kPeerFlagBytes == B200ATTN_PEER_FLAG_BYTES && kPeerMaxRanks == B200ATTN_PEER_MAX_RANKS &&
-                  (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 4) * 4 <= kPeerFlagBytes, "flag region");
+                  (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 8) * 4 <= kPeerFlagBytes, "flag region");
 
-int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast) {
-  // bytes crossing NVLink per rank: ONESHOT (world-1) x bytes, TWOSHOT 2 x (world-1)/world x bytes + one more
-  // flag barrier (~1.5 us): the same at world 2, so ONESHOT there; the crossover sits near 256 KiB at 4 and 8 ranks.
+int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast, int64_t push_slot_bytes) {
+  // PUSH (no flag round trips) while the (world-1) x bytes each rank posts stay latency-sized and fit a slot.
+  // Otherwise bytes crossing NVLink per rank: ONESHOT (world-1) x bytes, TWOSHOT 2 x (world-1)/world x bytes + one
+  // more flag barrier: the same at world 2, so ONESHOT there; the crossover sits near 256 KiB at 4 and 8 ranks.
+  if (world <= 1) return B200ATTN_AR_ONESHOT;
+  if (push_slot_bytes > 0 && bytes <= push_slot_bytes && (world - 1) * bytes <= (2 << 20) &&
+      env_flag("B200ATTN_AR_PUSH", true))
+    return B200ATTN_AR_PUSH;
   if (world <= 2) return B200ATTN_AR_ONESHOT;
   if (has_multicast && env_flag("B200ATTN_AR_MULTIMEM", false) && bytes >= (64 << 10)) return B200ATTN_AR_MULTIMEM;
   return bytes <= (256 << 10) ? B200ATTN_AR_ONESHOT : B200ATTN_AR_TWOSHOT;
 }
 
 int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratch, void* const* peer_flags,
-                            void* out, const void* mc_in, void* mc_out, int64_t numel, int32_t world,
-                            int32_t rank, int32_t algo, int32_t max_blocks, uint64_t timeout_ns, void* stream) {
+                            void* const* peer_push, int64_t push_slot_bytes, void* out, const void* mc_in,
+                            void* mc_out, int64_t numel, int32_t world, int32_t rank, int32_t algo,
+                            int32_t max_blocks, uint64_t timeout_ns, void* stream) {
   if (world != 1 && world != 2 && world != 4 && world != 8)
     return fail(B200ATTN_EUNSUPPORTED, "world %d (1, 2, 4 or 8 ranks)", world);
   if (rank < 0 || rank >= world) return fail(B200ATTN_EINVAL, "rank %d of %d", rank, world);
   if (numel < 0 || numel % 8) return fail(B200ATTN_EINVAL, "numel %lld must be a non-negative multiple of 8", (long long)numel);
   if (numel == 0) return 0;
   if (peer_in == nullptr || peer_flags == nullptr || out == nullptr) return fail(B200ATTN_EINVAL, "null pointer");
-  if (algo == B200ATTN_AR_AUTO) algo = b200attn_peer_allreduce_algo(numel * 2, world, mc_in != nullptr && mc_out != nullptr);
-  if (algo < B200ATTN_AR_ONESHOT || algo > B200ATTN_AR_MULTIMEM) return fail(B200ATTN_EINVAL, "algo %d", algo);
+  if (push_slot_bytes < 0 || push_slot_bytes % 16) return fail(B200ATTN_EINVAL, "push_slot_bytes must be a multiple of 16");
+  if (algo == B200ATTN_AR_AUTO)
+    algo = b200attn_peer_allreduce_algo(numel * 2, world, mc_in != nullptr && mc_out != nullptr,
+                                        peer_push != nullptr ? push_slot_bytes : 0);
+  if (algo < B200ATTN_AR_ONESHOT || algo > B200ATTN_AR_PUSH) return fail(B200ATTN_EINVAL, "algo %d", algo);
   if (algo == B200ATTN_AR_TWOSHOT && peer_scratch == nullptr) return fail(B200ATTN_EINVAL, "TWOSHOT needs peer_scratch");
   if (algo == B200ATTN_AR_MULTIMEM && (mc_in == nullptr || mc_out == nullptr))
     return fail(B200ATTN_EINVAL, "MULTIMEM needs multicast addresses");
+  if (algo == B200ATTN_AR_PUSH && (peer_push == nullptr || numel * 2 > push_slot_bytes))
+    return fail(B200ATTN_EINVAL, "PUSH needs peer_push with slots of at least %lld bytes", (long long)(numel * 2));
   PeerArgs a;
   memset(&a, 0, sizeof(a));
   for (int r = 0; r < world; ++r) {
-    if (peer_in[r] == nullptr || peer_flags[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_in[r]) % 16) ||
-        (reinterpret_cast<uintptr_t>(peer_flags[r]) % 16))
+    const bool need_in = algo != B200ATTN_AR_PUSH || r == rank;  // PUSH reads only the local input
+    if (peer_flags[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_flags[r]) % 16) ||
+        (need_in && (peer_in[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_in[r]) % 16))))
       return fail(B200ATTN_EINVAL, "peer_in/peer_flags[%d] null or not 16-byte aligned", r);
     a.in[r] = peer_in[r];
     a.ctl.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
@@ -865,18 +877,25 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
         return fail(B200ATTN_EINVAL, "peer_scratch[%d] null or not 16-byte aligned", r);
       a.scratch[r] = peer_scratch[r];
     }
+    if (algo == B200ATTN_AR_PUSH) {
+      if (peer_push[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_push[r]) % 16))
+        return fail(B200ATTN_EINVAL, "peer_push[%d] null or not 16-byte aligned", r);
+      a.push[r] = peer_push[r];
+    }
   }
   if (reinterpret_cast<uintptr_t>(out) % 16) return fail(B200ATTN_EINVAL, "out must be 16-byte aligned");
   if (algo != B200ATTN_AR_MULTIMEM && out == peer_in[rank]) return fail(B200ATTN_EINVAL, "out may not alias the input region");
   a.out = out;
   a.mc_in = mc_in;
   a.mc_out = mc_out;
+  a.push_slot_vec = push_slot_bytes / 16;
   a.ctl.world = world;
   a.ctl.rank = rank;
   a.ctl.timeout_ns = timeout_ns ? timeout_ns : 10000000000ull;
   a.ctl.soft_timeout = env_flag("B200ATTN_PEER_SOFT_TIMEOUT", false) ? 1 : 0;
   const int64_t n_vec = numel / 8;
-  const int64_t per_rank = algo == B200ATTN_AR_ONESHOT ? n_vec : n_vec - (world - 1) * (n_vec / world);
+  const bool whole = algo == B200ATTN_AR_ONESHOT || algo == B200ATTN_AR_PUSH;  // every rank touches every vector
+  const int64_t per_rank = whole ? n_vec : n_vec - (world - 1) * (n_vec / world);
   if (max_blocks <= 0) max_blocks = 64;
   if (max_blocks > kPeerMaxBlocks) max_blocks = kPeerMaxBlocks;
   int64_t grid = (per_rank + kPeerThreads - 1) / kPeerThreads;

@@ -108,8 +108,8 @@ cudaError_t launch_gather_kv(const GatherParams& p, int num_sms, cudaStream_t st
 constexpr int kPeerMaxRanks = 8;
 constexpr int kPeerMaxBlocks = 128;   // flag slots exist for this many blocks per launch
 constexpr int kPeerThreads = 512;
-constexpr size_t kPeerFlagBytes = 8192;  // >= (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 4) * 4, 16-byte multiple
-constexpr int kPeerOneShot = 1, kPeerTwoShot = 2, kPeerMultimem = 3;
+constexpr size_t kPeerFlagBytes = 8192;  // >= (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 8) * 4, 16-byte multiple
+constexpr int kPeerOneShot = 1, kPeerTwoShot = 2, kPeerMultimem = 3, kPeerPush = 4;
 struct PeerCtl {                   // who takes part in a flag barrier
   uint32_t* flags[kPeerMaxRanks];  // every rank's flag region (kPeerFlagBytes, zeroed once), index = rank
   int32_t world, rank;
@@ -123,6 +123,8 @@ struct PeerArgs {
   void* out;                       // local result
   const void* mc_in;               // multicast view of the input region (multimem) or null
   void* mc_out;                    // multicast view of the output region (multimem) or null
+  void* push[kPeerMaxRanks];       // every rank's receive region of the PUSH schedule: [3][world][push_slot_vec] x 16 B
+  int64_t push_slot_vec;
 };
 // Row exchange inside a KV-head replica group (tp.ReplicaSplit): rank g of the group owns rows
 // [B, row_bytes] (its query heads of every sequence); rank i serves sequences [b0_i, b0_i + per).

@@ -12,6 +12,12 @@
 //   TWOSHOT   reduce-scatter + all-gather inside ONE launch: rank r sums slice r of every peer into its
 //             scratch, a flag barrier publishes it, then every rank copies the other slices. (world-1)/world
 //             x 2 of the bytes cross NVLink instead of (world-1) x.
+//   PUSH      barrier-free ("Lamport") one-shot for latency-bound sizes: every rank WRITES its vectors into a
+//             slot of each peer's receive buffer and the receivers spin on the data itself — the buffers are
+//             pre-filled with a sentinel (bf16 -0.0, which senders canonicalise to +0.0, so no sum changes) and
+//             a 16-byte vector is complete when none of its halves is the sentinel. One posted NVLink write of
+//             latency instead of two flag round trips; three receive buffers rotate (step k uses k % 3 and
+//             re-arms the one of step k-1), so nothing is ever reset by the host. The input needs no peer mapping.
 //   MULTIMEM  NVLS: `multimem.ld_reduce` on the multicast address lets the NVSwitch add the replicas
 //             (fp32 accumulate), `multimem.st` broadcasts the sum; each rank handles slice r. Needs a
 //             multicast mapping of the allocation.
@@ -60,6 +66,8 @@ __device__ __forceinline__ uint32_t* epoch_of(uint32_t* flags, int block) {
 __device__ __forceinline__ uint32_t* error_of(uint32_t* flags) {
   return flags + kPeerMaxBlocks * kPeerMaxRanks + kPeerMaxBlocks;
 }
+// PUSH schedule state: {step, blocks done, vectors of the previous step, -}
+__device__ __forceinline__ uint32_t* push_state_of(uint32_t* flags) { return error_of(flags) + 4; }
 
 __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -185,6 +193,94 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_twoshot_kernel(Pe
   if (threadIdx.x == 0) *epoch_of(a.ctl.flags[a.ctl.rank], blockIdx.x) = epoch;
 }
 
+// ---- PUSH ("Lamport") one-shot --------------------------------------------------------------
+constexpr uint32_t kSentinelWord = 0x80008000u;  // two bf16 -0.0
+__device__ __forceinline__ uint32_t canon_word(uint32_t w) {  // -0.0 -> +0.0 in either half
+  if ((w & 0xffffu) == 0x8000u) w &= 0xffff0000u;
+  if ((w >> 16) == 0x8000u) w &= 0x0000ffffu;
+  return w;
+}
+__device__ __forceinline__ bool word_pending(uint32_t w) { return (w & 0xffffu) == 0x8000u || (w >> 16) == 0x8000u; }
+__device__ __forceinline__ bool vec_pending(const uint4& v) {
+  return word_pending(v.x) || word_pending(v.y) || word_pending(v.z) || word_pending(v.w);
+}
+__device__ __forceinline__ void st_peer_v4(void* p, const uint4& x) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(x.x), "r"(x.y), "r"(x.z), "r"(x.w)
+               : "memory");
+}
+
+// a.push[r] = rank r's receive region: [3 buffers][WORLD slots][slot_vec vectors]; slot s of a buffer holds
+// what rank s pushed. a.in[rank] is this rank's input (any device memory); a.out the local result.
+template <int WORLD>
+__global__ void __launch_bounds__(kPeerThreads) peer_allreduce_push_kernel(PeerArgs a, int64_t n_vec, int64_t slot_vec) {
+  pdl_prologue();
+  const int rank = a.ctl.rank;
+  uint32_t* state = push_state_of(a.ctl.flags[rank]);
+  const uint32_t step = state[0];
+  const int64_t n_prev = state[2];
+  const int cur = step % 3, prev = (step + 2) % 3;
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
+  const uint4* in = reinterpret_cast<const uint4*>(a.in[rank]);
+  uint4* mine = reinterpret_cast<uint4*>(a.push[rank]);
+  // 1. push my vectors into slot `rank` of every peer's current buffer (posted writes, no round trip)
+  for (int64_t i = tid; i < n_vec; i += stride) {
+    uint4 v = in[i];
+    v.x = canon_word(v.x); v.y = canon_word(v.y); v.z = canon_word(v.z); v.w = canon_word(v.w);
+#pragma unroll
+    for (int d = 1; d < WORLD; ++d) {
+      const int p = (rank + d) % WORLD;
+      st_peer_v4(reinterpret_cast<uint4*>(a.push[p]) + (static_cast<int64_t>(cur) * WORLD + rank) * slot_vec + i, v);
+    }
+  }
+  // 2. re-arm the buffer of the previous step (everything in it was consumed before that launch retired)
+  const uint4 sent = make_uint4(kSentinelWord, kSentinelWord, kSentinelWord, kSentinelWord);
+  for (int64_t i = tid; i < n_prev; i += stride) {
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      if (r != rank) mine[(static_cast<int64_t>(prev) * WORLD + r) * slot_vec + i] = sent;
+  }
+  // 3. wait for the peers' vectors to land in my current buffer, add in rank order
+  const uint64_t t0 = globaltimer_ns();
+  for (int64_t i = tid; i < n_vec; i += stride) {
+    uint4 v[WORLD];
+    v[rank] = in[i];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) {
+      if (r == rank) continue;
+      const uint4* src = mine + (static_cast<int64_t>(cur) * WORLD + r) * slot_vec + i;
+      uint32_t spins = 0;
+      while (true) {
+        v[r] = ld_peer_v4(src);
+        if (!vec_pending(v[r])) break;
+        if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > a.ctl.timeout_ns) {
+          uint32_t* e = error_of(a.ctl.flags[rank]);
+          e[0] = 2u; e[1] = blockIdx.x; e[2] = static_cast<uint32_t>(r); e[3] = step;
+          __threadfence_system();
+          if (!a.ctl.soft_timeout) __trap();
+          break;
+        }
+      }
+    }
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) acc_bf16x8(acc, v[r]);
+    reinterpret_cast<uint4*>(a.out)[i] = pack_bf16x8(acc);
+  }
+  // 4. the last block to finish advances the step (every block has read it by then)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t done = atomicAdd(state + 1, 1u);
+    if (done == gridDim.x - 1) {
+      state[1] = 0u;
+      state[2] = static_cast<uint32_t>(n_vec);
+      state[0] = step + 1;
+      __threadfence();
+    }
+  }
+}
+
 // NVLS: the switch reduces. mc_in / mc_out are MULTICAST addresses of the input / output regions;
 // the result lands in every rank's output region (a.out must be this rank's unicast view of it).
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_multimem_kernel(PeerArgs a, int64_t n_vec) {
@@ -232,7 +328,21 @@ static cudaError_t launch_world(const PeerArgs& a, int64_t n_vec, int algo, int 
   return peer_launch(peer_allreduce_twoshot_kernel<WORLD>, grid, pdl, stream, a, n_vec);
 }
 
+template <int WORLD>
+static cudaError_t launch_push(const PeerArgs& a, int64_t n_vec, int grid, bool pdl, cudaStream_t stream) {
+  return peer_launch(peer_allreduce_push_kernel<WORLD>, grid, pdl, stream, a, n_vec, a.push_slot_vec);
+}
+
 cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, bool pdl, cudaStream_t stream) {
+  if (algo == kPeerPush) {
+    switch (a.ctl.world) {
+      case 1: return launch_push<1>(a, n_vec, grid, pdl, stream);
+      case 2: return launch_push<2>(a, n_vec, grid, pdl, stream);
+      case 4: return launch_push<4>(a, n_vec, grid, pdl, stream);
+      case 8: return launch_push<8>(a, n_vec, grid, pdl, stream);
+      default: return cudaErrorInvalidValue;
+    }
+  }
   if (algo == kPeerMultimem) return peer_launch(peer_allreduce_multimem_kernel, grid, pdl, stream, a, n_vec);
   switch (a.ctl.world) {
     case 1: return launch_world<1>(a, n_vec, algo, grid, pdl, stream);

@@ -22,7 +22,8 @@ import torch
 from . import _lib
 
 ALGO_NAMES = {_lib.AR_AUTO: "auto", _lib.AR_ONESHOT: "oneshot", _lib.AR_TWOSHOT: "twoshot",
-              _lib.AR_MULTIMEM: "multimem"}
+              _lib.AR_MULTIMEM: "multimem", _lib.AR_PUSH: "push"}
+PUSH_MAX_BYTES = 1 << 20      # largest message the PUSH schedule is provisioned for (per slot)
 _ALIGN = 256
 
 
@@ -30,19 +31,27 @@ class PeerSetupError(RuntimeError):
     """Peer-mapped memory could not be established between the ranks."""
 
 
-def region_layout(max_numel: int) -> tuple[int, int, int, int]:
+def region_layout(max_numel: int, world: int = 0) -> tuple[int, int, int, int]:
     """(input offset, scratch/out offset, region capacity in bytes, total bytes) of one rank's allocation
-    for bf16 tensors of up to `max_numel` elements. The scratch region doubles as the multimem output
-    region, so it has the full capacity."""
+    for bf16 tensors of up to `max_numel` elements: [flags | input | scratch/out | push receive buffers]. The
+    scratch region doubles as the multimem output region, so it has the full capacity. With `world` > 1 the
+    allocation ends with the 3 x world receive slots of the PUSH schedule (see `push_layout`)."""
     cap = -(-(max_numel * 2 + 16) // _ALIGN) * _ALIGN
     off_in = _lib.PEER_FLAG_BYTES
     off_scr = off_in + cap
-    return off_in, off_scr, cap, off_scr + cap
+    return off_in, off_scr, cap, off_scr + cap + 3 * world * push_layout(max_numel, world)
 
 
-def choose_algo(nbytes: int, world: int, has_multicast: bool) -> int:
+def push_layout(max_numel: int, world: int) -> int:
+    """Bytes of one receive slot of the PUSH schedule (0 = not provisioned)."""
+    if world <= 1:
+        return 0
+    return min(-(-(max_numel * 2) // _ALIGN) * _ALIGN, PUSH_MAX_BYTES)
+
+
+def choose_algo(nbytes: int, world: int, has_multicast: bool, push_slot_bytes: int = 0) -> int:
     """The schedule `AUTO` resolves to (host arithmetic in the C library, no GPU needed)."""
-    return int(_lib.load().b200attn_peer_allreduce_algo(nbytes, world, int(bool(has_multicast))))
+    return int(_lib.load().b200attn_peer_allreduce_algo(nbytes, world, int(bool(has_multicast)), push_slot_bytes))
 
 
 class _RawCuda:
@@ -155,9 +164,11 @@ class PeerAllReduce:
         self.lib = _lib.load()
         self.mem = mem
         self.world, self.rank, self.max_numel = mem.world, mem.rank, max_numel
-        self.off_in, self.off_scr, self.cap, self.total = region_layout(max_numel)
+        self.off_in, self.off_scr, self.cap, self.total = region_layout(max_numel, mem.world)
         if mem.local.numel() < self.total:
-            raise ValueError("allocation smaller than region_layout(max_numel)")
+            raise ValueError("allocation smaller than region_layout(max_numel, world)")
+        self.push_slot_bytes = push_layout(max_numel, mem.world)
+        self.off_push = self.off_scr + self.cap
         self.local = mem.local
         self.base_ptrs = mem.base_ptrs
         self.multicast_ptr = mem.multicast_ptr
@@ -167,16 +178,28 @@ class PeerAllReduce:
         self._in = _ptr_array([p + self.off_in for p in self.base_ptrs])
         self._scr = _ptr_array([p + self.off_scr for p in self.base_ptrs])
         self._flags = _ptr_array(self.base_ptrs)
+        self._push = _ptr_array([p + self.off_push for p in self.base_ptrs]) if self.push_slot_bytes else None
         self._out_default = None
         self.last_algo = None
+        if self.push_slot_bytes:   # "not arrived" sentinel: bf16 -0.0 in every half word of the receive buffers
+            self.local[self.off_push: self.off_push + 3 * self.world * self.push_slot_bytes].view(torch.int16).fill_(-32768)
 
     @classmethod
     def create(cls, group=None, max_numel: int = 0, device=None, transport: str = "auto", **kw):
-        return cls(PeerMemory.create(group, region_layout(max_numel)[3], device, transport), max_numel, **kw)
+        import torch.distributed as dist
+        grp = group if group is not None else dist.group.WORLD
+        world = dist.get_world_size(grp)
+        ar = cls(PeerMemory.create(group, region_layout(max_numel, world)[3], device, transport), max_numel, **kw)
+        torch.cuda.synchronize()
+        dist.barrier(grp)            # every rank's receive buffers hold the sentinel before anyone pushes
+        return ar
 
     @classmethod
     def local_ranks(cls, world: int, max_numel: int, device="cuda", **kw):
-        return [cls(m, max_numel, **kw) for m in PeerMemory.local_ranks(world, region_layout(max_numel)[3], device)]
+        ars = [cls(m, max_numel, **kw)
+               for m in PeerMemory.local_ranks(world, region_layout(max_numel, world)[3], device)]
+        torch.cuda.synchronize()
+        return ars
 
     # ---- use ----------------------------------------------------------------------------------
     @property
@@ -210,10 +233,16 @@ class PeerAllReduce:
         n = x.numel()
         if n % 8 or n > self.max_numel:
             raise ValueError(f"numel {n}: multiple of 8, at most {self.max_numel}")
-        if x.data_ptr() != self.base_ptrs[self.rank] + self.off_in:
-            self.input(x.shape).copy_(x)
         if algo == _lib.AR_AUTO:
-            algo = choose_algo(2 * n, self.world, self.has_multicast)
+            algo = choose_algo(2 * n, self.world, self.has_multicast, self.push_slot_bytes)
+        in_ptrs = self._in
+        if algo == _lib.AR_PUSH:     # reads only the local input: any device memory, no staging copy
+            if x.data_ptr() != self.base_ptrs[self.rank] + self.off_in:
+                ptrs = [p + self.off_in for p in self.base_ptrs]
+                ptrs[self.rank] = x.data_ptr()
+                in_ptrs = _ptr_array(ptrs)
+        elif x.data_ptr() != self.base_ptrs[self.rank] + self.off_in:
+            self.input(x.shape).copy_(x)
         mc_in = mc_out = None
         if algo == _lib.AR_MULTIMEM:
             if not self.has_multicast:
@@ -228,7 +257,8 @@ class PeerAllReduce:
             res = out
         stream = torch.cuda.current_stream(x.device).cuda_stream
         _lib.check("b200attn_peer_allreduce", self.lib.b200attn_peer_allreduce(
-            self._in, self._scr, self._flags, res.data_ptr(), mc_in, mc_out, n, self.world, self.rank, algo,
+            in_ptrs, self._scr, self._flags, self._push, self.push_slot_bytes, res.data_ptr(), mc_in, mc_out, n,
+            self.world, self.rank, algo,
             self.max_blocks, self.timeout_ns, stream))
         self.last_algo = algo
         if algo == _lib.AR_MULTIMEM and out is not None:
