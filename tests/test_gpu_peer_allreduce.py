@@ -113,6 +113,18 @@ def test_peer_exchange_matches_replica_split_indexing(lib, R, batch):
     for ex, q in zip(exs, qs):
         ex.q.copy_(q.cuda())
     torch.cuda.synchronize()
+    # warm-up, phase by phase: the FIRST launch of a kernel loads its module, which can block the host behind a
+    # running kernel — with all 'ranks' driven by one host thread that would stall rank 1's launch behind rank 0's
+    # spinning kernel (a single-process artefact; real ranks have a host thread each)
+    for ex in exs:                                   # torch's own kernels first, with nothing spinning
+        ex.out_grp.copy_(ex.q_grp)
+        ex.out_grp.mul_(1)
+    torch.cuda.synchronize()
+    for phase in ("gather_q", "scatter_out"):
+        for ex, s in zip(exs, streams):
+            with torch.cuda.stream(s):
+                getattr(ex, phase)()
+        torch.cuda.synchronize()
     for it in range(2):
         for ex, s in zip(exs, streams):
             with torch.cuda.stream(s):
