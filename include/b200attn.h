@@ -284,7 +284,7 @@ B200ATTN_API int b200attn_gather_kv(
  *   out             local result. ONESHOT/TWOSHOT: any device pointer that no peer reads (it may
  *                   not alias peer_in). MULTIMEM: this rank's unicast view of the region `mc_out`
  *                   multicasts to.
- *   peer_push[r]    rank r's receive region of the PUSH schedule (or NULL array: PUSH unavailable):
+ *   peer_push[r]    rank r's receive region of the PUSH / PUSH2 schedules (or NULL array: unavailable):
  *                   3 x world x push_slot_bytes, filled ONCE with the bf16 pattern 0x8000 (-0.0, the
  *                   "not arrived" sentinel) before the first launch. PUSH reads its input only from
  *                   peer_in[rank], which may then be ANY local device pointer (no peer mapping needed).
@@ -303,6 +303,7 @@ B200ATTN_API int b200attn_gather_kv(
 #define B200ATTN_AR_TWOSHOT 2
 #define B200ATTN_AR_MULTIMEM 3
 #define B200ATTN_AR_PUSH 4
+#define B200ATTN_AR_PUSH2 5
 /* pure host arithmetic: the schedule AUTO resolves to for `bytes` of input on `world` ranks */
 B200ATTN_API int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_multicast,
                                                   int64_t push_slot_bytes);

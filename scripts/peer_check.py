@@ -66,13 +66,15 @@ def main():
             doc["transports"][tr] = {"unavailable": f"{type(e).__name__}: {str(e)[:400]}"}
             continue
         rec = {"multicast": ar.has_multicast, "algos": {}}
-        algos = [_lib.AR_PUSH, _lib.AR_ONESHOT, _lib.AR_TWOSHOT] + ([_lib.AR_MULTIMEM] if ar.has_multicast else [])
+        algos = [_lib.AR_PUSH, _lib.AR_PUSH2, _lib.AR_ONESHOT, _lib.AR_TWOSHOT] + ([_lib.AR_MULTIMEM] if ar.has_multicast else [])
         for algo in algos:
             name = peer.ALGO_NAMES[algo]
             arec = {"exact": True, "max_abs_err": 0.0, "us": {}}
             try:
                 for rows in ROWS:
                     if algo == _lib.AR_PUSH and 2 * rows * HIDDEN > ar.push_slot_bytes:
+                        continue
+                    if algo == _lib.AR_PUSH2 and 2 * rows * HIDDEN // world + 16 * world > ar.push_slot_bytes // 2:
                         continue
                     for it in range(2):
                         parts = inputs(world, rows, it)

@@ -35,13 +35,13 @@ def run_ranks(ars, xs, algo, repeats=1):
 
 
 @pytest.mark.parametrize("world", [1, 2, 4, 8])
-@pytest.mark.parametrize("algo", [_lib.AR_ONESHOT, _lib.AR_TWOSHOT, _lib.AR_PUSH])
+@pytest.mark.parametrize("algo", [_lib.AR_ONESHOT, _lib.AR_TWOSHOT, _lib.AR_PUSH, _lib.AR_PUSH2])
 @pytest.mark.parametrize("numel", [8, 8 * 37, 64 * 2048, 128 * 2048 + 24])
 def test_allreduce_matches_oracle_bit_exact(lib, world, algo, numel):
     g = torch.Generator().manual_seed(world * 1000 + numel)
     xs_cpu = [(torch.randn(numel, generator=g) * 3).to(torch.bfloat16) for _ in range(world)]
     ars = peer.PeerAllReduce.local_ranks(world, numel, timeout_s=5.0, max_blocks=16)
-    if algo == _lib.AR_PUSH and world == 1:
+    if algo in (_lib.AR_PUSH, _lib.AR_PUSH2) and world == 1:
         pytest.skip("PUSH needs peers")
     if numel > 64:                                  # -0.0 is the PUSH sentinel: inputs that contain it must still sum right
         for x in xs_cpu:

@@ -167,7 +167,9 @@ def test_peer_allreduce_schedule_choice_and_region_layout(lib, monkeypatch):
     assert peer.choose_algo(512 << 10, 2, False, 512 << 10) == _lib.AR_PUSH
     assert peer.choose_algo(512 << 10, 2, False, 256 << 10) == _lib.AR_ONESHOT      # slot too small
     assert peer.choose_algo(128 << 10, 8, False, 1 << 20) == _lib.AR_PUSH
-    assert peer.choose_algo(2 << 20, 8, False, 1 << 20) == _lib.AR_TWOSHOT          # 14 MiB of pushes: bandwidth-bound
+    assert peer.choose_algo(2 << 20, 8, False, 1 << 20) == _lib.AR_PUSH2            # 14 MiB of one-shot pushes: scatter-reduce instead
+    assert peer.choose_algo(1 << 20, 4, False, 1 << 20) == _lib.AR_PUSH2
+    assert peer.choose_algo(8 << 20, 8, False, 1 << 20) == _lib.AR_TWOSHOT          # a slice no longer fits half a slot
     assert peer.push_layout(128 * 2048, 1) == 0 and peer.push_layout(128 * 2048, 2) == 512 << 10
     assert peer.push_layout(1 << 22, 8) == peer.PUSH_MAX_BYTES
     assert peer.region_layout(128 * 2048, 2)[3] == peer.region_layout(128 * 2048)[3] + 3 * 2 * (512 << 10)

@@ -14,7 +14,7 @@ LIB_PATH = PKG_DIR / "libb200attn.so"
 
 ABI_VERSION = 7
 PEER_FLAG_BYTES = 8192
-AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH = 0, 1, 2, 3, 4
+AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH, AR_PUSH2 = 0, 1, 2, 3, 4, 5
 KV_BF16 = 0
 KV_FP8_E4M3 = 1
 VARIANT_AUTO = 0

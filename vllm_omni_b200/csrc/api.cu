@@ -835,9 +835,11 @@ int32_t b200attn_peer_allreduce_algo(int64_t bytes, int32_t world, int32_t has_m
   // Otherwise bytes crossing NVLink per rank: ONESHOT (world-1) x bytes, TWOSHOT 2 x (world-1)/world x bytes + one
   // more flag barrier: the same at world 2, so ONESHOT there; the crossover sits near 256 KiB at 4 and 8 ranks.
   if (world <= 1) return B200ATTN_AR_ONESHOT;
-  if (push_slot_bytes > 0 && bytes <= push_slot_bytes && (world - 1) * bytes <= (2 << 20) &&
-      env_flag("B200ATTN_AR_PUSH", true))
-    return B200ATTN_AR_PUSH;
+  if (push_slot_bytes > 0 && env_flag("B200ATTN_AR_PUSH", true)) {
+    if (bytes <= push_slot_bytes && (world - 1) * bytes <= (2 << 20)) return B200ATTN_AR_PUSH;
+    // PUSH2 needs the longest slice (<= bytes/world + 16 * world) to fit half a slot
+    if (world >= 4 && bytes / world + 16 * world <= push_slot_bytes / 2) return B200ATTN_AR_PUSH2;
+  }
   if (world <= 2) return B200ATTN_AR_ONESHOT;
   if (has_multicast && env_flag("B200ATTN_AR_MULTIMEM", false) && bytes >= (64 << 10)) return B200ATTN_AR_MULTIMEM;
   return bytes <= (256 << 10) ? B200ATTN_AR_ONESHOT : B200ATTN_AR_TWOSHOT;
@@ -857,16 +859,22 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
   if (algo == B200ATTN_AR_AUTO)
     algo = b200attn_peer_allreduce_algo(numel * 2, world, mc_in != nullptr && mc_out != nullptr,
                                         peer_push != nullptr ? push_slot_bytes : 0);
-  if (algo < B200ATTN_AR_ONESHOT || algo > B200ATTN_AR_PUSH) return fail(B200ATTN_EINVAL, "algo %d", algo);
+  if (algo < B200ATTN_AR_ONESHOT || algo > B200ATTN_AR_PUSH2) return fail(B200ATTN_EINVAL, "algo %d", algo);
   if (algo == B200ATTN_AR_TWOSHOT && peer_scratch == nullptr) return fail(B200ATTN_EINVAL, "TWOSHOT needs peer_scratch");
   if (algo == B200ATTN_AR_MULTIMEM && (mc_in == nullptr || mc_out == nullptr))
     return fail(B200ATTN_EINVAL, "MULTIMEM needs multicast addresses");
   if (algo == B200ATTN_AR_PUSH && (peer_push == nullptr || numel * 2 > push_slot_bytes))
     return fail(B200ATTN_EINVAL, "PUSH needs peer_push with slots of at least %lld bytes", (long long)(numel * 2));
+  const int64_t n_vec_all = numel / 8;
+  const int64_t longest_slice = n_vec_all - (world - 1) * (n_vec_all / world);
+  if (algo == B200ATTN_AR_PUSH2 && (peer_push == nullptr || world < 2 || longest_slice > push_slot_bytes / 32))
+    return fail(B200ATTN_EINVAL, "PUSH2 needs >= 2 ranks and peer_push slots of at least %lld bytes",
+                (long long)(longest_slice * 32));
+  const bool pushy = algo == B200ATTN_AR_PUSH || algo == B200ATTN_AR_PUSH2;
   PeerArgs a;
   memset(&a, 0, sizeof(a));
   for (int r = 0; r < world; ++r) {
-    const bool need_in = algo != B200ATTN_AR_PUSH || r == rank;  // PUSH reads only the local input
+    const bool need_in = !pushy || r == rank;  // PUSH / PUSH2 read only the local input
     if (peer_flags[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_flags[r]) % 16) ||
         (need_in && (peer_in[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_in[r]) % 16))))
       return fail(B200ATTN_EINVAL, "peer_in/peer_flags[%d] null or not 16-byte aligned", r);
@@ -877,7 +885,7 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
         return fail(B200ATTN_EINVAL, "peer_scratch[%d] null or not 16-byte aligned", r);
       a.scratch[r] = peer_scratch[r];
     }
-    if (algo == B200ATTN_AR_PUSH) {
+    if (pushy) {
       if (peer_push[r] == nullptr || (reinterpret_cast<uintptr_t>(peer_push[r]) % 16))
         return fail(B200ATTN_EINVAL, "peer_push[%d] null or not 16-byte aligned", r);
       a.push[r] = peer_push[r];
@@ -897,6 +905,8 @@ int b200attn_peer_allreduce(const void* const* peer_in, void* const* peer_scratc
   const bool whole = algo == B200ATTN_AR_ONESHOT || algo == B200ATTN_AR_PUSH;  // every rank touches every vector
   const int64_t per_rank = whole ? n_vec : n_vec - (world - 1) * (n_vec / world);
   if (max_blocks <= 0) max_blocks = 64;
+  if (pushy && reinterpret_cast<uintptr_t>(out) == reinterpret_cast<uintptr_t>(peer_in[rank]))
+    return fail(B200ATTN_EINVAL, "out may not alias the input");
   if (max_blocks > kPeerMaxBlocks) max_blocks = kPeerMaxBlocks;
   int64_t grid = (per_rank + kPeerThreads - 1) / kPeerThreads;
   if (grid < 1) grid = 1;

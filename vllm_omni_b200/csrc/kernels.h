@@ -109,7 +109,7 @@ constexpr int kPeerMaxRanks = 8;
 constexpr int kPeerMaxBlocks = 128;   // flag slots exist for this many blocks per launch
 constexpr int kPeerThreads = 512;
 constexpr size_t kPeerFlagBytes = 8192;  // >= (kPeerMaxBlocks * (kPeerMaxRanks + 1) + 8) * 4, 16-byte multiple
-constexpr int kPeerOneShot = 1, kPeerTwoShot = 2, kPeerMultimem = 3, kPeerPush = 4;
+constexpr int kPeerOneShot = 1, kPeerTwoShot = 2, kPeerMultimem = 3, kPeerPush = 4, kPeerPush2 = 5;
 struct PeerCtl {                   // who takes part in a flag barrier
   uint32_t* flags[kPeerMaxRanks];  // every rank's flag region (kPeerFlagBytes, zeroed once), index = rank
   int32_t world, rank;

@@ -18,6 +18,8 @@
 //             a 16-byte vector is complete when none of its halves is the sentinel. One posted NVLink write of
 //             latency instead of two flag round trips; three receive buffers rotate (step k uses k % 3 and
 //             re-arms the one of step k-1), so nothing is ever reset by the host. The input needs no peer mapping.
+//   PUSH2     the same idea for bandwidth-sized messages on 4/8 ranks: barrier-free reduce-scatter + all-gather
+//             (copies of slice p are posted to rank p, which adds them in rank order and posts the sum to all).
 //   MULTIMEM  NVLS: `multimem.ld_reduce` on the multicast address lets the NVSwitch add the replicas
 //             (fp32 accumulate), `multimem.st` broadcasts the sum; each rank handles slice r. Needs a
 //             multicast mapping of the allocation.
@@ -69,6 +71,14 @@ __device__ __forceinline__ uint32_t* error_of(uint32_t* flags) {
 // PUSH schedule state: {step, blocks done, vectors of the previous step, -}
 __device__ __forceinline__ uint32_t* push_state_of(uint32_t* flags) { return error_of(flags) + 4; }
 
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -80,9 +90,10 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
 
 // Block-wide barrier with the same-index block of every peer.
 //   fence = true : data written by this block before the barrier is visible to the peers after it
-//                  (fence.sys before the flag store = release, fence.sys after the spin = acquire; bar.sync
-//                  makes both cumulative over the block). A system-scope fence drains to NVLink and costs
-//                  microseconds, so it is paid only where a peer consumes what this launch produced.
+//                  (st.release.sys flag, one ld.acquire.sys once the flag is seen; bar.sync makes both
+//                  cumulative over the block). System-scope release/acquire drains to NVLink and costs
+//                  microseconds (measured: +3-4 us per barrier, two explicit fence.sys even more), so it is
+//                  paid only where a peer consumes what this launch produced.
 //   fence = false: control only, relaxed flag traffic. Enough (a) at kernel start, where the data the peers
 //                  read was completed by an EARLIER kernel of their stream (visible at kernel completion), and
 //                  (b) for "I have finished reading your buffer", where every load's value was consumed
@@ -92,8 +103,10 @@ __device__ __forceinline__ void peer_barrier(const PeerCtl& a, uint32_t& epoch, 
   epoch += 1;
   const int t = threadIdx.x;
   if (t < a.world) {
-    if (fence) __threadfence_system();
-    st_relaxed_sys(slot_of(a.flags[t], blockIdx.x, a.rank), epoch);
+    if (fence)
+      st_release_sys(slot_of(a.flags[t], blockIdx.x, a.rank), epoch);
+    else
+      st_relaxed_sys(slot_of(a.flags[t], blockIdx.x, a.rank), epoch);
     const uint32_t* mine = slot_of(a.flags[a.rank], blockIdx.x, t);
     const uint64_t t0 = globaltimer_ns();
     uint32_t spins = 0;
@@ -106,7 +119,7 @@ __device__ __forceinline__ void peer_barrier(const PeerCtl& a, uint32_t& epoch, 
         break;  // test mode: give up on this wait, the host reads the error words
       }
     }
-    if (fence) __threadfence_system();
+    if (fence) (void)ld_acquire_sys(mine);   // the spin saw the flag relaxed: one acquire load orders what follows
   }
   __syncthreads();
 }
@@ -209,14 +222,89 @@ __device__ __forceinline__ void st_peer_v4(void* p, const uint4& x) {
                : "memory");
 }
 
-// a.push[r] = rank r's receive region: [3 buffers][WORLD slots][slot_vec vectors]; slot s of a buffer holds
-// what rank s pushed. a.in[rank] is this rank's input (any device memory); a.out the local result.
+// a.push[r] = rank r's receive region: 3 rotating buffers of WORLD * slot_vec vectors each. Layout inside a buffer:
+//   PUSH  (kind 1): [WORLD slots][slot_vec]                       slot s = what rank s pushed (whole message)
+//   PUSH2 (kind 2): [A: WORLD slots][slot_vec/2] [B: WORLD slots][slot_vec/2]
+//                   A[s] = rank s's copy of MY slice (to be reduced here), B[s] = slice s already reduced by rank s
+// a.in[rank] is this rank's input (any device memory); a.out the local result.
+// State words (push_state_of): {step, blocks done, vectors of the previous step, kind of the previous step}.
+__device__ __forceinline__ int64_t slice_len(int64_t n_vec, int world, int r) {
+  const int64_t part = n_vec / world;
+  return r == world - 1 ? n_vec - part * (world - 1) : part;
+}
+
+// spin until the 16-byte vector at `src` (local memory a peer writes) holds no sentinel half
+__device__ __forceinline__ uint4 poll_vec(const PeerArgs& a, const uint4* src, uint64_t t0, int from, uint32_t step) {
+  uint32_t spins = 0;
+  uint4 v;
+  while (true) {
+    v = ld_peer_v4(src);
+    if (!vec_pending(v)) break;
+    if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > a.ctl.timeout_ns) {
+      uint32_t* e = error_of(a.ctl.flags[a.ctl.rank]);
+      e[0] = 2u; e[1] = blockIdx.x; e[2] = static_cast<uint32_t>(from); e[3] = step;
+      __threadfence_system();
+      if (!a.ctl.soft_timeout) __trap();
+      break;
+    }
+  }
+  return v;
+}
+
+// re-arm what the previous step received in buffer `prev` (all of it was consumed before that launch retired)
+template <int WORLD>
+__device__ __forceinline__ void push_rearm(uint4* mine, int prev, uint32_t kind, int64_t n_prev, int64_t slot_vec,
+                                           int rank, int64_t tid, int64_t stride) {
+  const uint4 sent = make_uint4(kSentinelWord, kSentinelWord, kSentinelWord, kSentinelWord);
+  uint4* buf = mine + static_cast<int64_t>(prev) * WORLD * slot_vec;
+  if (kind == 1u) {
+    for (int64_t i = tid; i < n_prev; i += stride) {
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r)
+        if (r != rank) buf[r * slot_vec + i] = sent;
+    }
+  } else if (kind == 2u) {
+    const int64_t cap = slot_vec / 2, part = n_prev / WORLD;
+    const int64_t my_len = slice_len(n_prev, WORLD, rank), longest = slice_len(n_prev, WORLD, WORLD - 1);
+    uint4* bufB = buf + WORLD * cap;
+    for (int64_t j = tid; j < longest; j += stride) {
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) {
+        if (r == rank) continue;
+        if (j < my_len) buf[r * cap + j] = sent;
+        if (j < (r == WORLD - 1 ? longest : part)) bufB[r * cap + j] = sent;
+      }
+    }
+  }
+}
+
+// the last block to finish advances the step (every block has read the state by then)
+__device__ __forceinline__ void push_advance(uint32_t* state, uint32_t step, int64_t n_vec, uint32_t kind) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t done = atomicAdd(state + 1, 1u);
+    if (done == gridDim.x - 1) {
+      state[1] = 0u;
+      state[2] = static_cast<uint32_t>(n_vec);
+      state[3] = kind;
+      state[0] = step + 1;
+      __threadfence();
+    }
+  }
+}
+
+__device__ __forceinline__ uint4 canon_vec(uint4 v) {
+  v.x = canon_word(v.x); v.y = canon_word(v.y); v.z = canon_word(v.z); v.w = canon_word(v.w);
+  return v;
+}
+
 template <int WORLD>
 __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_push_kernel(PeerArgs a, int64_t n_vec, int64_t slot_vec) {
   pdl_prologue();
   const int rank = a.ctl.rank;
   uint32_t* state = push_state_of(a.ctl.flags[rank]);
-  const uint32_t step = state[0];
+  const uint32_t step = state[0], prev_kind = state[3];
   const int64_t n_prev = state[2];
   const int cur = step % 3, prev = (step + 2) % 3;
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x;
@@ -225,60 +313,89 @@ __global__ void __launch_bounds__(kPeerThreads) peer_allreduce_push_kernel(PeerA
   uint4* mine = reinterpret_cast<uint4*>(a.push[rank]);
   // 1. push my vectors into slot `rank` of every peer's current buffer (posted writes, no round trip)
   for (int64_t i = tid; i < n_vec; i += stride) {
-    uint4 v = in[i];
-    v.x = canon_word(v.x); v.y = canon_word(v.y); v.z = canon_word(v.z); v.w = canon_word(v.w);
+    const uint4 v = canon_vec(in[i]);
 #pragma unroll
     for (int d = 1; d < WORLD; ++d) {
       const int p = (rank + d) % WORLD;
       st_peer_v4(reinterpret_cast<uint4*>(a.push[p]) + (static_cast<int64_t>(cur) * WORLD + rank) * slot_vec + i, v);
     }
   }
-  // 2. re-arm the buffer of the previous step (everything in it was consumed before that launch retired)
-  const uint4 sent = make_uint4(kSentinelWord, kSentinelWord, kSentinelWord, kSentinelWord);
-  for (int64_t i = tid; i < n_prev; i += stride) {
-#pragma unroll
-    for (int r = 0; r < WORLD; ++r)
-      if (r != rank) mine[(static_cast<int64_t>(prev) * WORLD + r) * slot_vec + i] = sent;
-  }
+  // 2. re-arm the buffer of the previous step
+  push_rearm<WORLD>(mine, prev, prev_kind, n_prev, slot_vec, rank, tid, stride);
   // 3. wait for the peers' vectors to land in my current buffer, add in rank order
   const uint64_t t0 = globaltimer_ns();
   for (int64_t i = tid; i < n_vec; i += stride) {
     uint4 v[WORLD];
     v[rank] = in[i];
 #pragma unroll
-    for (int r = 0; r < WORLD; ++r) {
-      if (r == rank) continue;
-      const uint4* src = mine + (static_cast<int64_t>(cur) * WORLD + r) * slot_vec + i;
-      uint32_t spins = 0;
-      while (true) {
-        v[r] = ld_peer_v4(src);
-        if (!vec_pending(v[r])) break;
-        if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > a.ctl.timeout_ns) {
-          uint32_t* e = error_of(a.ctl.flags[rank]);
-          e[0] = 2u; e[1] = blockIdx.x; e[2] = static_cast<uint32_t>(r); e[3] = step;
-          __threadfence_system();
-          if (!a.ctl.soft_timeout) __trap();
-          break;
-        }
-      }
-    }
+    for (int r = 0; r < WORLD; ++r)
+      if (r != rank) v[r] = poll_vec(a, mine + (static_cast<int64_t>(cur) * WORLD + r) * slot_vec + i, t0, r, step);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int r = 0; r < WORLD; ++r) acc_bf16x8(acc, v[r]);
     reinterpret_cast<uint4*>(a.out)[i] = pack_bf16x8(acc);
   }
-  // 4. the last block to finish advances the step (every block has read it by then)
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    const uint32_t done = atomicAdd(state + 1, 1u);
-    if (done == gridDim.x - 1) {
-      state[1] = 0u;
-      state[2] = static_cast<uint32_t>(n_vec);
-      state[0] = step + 1;
-      __threadfence();
+  push_advance(state, step, n_vec, 1u);
+}
+
+// PUSH2: barrier-free reduce-scatter + all-gather. Rank r owns slice r: every rank posts its copy of slice p
+// to rank p (A slots), rank p adds the copies in rank order and posts the sum to everybody (B slots). Two posted
+// writes of latency, 2 (world-1)/world of the bytes per rank on the wire; no flags, no fences.
+template <int WORLD>
+__global__ void __launch_bounds__(kPeerThreads) peer_allreduce_push2_kernel(PeerArgs a, int64_t n_vec, int64_t slot_vec) {
+  pdl_prologue();
+  const int rank = a.ctl.rank;
+  uint32_t* state = push_state_of(a.ctl.flags[rank]);
+  const uint32_t step = state[0], prev_kind = state[3];
+  const int64_t n_prev = state[2];
+  const int cur = step % 3, prev = (step + 2) % 3;
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * kPeerThreads + threadIdx.x;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kPeerThreads;
+  const int64_t cap = slot_vec / 2, part = n_vec / WORLD;
+  const int64_t my_len = slice_len(n_vec, WORLD, rank), longest = slice_len(n_vec, WORLD, WORLD - 1);
+  const int64_t buf_off = static_cast<int64_t>(cur) * WORLD * slot_vec;
+  const uint4* in = reinterpret_cast<const uint4*>(a.in[rank]);
+  uint4* out = reinterpret_cast<uint4*>(a.out);
+  uint4* mine = reinterpret_cast<uint4*>(a.push[rank]);
+  // 1. scatter: my copy of slice p goes to A[rank] of rank p
+  for (int64_t j = tid; j < longest; j += stride) {
+#pragma unroll
+    for (int d = 1; d < WORLD; ++d) {
+      const int p = (rank + d) % WORLD;
+      if (j < (p == WORLD - 1 ? longest : part))
+        st_peer_v4(reinterpret_cast<uint4*>(a.push[p]) + buf_off + rank * cap + j, canon_vec(in[p * part + j]));
     }
   }
+  push_rearm<WORLD>(mine, prev, prev_kind, n_prev, slot_vec, rank, tid, stride);
+  // 2. reduce my slice in rank order, keep it and post it to B[rank] of every peer
+  const uint64_t t0 = globaltimer_ns();
+  for (int64_t j = tid; j < my_len; j += stride) {
+    uint4 v[WORLD];
+    v[rank] = in[rank * part + j];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      if (r != rank) v[r] = poll_vec(a, mine + buf_off + r * cap + j, t0, r, step);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) acc_bf16x8(acc, v[r]);
+    const uint4 sum = canon_vec(pack_bf16x8(acc));  // a sum that starts from +0 is never -0: canon is a no-op kept for safety
+    out[rank * part + j] = sum;
+#pragma unroll
+    for (int d = 1; d < WORLD; ++d) {
+      const int p = (rank + d) % WORLD;
+      st_peer_v4(reinterpret_cast<uint4*>(a.push[p]) + buf_off + WORLD * cap + rank * cap + j, sum);
+    }
+  }
+  // 3. gather: the other slices arrive reduced in B[r]
+  for (int64_t j = tid; j < longest; j += stride) {
+#pragma unroll
+    for (int d = 1; d < WORLD; ++d) {
+      const int r = (rank + d) % WORLD;
+      if (j < (r == WORLD - 1 ? longest : part))
+        out[r * part + j] = poll_vec(a, mine + buf_off + WORLD * cap + r * cap + j, t0, r, step);
+    }
+  }
+  push_advance(state, step, n_vec, 2u);
 }
 
 // NVLS: the switch reduces. mc_in / mc_out are MULTICAST addresses of the input / output regions;
@@ -334,6 +451,14 @@ static cudaError_t launch_push(const PeerArgs& a, int64_t n_vec, int grid, bool 
 }
 
 cudaError_t launch_peer_allreduce(const PeerArgs& a, int64_t n_vec, int algo, int grid, bool pdl, cudaStream_t stream) {
+  if (algo == kPeerPush2) {
+    switch (a.ctl.world) {
+      case 2: return peer_launch(peer_allreduce_push2_kernel<2>, grid, pdl, stream, a, n_vec, a.push_slot_vec);
+      case 4: return peer_launch(peer_allreduce_push2_kernel<4>, grid, pdl, stream, a, n_vec, a.push_slot_vec);
+      case 8: return peer_launch(peer_allreduce_push2_kernel<8>, grid, pdl, stream, a, n_vec, a.push_slot_vec);
+      default: return cudaErrorInvalidValue;
+    }
+  }
   if (algo == kPeerPush) {
     switch (a.ctl.world) {
       case 1: return launch_push<1>(a, n_vec, grid, pdl, stream);

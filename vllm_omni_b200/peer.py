@@ -22,7 +22,7 @@ import torch
 from . import _lib
 
 ALGO_NAMES = {_lib.AR_AUTO: "auto", _lib.AR_ONESHOT: "oneshot", _lib.AR_TWOSHOT: "twoshot",
-              _lib.AR_MULTIMEM: "multimem", _lib.AR_PUSH: "push"}
+              _lib.AR_MULTIMEM: "multimem", _lib.AR_PUSH: "push", _lib.AR_PUSH2: "push2"}
 PUSH_MAX_BYTES = 1 << 20      # largest message the PUSH schedule is provisioned for (per slot)
 _ALIGN = 256
 
@@ -236,7 +236,7 @@ class PeerAllReduce:
         if algo == _lib.AR_AUTO:
             algo = choose_algo(2 * n, self.world, self.has_multicast, self.push_slot_bytes)
         in_ptrs = self._in
-        if algo == _lib.AR_PUSH:     # reads only the local input: any device memory, no staging copy
+        if algo in (_lib.AR_PUSH, _lib.AR_PUSH2):     # read only the local input: any device memory, no staging copy
             if x.data_ptr() != self.base_ptrs[self.rank] + self.off_in:
                 ptrs = [p + self.off_in for p in self.base_ptrs]
                 ptrs[self.rank] = x.data_ptr()
