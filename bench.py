@@ -75,37 +75,52 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled every 100 ms while the timed region runs."""
+    """nvidia-smi clocks/throttle reasons sampled every 100 ms while the step runs back to back: started before the
+    warm-up (nvidia-smi needs up to a second before its first line, longer than a short timed region), read by a
+    thread, stopped right after the timed region. `count()` = lines so far."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.proc = index, None
+        self.index, self.proc, self.lines, self.thread = index, None, [], None
 
     def __enter__(self):
+        import threading
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                  "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
+            return self
+
+        def pump():
+            for line in self.proc.stdout:
+                self.lines.append(line)
+
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
         return self
+
+    def count(self) -> int:
+        return len(self.lines)
 
     def __exit__(self, *exc):
         self.result = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.proc is None:
             return
-        time.sleep(0.15)
+        time.sleep(0.12)
         self.proc.terminate()
         try:
-            out, _ = self.proc.communicate(timeout=5)
+            self.proc.wait(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-            out, _ = self.proc.communicate()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
         sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
+        for line in list(self.lines):
             f = [x.strip() for x in line.split(",")]
             if len(f) < 7:
                 continue
@@ -118,7 +133,8 @@ class ClockSampler:
                     reasons.add(n)
         if sm:
             self.result = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw),
-                           "reasons": sorted(reasons), "samples": len(sm)}
+                           "reasons": sorted(reasons), "samples": len(sm),
+                           "window": "last warm-up steps + timed region (the same step replayed back to back)"}
 
 
 T0 = time.perf_counter()
@@ -376,11 +392,24 @@ def run_b200(args, wl):
     g_step = capture(step)
     log(f"step {'captured' if g_step is not None else 'NOT captured (eager)'}")
     run_step = g_step.replay if g_step is not None else step
-    for _ in range(max(args.warmup, 3)):
-        run_step()
-    barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
+        for _ in range(max(args.warmup, 3)):
+            run_step()
+        # keep the load on until rank 0's sampler has its first line (every rank runs the same number of extra
+        # steps: the steps contain collectives), at most ~4 s
+        t_lim = time.perf_counter() + 4.0
+        while True:
+            need = torch.tensor([1 if (rank == 0 and clk.proc is not None and clk.count() == 0
+                                       and time.perf_counter() < t_lim) else 0], device="cuda")
+            if world > 1:
+                import torch.distributed as dist
+                dist.broadcast(need, 0)
+            if int(need.item()) == 0:
+                break
+            for _ in range(8):
+                run_step()
+        barrier(world)
         e0.record()
         for _ in range(args.steps):
             run_step()
@@ -504,18 +533,29 @@ def run_e2e(args, wl, inp, B, hq, hkv, d, L, splits, ws, world, global_batch, rs
     qkv_dev = torch.cat([inp.q.reshape(B, -1), inp.new_k.reshape(B, -1), inp.new_v.reshape(B, -1)], dim=1)
     host_qkv = [qkv_dev.cpu().pin_memory() for _ in range(L)]
     host_out = [torch.empty(B, hq * d, dtype=torch.bfloat16).pin_memory() for _ in range(L)]
+    # one step = H2D of every layer's q/k/v + the layer kernels + D2H of every layer's output; replayed as a CUDA
+    # graph with the copies as graph nodes (how vLLM replays decode), eager launches if capture fails / --no-graph
+    run_step, mode = (lambda: runner.step(host_qkv, host_out)), "eager"
+    if not args.no_graph:
+        try:
+            g = runner.capture(host_qkv, host_out)
+            run_step, mode = g.replay, "cuda-graph replay (H2D/D2H copy nodes inside)"
+        except Exception as ex:  # noqa: BLE001
+            print(f"[bench] e2e graph capture failed ({type(ex).__name__}: {ex}); eager", file=sys.stderr)
+            torch.cuda.synchronize()
     for _ in range(3):
-        runner.step(host_qkv, host_out)
+        run_step()
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        runner.step(host_qkv, host_out)
+        run_step()
     e1.record()
     torch.cuda.synchronize()
     ms = max_over_ranks(e0.elapsed_time(e1), world) / args.steps
     return {"value": global_batch / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
             "h2d_bytes_per_step": runner.h2d_bytes_per_layer * L, "d2h_bytes_per_step": runner.d2h_bytes_per_layer * L,
+            "launch_mode": mode,
             "api": "B200AttentionImpl.do_kv_cache_update + forward via HostStepRunner (pinned host q/k/v in, output out)"}
 
 

@@ -6,6 +6,11 @@ per layer, the step's q/k/v arrive in pinned host memory, are copied to the devi
 (vllm/model_executor/layers/attention/attention.py:509-528), and the attention output is copied back
 to pinned host memory. Copies run on their own streams, double-buffered, so layer l+1's H2D and layer
 l-1's D2H overlap layer l's kernels.
+
+`capture()` records one whole step — the H2D copies, every kernel and the D2H copies, on all three
+streams — into a CUDA graph bound to the caller's pinned staging buffers, the way vLLM replays decode
+steps (persistent input buffers + FULL cudagraphs, `qwen3_omni_moe.yaml:20`): `replay()` then costs one
+launch on the host, and the copies are still part of every step.
 """
 from __future__ import annotations
 
@@ -74,3 +79,16 @@ class HostStepRunner:
                 out_free[b].record(self.s_out)
         cur.wait_stream(self.s_out)
         cur.wait_stream(self.s_in)
+
+    def capture(self, host_qkv: list[torch.Tensor], host_out: list[torch.Tensor]) -> torch.cuda.CUDAGraph:
+        """One step over these pinned buffers as a CUDA graph (copy nodes included). Refill `host_qkv`
+        in place between replays; results land in `host_out` when the replay's stream work completes."""
+        for t in (*host_qkv, *host_out):
+            if not t.is_pinned():
+                raise ValueError("capture() needs pinned host buffers (their addresses are baked into the graph)")
+        self.step(host_qkv, host_out)       # lazy initialisation (tensor maps, workspaces) outside the capture
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self.step(host_qkv, host_out)
+        return graph
