@@ -13,6 +13,16 @@ pytestmark = pytest.mark.gpu
 TOL = 2e-3
 
 
+@pytest.fixture(autouse=True, params=["mma_sync", "umma"])
+def prefill_kernel(request, monkeypatch):
+    """Every case runs on both prefill kernels: the mma.sync one (paged_prefill.cu) and the tcgen05 / TMEM one
+    (paged_prefill_umma.cu, bf16 caches). The library reads the switch at every call."""
+    if request.param == "umma" and request.node.callspec.params.get("fp8", False):
+        pytest.skip("fp8 caches are served by the mma.sync kernel")
+    monkeypatch.setenv("B200ATTN_PREFILL_UMMA", "1" if request.param == "umma" else "0")
+    return request.param
+
+
 def run_prefill(c, q_lens, hq, seed=0, q_std=1.0):
     g = torch.Generator().manual_seed(seed)
     T = sum(q_lens)

@@ -14,6 +14,8 @@ namespace {
 
 thread_local char g_err[512] = "";
 
+constexpr bool kPrefillUmmaDefault = false;  // flipped once the tcgen05 prefill kernel is parity-green on the GPU
+
 int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -158,12 +160,16 @@ int get_kv_map(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, 
 // box = 64 x 16 x 2 x 1 x 1: one 16-token x 128-dim tile per op, landing as two 2 KiB halves of
 // SWIZZLE_128B rows — the layout the math reads with ldmatrix.
 thread_local KvMapEntry g_maps5[kMapCache];
+thread_local KvMapEntry g_maps5h[kMapCache];  // bf16, box of ONE 64-element half (UMMA operand staging)
 
+// box_halves = 2: one op moves both 64-element halves of a 16-token tile (4 KiB, the layout ldmatrix reads);
+// box_halves = 1: one op moves one half (2 KiB), so a kernel can place the halves of many tiles into two
+// [tokens][128 B] regions — the SWIZZLE_128B operand layout tcgen05.mma descriptors describe.
 int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv, int32_t bs, bool fp8,
-                const CUtensorMap** out_map) {
-  KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, fp8 ? 1 : 0};
+                const CUtensorMap** out_map, int box_halves = 2) {
+  KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, fp8 ? 1 : (box_halves == 1 ? 2 : 0)};
   const size_t slot = (reinterpret_cast<uintptr_t>(ptr) >> 8) % kMapCache;
-  KvMapEntry& e = g_maps5[slot];
+  KvMapEntry& e = (box_halves == 1 ? g_maps5h : g_maps5)[slot];
   if (e.valid && e.key == key) {
     *out_map = &e.map;
     return 0;
@@ -199,7 +205,7 @@ int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb,
   cuuint64_t gdim[5] = {64, static_cast<cuuint64_t>(bs), 2, static_cast<cuuint64_t>(hkv), static_cast<cuuint64_t>(nb)};
   cuuint64_t gstr[4] = {static_cast<cuuint64_t>(st_slot), 128, static_cast<cuuint64_t>(st_head),
                         static_cast<cuuint64_t>(st_block)};
-  cuuint32_t box[5] = {64, static_cast<cuuint32_t>(kTileTokens), 2, 1, 1};
+  cuuint32_t box[5] = {64, static_cast<cuuint32_t>(kTileTokens), static_cast<cuuint32_t>(box_halves), 1, 1};
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = enc(&e.map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), gdim, gstr, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -773,15 +779,18 @@ int b200attn_paged_prefill(const void* q, int64_t q_stride_tok, const void* k_ca
   p.k_scale = k_scale;
   p.v_scale = v_scale;
   p.scale_stride = scale_numel > 1 ? 1 : 0;
+  // bf16 caches: the tcgen05 / TMEM kernel (B200ATTN_PREFILL_UMMA=0 selects the mma.sync kernel, which also serves fp8)
+  const bool umma = !fp8 && env_flag("B200ATTN_PREFILL_UMMA", kPrefillUmmaDefault);
   const CUtensorMap *mk = nullptr, *mv = nullptr;
   if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks, num_kv_heads,
-                           block_size, fp8, &mk))
+                           block_size, fp8, &mk, umma ? 1 : 2))
     return rc;
   const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
   if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks, num_kv_heads,
-                           block_size, fp8, &mv))
+                           block_size, fp8, &mv, umma ? 1 : 2))
     return rc;
-  cudaError_t e = launch_paged_prefill(tm_k, *mv, p, fp8, static_cast<cudaStream_t>(stream));
+  cudaError_t e = umma ? launch_paged_prefill_umma(tm_k, *mv, p, static_cast<cudaStream_t>(stream))
+                       : launch_paged_prefill(tm_k, *mv, p, fp8, static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "paged_prefill launch");
 }
 

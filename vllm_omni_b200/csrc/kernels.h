@@ -51,6 +51,9 @@ struct PrefillParams {
 cudaError_t launch_paged_prefill(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const PrefillParams& p, bool fp8,
                                  cudaStream_t stream);
 size_t prefill_smem_bytes(bool fp8);
+cudaError_t launch_paged_prefill_umma(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const PrefillParams& p,
+                                      cudaStream_t stream);
+size_t prefill_umma_smem_bytes();
 
 struct CacheWriteParams {
   const __nv_bfloat16* key;
