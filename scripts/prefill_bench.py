@@ -3,6 +3,7 @@
 TFLOP/s counted as 4 * d * Hq * (number of attended (query, key) pairs); FlashAttention's paged varlen
 call on the same memory as the comparator. One JSON line per case and implementation."""
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -24,7 +25,7 @@ def pairs(S, n):
     return n * (S - n) + n * (n + 1) // 2
 
 
-for fp8 in (False, True):
+for fp8 in ((False,) if "--bf16-only" in sys.argv else (False, True)):
     for name, seqs in CASES:
         B = len(seqs)
         lens = torch.tensor([s for s, _ in seqs], dtype=torch.int32)
@@ -61,7 +62,17 @@ for fp8 in (False, True):
                                    max_seqlen_k=int(lens.max()), seqused_k=lens_d, softmax_scale=D ** -0.5,
                                    causal=True, block_table=bt_d, out=out2, fa_version=ver)
 
-        impls = [("b200attn paged_prefill", ours)]
+        def ours_umma():
+            os.environ["B200ATTN_PREFILL_UMMA"] = "1"
+            try:
+                ours()
+            finally:
+                os.environ["B200ATTN_PREFILL_UMMA"] = "0"
+
+        os.environ["B200ATTN_PREFILL_UMMA"] = "0"
+        impls = [("b200attn paged_prefill (mma.sync)", ours)]
+        if not fp8:
+            impls.append(("b200attn paged_prefill (tcgen05/TMEM)", ours_umma))
         if not fp8:
             out2 = torch.empty_like(q)
             for ver in (2, 4):
@@ -80,7 +91,7 @@ for fp8 in (False, True):
                     a.record(); fn(); b_.record(); torch.cuda.synchronize()
                     ts.append(a.elapsed_time(b_))
                 ms = sorted(ts)[2]
-                res = out if fn is ours else out2
+                res = out if fn in (ours, ours_umma) else out2
                 if ref is None:
                     ref = res.float().clone()
                 print(json.dumps({"case": name, "kv": "fp8" if fp8 else "bf16", "impl": iname, "ms": round(ms, 3),

@@ -14,7 +14,7 @@ namespace {
 
 thread_local char g_err[512] = "";
 
-constexpr bool kPrefillUmmaDefault = false;  // flipped once the tcgen05 prefill kernel is parity-green on the GPU
+constexpr bool kPrefillUmmaDefault = true;  // parity-green on B200 (tests/test_gpu_prefill.py runs both kernels)
 
 int fail(int code, const char* fmt, ...) {
   va_list ap;

@@ -11,8 +11,9 @@
 //                                            the softmax threads in the swizzled K-major layout), B = V MN-major
 // K/V pages are staged by TMA straight into the SWIZZLE_128B layout the UMMA descriptors describe (two boxes of
 // 64 d x 16 tokens per page, one per 128-byte half of the head dimension), two stages of 64 KiB. S is double-
-// buffered in TMEM (2 x 128 columns) so Q.K^T of block j+1 runs under the softmax of block j; O lives in 128
-// more columns and is rescaled in TMEM only when a row maximum grows by more than 2^kTau (lazy rescale).
+// buffered in TMEM (2 x 128 columns) and P in shared memory, so Q.K^T of block j+1 and P.V of block j-1 run under
+// the softmax of block j; O lives in 128 more columns and is rescaled in TMEM only when a row maximum grows by
+// more than 2^kTau (lazy rescale).
 //
 // Warp roles (192 threads): warps 0-3 softmax / correction / epilogue (warp w touches TMEM lanes 32w..32w+31),
 // warp 4 TMA producer, warp 5 TMEM allocation + single-thread MMA issue.
@@ -33,14 +34,14 @@ constexpr uint32_t kUpTmemCols = 512;  // S0 | S1 | O | (unused): power of two
 
 struct UpSmem {
   alignas(1024) uint8_t q[2][kUpHalf];             // A of Q.K^T: [d half][row][64 d]
-  alignas(1024) uint8_t p[2][kUpHalf];             // A of P.V:   [token half][row][64 tokens]
+  alignas(1024) uint8_t p[2][2][kUpHalf];          // A of P.V, double-buffered: [buffer][token half][row][64 tokens]
   alignas(1024) uint8_t k[kUpStages][2][kUpHalf];  // B of Q.K^T: [d half][token][64 d]
   alignas(1024) uint8_t v[kUpStages][2][kUpHalf];  // B of P.V (MN-major): [d half][token][64 d]
   alignas(8) uint64_t kv_full[kUpStages];
   alignas(8) uint64_t kv_empty[kUpStages];
   alignas(8) uint64_t s_full[2];
   alignas(8) uint64_t p_full;
-  alignas(8) uint64_t pv_done;
+  alignas(8) uint64_t pv_done[2];  // P.V of block j has completed: barrier j & 1 (never more than one phase ahead of a waiter)
   uint32_t tmem_base;
 };
 
@@ -95,7 +96,8 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       mbar_init(&sm.s_full[s], 1);
     }
     mbar_init(&sm.p_full, 128);
-    mbar_init(&sm.pv_done, 1);
+    mbar_init(&sm.pv_done[0], 1);
+    mbar_init(&sm.pv_done[1], 1);
     fence_barrier_init();
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
@@ -157,7 +159,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     if (lane == 0) {
       constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);
-      const uint32_t q_addr = smem_u32(&sm.q[0][0]), p_addr = smem_u32(&sm.p[0][0]);
+      const uint32_t q_addr = smem_u32(&sm.q[0][0]);
       auto issue_qk = [&](int j) {
         const int st = j & 1;
         mbar_wait(&sm.kv_full[st], (j >> 1) & 1);
@@ -176,7 +178,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
         if (j + 1 < nblk) issue_qk(j + 1);
         mbar_wait(&sm.p_full, j & 1);
         tc_fence_after_sync();
-        const uint32_t v_addr = smem_u32(&sm.v[j & 1][0][0]);
+        const uint32_t v_addr = smem_u32(&sm.v[j & 1][0][0]), p_addr = smem_u32(&sm.p[j & 1][0][0]);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {  // KV tokens 16 kk .. 16 kk + 15
           const uint64_t da = umma_desc_sw128(p_addr + (kk >> 2) * kUpHalf + (kk & 3) * 32, 16, 1024);
@@ -186,7 +188,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
                          idesc_pv, j > 0 || kk > 0);
         }
         umma_commit(&sm.kv_empty[j & 1]);
-        umma_commit(&sm.pv_done);
+        umma_commit(&sm.pv_done[j & 1]);
       }
     }
   } else {
@@ -197,56 +199,64 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
     const float scale = p.scale_log2;
     float m = -CUDART_INF_F, l = 0.f;
-    uint32_t x[32];
     for (int j = 0; j < nblk; ++j) {
       const int st = j & 1;
       const uint32_t tm_s = tm_s0 + st * 128 + lane_off;
       const int t_base = j * kUpBlk;
       const int lim = row_ok ? min(kv_end, pos + 1) - t_base : 0;  // columns [0, lim) of this block are visible
+      const bool full = __all_sync(0xffffffffu, lim >= kUpBlk);    // no mask anywhere in this warp's rows
       mbar_wait(&sm.s_full[st], (j >> 1) & 1);
       tc_fence_after_sync();
-      // ---- pass 1: row maximum of the visible scores
+      // ---- the row's 128 scores: four TMEM loads in flight, one wait
+      uint32_t x[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld32(tm_s + c * 32, x[c]);
+      tmem_ld_wait();
       float mx = -CUDART_INF_F;
+      if (full) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld32(tm_s + c * 32, x);
-        tmem_ld_wait();
+        for (int c = 0; c < 4; ++c)
 #pragma unroll
-        for (int e = 0; e < 32; ++e)
-          if (c * 32 + e < lim) mx = fmaxf(mx, __uint_as_float(x[e]) * scale);
+          for (int e = 0; e < 32; ++e) mx = fmaxf(mx, __uint_as_float(x[c][e]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int e = 0; e < 32; ++e)
+            if (c * 32 + e < lim) mx = fmaxf(mx, __uint_as_float(x[c][e]));
       }
+      mx *= scale;  // scale > 0: max commutes with it
       const bool grow = mx > m + kTau;  // also the first visible block (m = -inf)
       const float m_new = grow ? mx : m;
       const float alpha = (grow && m != -CUDART_INF_F) ? fast_exp2(m - m_new) : 1.f;
       m = m_new;
       const float mu = (m == -CUDART_INF_F) ? 0.f : m;
-      // ---- P(j-1).V must have been consumed before P, V tail rows or O are touched
-      if (j > 0) {
-        mbar_wait(&sm.pv_done, (j - 1) & 1);
-        tc_fence_after_sync();
-      }
-      // ---- pass 2: P = exp2(S * scale - m) as bf16 into the swizzled A-operand layout; row sum
+      // ---- this P buffer was last read by P.V of block j - 2
+      if (j >= 2) mbar_wait(&sm.pv_done[st], ((j >> 1) - 1) & 1);
+      // ---- P = exp2(S * scale - m) as bf16 into the swizzled A-operand layout; row sum
       float sum = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        tmem_ld32(tm_s + c * 32, x);
-        tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
-          const float p0 = (c * 32 + e < lim) ? fast_exp2(fmaf(__uint_as_float(x[e]), scale, -mu)) : 0.f;
-          const float p1 = (c * 32 + e + 1 < lim) ? fast_exp2(fmaf(__uint_as_float(x[e + 1]), scale, -mu)) : 0.f;
+          float p0 = fast_exp2(fmaf(__uint_as_float(x[c][e]), scale, -mu));
+          float p1 = fast_exp2(fmaf(__uint_as_float(x[c][e + 1]), scale, -mu));
+          if (!full) {
+            if (c * 32 + e >= lim) p0 = 0.f;
+            if (c * 32 + e + 1 >= lim) p1 = 0.f;
+          }
           sum += p0 + p1;
           pk[e >> 1] = pack_bf16x2(p0, p1);
         }
-        uint8_t* prow = &sm.p[c >> 1][r * 128];
+        uint8_t* prow = &sm.p[st][c >> 1][r * 128];
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4)
           *reinterpret_cast<uint4*>(prow + ((((c & 1) * 4 + q4) ^ (r & 7)) << 4)) =
               make_uint4(pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2], pk[4 * q4 + 3]);
       }
       l = l * alpha + sum;
-      // ---- V rows past the end of the sequence hold whatever the page (or the previous block) held: zero them so
+      // ---- V rows past the end of the sequence hold whatever the page (or an earlier block) held: zero them so
       // that 0 x NaN cannot reach O (thread r owns token row r of the block)
       if (t_base + kUpBlk > kv_end && t_base + r >= kv_end) {
 #pragma unroll
@@ -256,15 +266,20 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
           for (int c = 0; c < 8; ++c) vr[c] = make_uint4(0u, 0u, 0u, 0u);
         }
       }
-      // ---- lazy rescale of O in TMEM (warp-uniform: tcgen05.ld/st are warp-wide)
+      // ---- lazy rescale of O in TMEM (warp-uniform: tcgen05.ld/st are warp-wide); needs P.V of block j - 1 done
       if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+        mbar_wait(&sm.pv_done[st ^ 1], ((j - 1) >> 1) & 1);
+        tc_fence_after_sync();
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          tmem_ld32(tm_o + lane_off + c * 32, x);
-          tmem_ld_wait();
+          tmem_ld32(tm_o + lane_off + c * 32, x[c]);
+        }
+        tmem_ld_wait();
 #pragma unroll
-          for (int e = 0; e < 32; ++e) x[e] = __float_as_uint(__uint_as_float(x[e]) * alpha);
-          tmem_st32(tm_o + lane_off + c * 32, x);
+        for (int c = 0; c < 4; ++c) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) x[c][e] = __float_as_uint(__uint_as_float(x[c][e]) * alpha);
+          tmem_st32(tm_o + lane_off + c * 32, x[c]);
         }
         tmem_st_wait();
       }
@@ -272,10 +287,11 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       tc_fence_before_sync();
       mbar_arrive(&sm.p_full);
     }
+    uint32_t x[32];
     // ---- epilogue: O / l -> bf16 -> global (256 contiguous bytes per row)
     const float inv = l > 0.f ? 1.f / l : 0.f;
     if (nblk > 0) {
-      mbar_wait(&sm.pv_done, (nblk - 1) & 1);
+      mbar_wait(&sm.pv_done[(nblk - 1) & 1], ((nblk - 1) >> 1) & 1);
       tc_fence_after_sync();
     }
     const int h = kvh * p.group + sub * kUpHeads + hh;
