@@ -1,47 +1,53 @@
 // Causal varlen attention over the paged KV cache on the 5th-generation tensor cores (tcgen05 / UMMA,
-// accumulators in TMEM) — the "dense enough to pay off" case of GQA query-group packing: a CTA owns 16 query
-// tokens x the 8 query heads of one KV head = 128 rows, exactly one M = 128 UMMA tile with no padding at G = 8
-// (the mma.sync kernel in paged_prefill.cu stays the path for FP8 caches and is the comparison point).
+// accumulators in TMEM) — the "dense enough to pay off" case of GQA query-group packing: 16 query tokens x the
+// 8 query heads of one KV head = 128 rows are exactly one M = 128 UMMA tile with no padding at G = 8, and a CTA
+// owns TWO such tiles (32 consecutive query tokens) that share every staged K/V block, which halves the L2 -> SM
+// traffic that bounded the one-tile version (measured 408 TFLOP/s at 3.1 TB/s of L2 reads).
+// The mma.sync kernel in paged_prefill.cu stays the path for FP8 caches and is the comparison point.
 // Same call as paged_prefill.cu (vllm/v1/attention/backends/flash_attn.py:758-819 with max_query_len > 1).
 //
-// Per KV block of 128 tokens (8 pages of 16):
-//   S[128 x 128]  = Q[128 x 128d] . K^T      8 x tcgen05.mma m128 n128 k16, A and B K-major from shared memory
-//   P = exp2(S * scale - m) (causal / tail masked), row statistics in registers: thread r owns row r (TMEM lane r)
-//   O[128 x 128d] += P[128 x 128] . V        16 x tcgen05.mma m128 n64 k16, A = P (bf16, written to shared memory by
+// Per KV block of 64 tokens (4 pages of 16) and per tile t:
+//   S_t[128 x 64]  = Q_t[128 x 128d] . K^T   8 x tcgen05.mma m128 n64 k16, A and B K-major from shared memory
+//   P_t = exp2(S_t * scale - m) (causal / tail masked), row statistics in registers: thread r of warpgroup t owns
+//         row r (TMEM lane r)
+//   O_t[128 x 128d] += P_t[128 x 64] . V     8 x tcgen05.mma m128 n64 k16, A = P_t (bf16, written to shared memory by
 //                                            the softmax threads in the swizzled K-major layout), B = V MN-major
 // K/V pages are staged by TMA straight into the SWIZZLE_128B layout the UMMA descriptors describe (two boxes of
-// 64 d x 16 tokens per page, one per 128-byte half of the head dimension), two stages of 64 KiB. S is double-
-// buffered in TMEM (2 x 128 columns) and P in shared memory, so Q.K^T of block j+1 and P.V of block j-1 run under
-// the softmax of block j; O lives in 128 more columns and is rescaled in TMEM only when a row maximum grows by
-// more than 2^kTau (lazy rescale).
+// 64 d x 16 tokens per page, one per 128-byte half of the head dimension), three stages of 32 KiB. S is double-
+// buffered in TMEM (2 tiles x 2 x 64 columns) and P in shared memory, so Q.K^T of block j+1 and P.V of block j-1
+// run under the softmax of block j and the two tiles' softmax warpgroups alternate on the tensor core; O lives in
+// 2 x 128 more columns (512 in all) and is rescaled in TMEM only when a row maximum grows by more than 2^kTau.
 //
-// Warp roles (192 threads): warps 0-3 softmax / correction / epilogue (warp w touches TMEM lanes 32w..32w+31),
-// warp 4 TMA producer, warp 5 TMEM allocation + single-thread MMA issue.
+// Warp roles (320 threads): warps 0-3 / 4-7 softmax, correction and epilogue of tile 0 / 1 (warp w touches TMEM
+// lanes 32 (w % 4) ..), warp 8 TMA producer, warp 9 TMEM allocation + single-thread MMA issue.
 #include "kernels.h"
 #include "sk_math.cuh"
 #include "umma.cuh"
 
 namespace b200 {
 
-constexpr int kUpTok = 16;             // query tokens per CTA
-constexpr int kUpHeads = 8;            // query-head slots per CTA (rows = token * 8 + head slot)
-constexpr int kUpBlk = 128;            // KV tokens per block
+constexpr int kUpQT = 2;               // 128-row query tiles per CTA
+constexpr int kUpTok = 16;             // query tokens per tile
+constexpr int kUpCtaTok = kUpQT * kUpTok;
+constexpr int kUpHeads = 8;            // query-head slots per tile (rows = token * 8 + head slot)
+constexpr int kUpBlk = 64;             // KV tokens per block
 constexpr int kUpTiles = kUpBlk / kTileTokens;  // 16-token pages per block
-constexpr int kUpHalf = 128 * 128;     // one [128 rows][128 B] swizzled operand half: 16 KiB
-constexpr int kUpStages = 2;
-constexpr int kUpThreads = 192;
-constexpr uint32_t kUpTmemCols = 512;  // S0 | S1 | O | (unused): power of two
+constexpr int kUpQHalf = 128 * 128;    // Q / P operand half: [128 rows][128 B] = 16 KiB
+constexpr int kUpKvHalf = kUpBlk * 128;  // K / V operand half: [64 tokens][128 B] = 8 KiB
+constexpr int kUpStages = 3;
+constexpr int kUpThreads = kUpQT * 128 + 64;
+constexpr uint32_t kUpTmemCols = 512;  // S[t][buf]: 64 columns at t * 128 + buf * 64; O[t]: 128 columns at 256 + t * 128
 
 struct UpSmem {
-  alignas(1024) uint8_t q[2][kUpHalf];             // A of Q.K^T: [d half][row][64 d]
-  alignas(1024) uint8_t p[2][2][kUpHalf];          // A of P.V, double-buffered: [buffer][token half][row][64 tokens]
-  alignas(1024) uint8_t k[kUpStages][2][kUpHalf];  // B of Q.K^T: [d half][token][64 d]
-  alignas(1024) uint8_t v[kUpStages][2][kUpHalf];  // B of P.V (MN-major): [d half][token][64 d]
+  alignas(1024) uint8_t q[kUpQT][2][kUpQHalf];     // A of Q.K^T: [tile][d half][row][64 d]
+  alignas(1024) uint8_t p[kUpQT][2][kUpQHalf];     // A of P.V, double-buffered: [tile][buffer][row][64 tokens]
+  alignas(1024) uint8_t k[kUpStages][2][kUpKvHalf];  // B of Q.K^T: [d half][token][64 d]
+  alignas(1024) uint8_t v[kUpStages][2][kUpKvHalf];  // B of P.V (MN-major): [d half][token][64 d]
   alignas(8) uint64_t kv_full[kUpStages];
   alignas(8) uint64_t kv_empty[kUpStages];
-  alignas(8) uint64_t s_full[2];
-  alignas(8) uint64_t p_full;
-  alignas(8) uint64_t pv_done[2];  // P.V of block j has completed: barrier j & 1 (never more than one phase ahead of a waiter)
+  alignas(8) uint64_t s_full[kUpQT][2];
+  alignas(8) uint64_t p_full[kUpQT];
+  alignas(8) uint64_t pv_done[kUpQT][2];  // P_t.V of block j has completed: barrier [t][j & 1] (a waiter is never more than one phase behind)
   uint32_t tmem_base;
 };
 
@@ -54,18 +60,19 @@ __device__ __forceinline__ void tma_load_5d_half(uint32_t dst, const CUtensorMap
       : "memory");
 }
 
-// same tile-slot scheme as paged_prefill.cu (pf_locate)
+// CTA -> (sequence, 32-token query chunk), the slot scheme of paged_prefill.cu (pf_locate) at 32-token granularity:
+// sequence b owns slots [qsl[b] / 32 + b, qsl[b+1] / 32 + b + 1), always enough for its ceil(q_len / 32) chunks.
 __device__ __forceinline__ bool up_locate(const PrefillParams& p, int slot, int& b, int& qt, int& q0, int& q_len) {
   int lo = 0, hi = p.batch;
   while (hi - lo > 1) {
     const int mid = (lo + hi) >> 1;
-    if ((__ldg(p.query_start_loc + mid) >> 4) + mid <= slot) lo = mid; else hi = mid;
+    if ((__ldg(p.query_start_loc + mid) >> 5) + mid <= slot) lo = mid; else hi = mid;
   }
   b = lo;
   q0 = __ldg(p.query_start_loc + b);
   q_len = __ldg(p.query_start_loc + b + 1) - q0;
-  qt = slot - ((q0 >> 4) + b);
-  return qt * kUpTok < q_len;
+  qt = slot - ((q0 >> 5) + b);
+  return qt * kUpCtaTok < q_len;
 }
 
 __global__ void __launch_bounds__(kUpThreads, 1)
@@ -74,17 +81,18 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
   extern __shared__ uint8_t smem_raw[];
   UpSmem& sm = *reinterpret_cast<UpSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kProducerWarp = kUpQT * 4, kMmaWarp = kUpQT * 4 + 1;
 
   int b, qt, q0, q_len;
-  // heavy (late) tiles first; the whole CTA leaves together, before any barrier or TMEM allocation
+  // heavy (late) chunks first; the whole CTA leaves together, before any barrier or TMEM allocation
   if (!up_locate(p, static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x), b, qt, q0, q_len)) return;
   const int hs = blockIdx.y;
   const int kvh = hs / p.subgroups, sub = hs % p.subgroups;
   const int heads_here = min(kUpHeads, p.group - sub * kUpHeads);
   const int S = max(0, __ldg(p.seq_lens + b));
-  const int i0 = qt * kUpTok;
+  const int i0 = qt * kUpCtaTok;
   const int ctx0 = S - q_len;  // cache position of the sequence's first new token
-  const int kv_end = max(0, min(S, ctx0 + i0 + kUpTok));
+  const int kv_end = max(0, min(S, ctx0 + min(q_len, i0 + kUpCtaTok)));  // the chunk's last query sees [0, kv_end)
   const int ntiles = (kv_end + kTileTokens - 1) / kTileTokens;
   const int nblk = (kv_end + kUpBlk - 1) / kUpBlk;
 
@@ -93,19 +101,23 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     for (int s = 0; s < kUpStages; ++s) {
       mbar_init(&sm.kv_full[s], 1);
       mbar_init(&sm.kv_empty[s], 1);
-      mbar_init(&sm.s_full[s], 1);
     }
-    mbar_init(&sm.p_full, 128);
-    mbar_init(&sm.pv_done[0], 1);
-    mbar_init(&sm.pv_done[1], 1);
+#pragma unroll
+    for (int t = 0; t < kUpQT; ++t) {
+      mbar_init(&sm.s_full[t][0], 1);
+      mbar_init(&sm.s_full[t][1], 1);
+      mbar_init(&sm.p_full[t], 128);
+      mbar_init(&sm.pv_done[t][0], 1);
+      mbar_init(&sm.pv_done[t][1], 1);
+    }
     fence_barrier_init();
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_v);
   }
-  if (warp == 5) tmem_alloc<kUpTmemCols>(&sm.tmem_base);
-  // ---- Q tile -> shared memory (swizzled K-major A operand); rows of absent tokens / head slots are zero
-  if (warp < 4) {
-    const int r = threadIdx.x, i = r >> 3, hh = r & 7;
+  if (warp == kMmaWarp) tmem_alloc<kUpTmemCols>(&sm.tmem_base);
+  // ---- Q tiles -> shared memory (swizzled K-major A operand); rows of absent tokens / head slots are zero
+  if (warp < kUpQT * 4) {
+    const int t = warp >> 2, r = threadIdx.x & 127, i = t * kUpTok + (r >> 3), hh = r & 7;
     const bool ok = (i0 + i < q_len) && (hh < heads_here);
     const int h = kvh * p.group + sub * kUpHeads + hh;
     const int4* src = reinterpret_cast<const int4*>(p.q + static_cast<int64_t>(q0 + i0 + i) * p.q_stride_tok +
@@ -113,7 +125,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
 #pragma unroll
     for (int c = 0; c < 16; ++c) {
       const int4 x = ok ? __ldg(src + c) : make_int4(0, 0, 0, 0);
-      *reinterpret_cast<int4*>(&sm.q[c >> 3][r * 128 + (((c & 7) ^ (r & 7)) << 4)]) = x;
+      *reinterpret_cast<int4*>(&sm.q[t][c >> 3][r * 128 + (((c & 7) ^ (r & 7)) << 4)]) = x;
     }
     fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
   }
@@ -121,15 +133,14 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = sm.tmem_base;
-  const uint32_t tm_s0 = tmem, tm_o = tmem + 256;
 
-  if (warp == 4) {
+  if (warp == kProducerWarp) {
     // ===================== TMA producer =====================
-    const uint64_t pol = l2_policy_evict_last();  // the other query tiles of the sequence re-read these pages
+    const uint64_t pol = l2_policy_evict_last();  // the other query chunks of the sequence re-read these pages
     int page0 = -32, ids = 0;
     for (int j = 0; j < nblk; ++j) {
-      const int st = j & 1;
-      if (j >= kUpStages) mbar_wait(&sm.kv_empty[st], ((j >> 1) - 1) & 1);
+      const int st = j % kUpStages, use = j / kUpStages;
+      if (use > 0) mbar_wait(&sm.kv_empty[st], (use - 1) & 1);
       const int t0 = j * kUpTiles;
       const int nt = min(kUpTiles, ntiles - t0);
       if (lane == 0) mbar_arrive_expect_tx(&sm.kv_full[st], static_cast<uint32_t>(nt * 2 * kTileBytesBf16));
@@ -154,73 +165,81 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == kMmaWarp) {
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
-      constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, false, false);
-      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);
-      const uint32_t q_addr = smem_u32(&sm.q[0][0]);
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64, false, false);     // S = Q.K^T, B K-major
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);   // O += P.V, B MN-major
       auto issue_qk = [&](int j) {
-        const int st = j & 1;
-        mbar_wait(&sm.kv_full[st], (j >> 1) & 1);
+        const int st = j % kUpStages;
+        mbar_wait(&sm.kv_full[st], (j / kUpStages) & 1);
         tc_fence_after_sync();
         const uint32_t k_addr = smem_u32(&sm.k[st][0][0]);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // d = 16 kk .. 16 kk + 15: half kk / 4, 32-byte step inside the swizzled row
-          const uint32_t o = (kk >> 2) * kUpHalf + (kk & 3) * 32;
-          umma_bf16_ss(tm_s0 + st * 128, umma_desc_sw128(q_addr + o, 16, 1024), umma_desc_sw128(k_addr + o, 16, 1024),
-                       idesc_qk, kk > 0);
+        for (int t = 0; t < kUpQT; ++t) {
+          const uint32_t q_addr = smem_u32(&sm.q[t][0][0]);
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk)  // d = 16 kk ..: half kk / 4, 32-byte step inside the swizzled row
+            umma_bf16_ss(tmem + t * 128 + (j & 1) * 64,
+                         umma_desc_sw128(q_addr + (kk >> 2) * kUpQHalf + (kk & 3) * 32, 16, 1024),
+                         umma_desc_sw128(k_addr + (kk >> 2) * kUpKvHalf + (kk & 3) * 32, 16, 1024), idesc, kk > 0);
+          umma_commit(&sm.s_full[t][j & 1]);
         }
-        umma_commit(&sm.s_full[st]);
       };
       if (nblk > 0) issue_qk(0);
       for (int j = 0; j < nblk; ++j) {
         if (j + 1 < nblk) issue_qk(j + 1);
-        mbar_wait(&sm.p_full, j & 1);
-        tc_fence_after_sync();
-        const uint32_t v_addr = smem_u32(&sm.v[j & 1][0][0]), p_addr = smem_u32(&sm.p[j & 1][0][0]);
+        const uint32_t v_addr = smem_u32(&sm.v[j % kUpStages][0][0]);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // KV tokens 16 kk .. 16 kk + 15
-          const uint64_t da = umma_desc_sw128(p_addr + (kk >> 2) * kUpHalf + (kk & 3) * 32, 16, 1024);
+        for (int t = 0; t < kUpQT; ++t) {
+          mbar_wait(&sm.p_full[t], j & 1);
+          tc_fence_after_sync();
+          const uint32_t p_addr = smem_u32(&sm.p[t][j & 1][0]);
 #pragma unroll
-          for (int nh = 0; nh < 2; ++nh)  // d halves: one 64-wide MN atom each
-            umma_bf16_ss(tm_o + nh * 64, da, umma_desc_sw128(v_addr + nh * kUpHalf + kk * 2048, kUpHalf, 1024),
-                         idesc_pv, j > 0 || kk > 0);
+          for (int kk = 0; kk < 4; ++kk) {  // KV tokens 16 kk .. 16 kk + 15
+            const uint64_t da = umma_desc_sw128(p_addr + kk * 32, 16, 1024);
+#pragma unroll
+            for (int nh = 0; nh < 2; ++nh)  // d halves: one 64-wide MN atom each
+              umma_bf16_ss(tmem + 256 + t * 128 + nh * 64, da,
+                           umma_desc_sw128(v_addr + nh * kUpKvHalf + kk * 2048, kUpKvHalf, 1024), idesc_pv,
+                           j > 0 || kk > 0);
+          }
+          umma_commit(&sm.pv_done[t][j & 1]);
         }
-        umma_commit(&sm.kv_empty[j & 1]);
-        umma_commit(&sm.pv_done[j & 1]);
+        umma_commit(&sm.kv_empty[j % kUpStages]);  // every MMA that read this stage has been issued before
       }
     }
   } else {
-    // ===================== softmax / correction / epilogue: thread r = row r =====================
-    const int r = threadIdx.x, i = r >> 3, hh = r & 7;
+    // ===================== softmax / correction / epilogue: warpgroup t, thread r = row r =====================
+    const int t = warp >> 2, r = threadIdx.x & 127, i = t * kUpTok + (r >> 3), hh = r & 7;
     const bool row_ok = (i0 + i < q_len) && (hh < heads_here);
     const int pos = ctx0 + i0 + i;  // cache position of this row's query token
-    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t tm_o = tmem + 256 + t * 128 + lane_off;
     const float scale = p.scale_log2;
     float m = -CUDART_INF_F, l = 0.f;
     for (int j = 0; j < nblk; ++j) {
-      const int st = j & 1;
-      const uint32_t tm_s = tm_s0 + st * 128 + lane_off;
+      const int buf = j & 1, st = j % kUpStages;
+      const uint32_t tm_s = tmem + t * 128 + buf * 64 + lane_off;
       const int t_base = j * kUpBlk;
       const int lim = row_ok ? min(kv_end, pos + 1) - t_base : 0;  // columns [0, lim) of this block are visible
       const bool full = __all_sync(0xffffffffu, lim >= kUpBlk);    // no mask anywhere in this warp's rows
-      mbar_wait(&sm.s_full[st], (j >> 1) & 1);
+      mbar_wait(&sm.s_full[t][buf], (j >> 1) & 1);
       tc_fence_after_sync();
-      // ---- the row's 128 scores: four TMEM loads in flight, one wait
-      uint32_t x[4][32];
+      // ---- the row's 64 scores: two TMEM loads in flight, one wait
+      uint32_t x[2][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(tm_s + c * 32, x[c]);
+      for (int c = 0; c < 2; ++c) tmem_ld32(tm_s + c * 32, x[c]);
       tmem_ld_wait();
       float mx = -CUDART_INF_F;
       if (full) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < 2; ++c)
 #pragma unroll
           for (int e = 0; e < 32; ++e) mx = fmaxf(mx, __uint_as_float(x[c][e]));
       } else {
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < 2; ++c)
 #pragma unroll
           for (int e = 0; e < 32; ++e)
             if (c * 32 + e < lim) mx = fmaxf(mx, __uint_as_float(x[c][e]));
@@ -232,11 +251,12 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       m = m_new;
       const float mu = (m == -CUDART_INF_F) ? 0.f : m;
       // ---- this P buffer was last read by P.V of block j - 2
-      if (j >= 2) mbar_wait(&sm.pv_done[st], ((j >> 1) - 1) & 1);
-      // ---- P = exp2(S * scale - m) as bf16 into the swizzled A-operand layout; row sum
+      if (j >= 2) mbar_wait(&sm.pv_done[t][buf], ((j >> 1) - 1) & 1);
+      // ---- P = exp2(S * scale - m) as bf16 into the swizzled A-operand layout (one 128-byte row); row sum
       float sum = 0.f;
+      uint8_t* prow = &sm.p[t][buf][r * 128];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t pk[16];
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
@@ -249,16 +269,15 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
           sum += p0 + p1;
           pk[e >> 1] = pack_bf16x2(p0, p1);
         }
-        uint8_t* prow = &sm.p[st][c >> 1][r * 128];
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4)
-          *reinterpret_cast<uint4*>(prow + ((((c & 1) * 4 + q4) ^ (r & 7)) << 4)) =
+          *reinterpret_cast<uint4*>(prow + (((c * 4 + q4) ^ (r & 7)) << 4)) =
               make_uint4(pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2], pk[4 * q4 + 3]);
       }
       l = l * alpha + sum;
-      // ---- V rows past the end of the sequence hold whatever the page (or an earlier block) held: zero them so
-      // that 0 x NaN cannot reach O (thread r owns token row r of the block)
-      if (t_base + kUpBlk > kv_end && t_base + r >= kv_end) {
+      // ---- V rows past the end of the chunk's context hold whatever the page (or an earlier block) held: zero them
+      // so that 0 x NaN cannot reach O. Both warpgroups do it (same zeros) because each publishes only its own P.
+      if (t_base + kUpBlk > kv_end && r < kUpBlk && t_base + r >= kv_end) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint4* vr = reinterpret_cast<uint4*>(&sm.v[st][half][r * 128]);
@@ -268,30 +287,32 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       }
       // ---- lazy rescale of O in TMEM (warp-uniform: tcgen05.ld/st are warp-wide); needs P.V of block j - 1 done
       if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
-        mbar_wait(&sm.pv_done[st ^ 1], ((j - 1) >> 1) & 1);
+        mbar_wait(&sm.pv_done[t][buf ^ 1], ((j - 1) >> 1) & 1);
         tc_fence_after_sync();
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          tmem_ld32(tm_o + lane_off + c * 32, x[c]);
-        }
-        tmem_ld_wait();
+        for (int c = 0; c < 4; c += 2) {
+          tmem_ld32(tm_o + c * 32, x[0]);
+          tmem_ld32(tm_o + c * 32 + 32, x[1]);
+          tmem_ld_wait();
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) x[c][e] = __float_as_uint(__uint_as_float(x[c][e]) * alpha);
-          tmem_st32(tm_o + lane_off + c * 32, x[c]);
+          for (int e = 0; e < 32; ++e) {
+            x[0][e] = __float_as_uint(__uint_as_float(x[0][e]) * alpha);
+            x[1][e] = __float_as_uint(__uint_as_float(x[1][e]) * alpha);
+          }
+          tmem_st32(tm_o + c * 32, x[0]);
+          tmem_st32(tm_o + c * 32 + 32, x[1]);
         }
         tmem_st_wait();
       }
       fence_proxy_async_smem();
       tc_fence_before_sync();
-      mbar_arrive(&sm.p_full);
+      mbar_arrive(&sm.p_full[t]);
     }
-    uint32_t x[32];
     // ---- epilogue: O / l -> bf16 -> global (256 contiguous bytes per row)
+    uint32_t x[32];
     const float inv = l > 0.f ? 1.f / l : 0.f;
     if (nblk > 0) {
-      mbar_wait(&sm.pv_done[(nblk - 1) & 1], ((nblk - 1) >> 1) & 1);
+      mbar_wait(&sm.pv_done[t][(nblk - 1) & 1], ((nblk - 1) >> 1) & 1);
       tc_fence_after_sync();
     }
     const int h = kvh * p.group + sub * kUpHeads + hh;
@@ -300,7 +321,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       if (nblk > 0) {
-        tmem_ld32(tm_o + lane_off + c * 32, x);
+        tmem_ld32(tm_o + c * 32, x);
         tmem_ld_wait();
       } else {
 #pragma unroll
@@ -322,7 +343,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
   // ---- teardown: every TMEM access has completed before the allocating warp frees it
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == 5) tmem_free<kUpTmemCols>(tmem);
+  if (warp == kMmaWarp) tmem_free<kUpTmemCols>(tmem);
 }
 
 size_t prefill_umma_smem_bytes() { return sizeof(UpSmem) + 1024; }
@@ -339,7 +360,7 @@ cudaError_t launch_paged_prefill_umma(const CUtensorMap& tm_k, const CUtensorMap
       return e;
     configured_dev = dev;
   }
-  const dim3 grid(static_cast<unsigned>(p.num_tokens / kUpTok + p.batch),
+  const dim3 grid(static_cast<unsigned>(p.num_tokens / kUpCtaTok + p.batch),
                   static_cast<unsigned>(p.num_kv_heads * p.subgroups));
   paged_prefill_umma_kernel<<<grid, kUpThreads, smem, stream>>>(tm_k, tm_v, p);
   return cudaGetLastError();
