@@ -13,8 +13,9 @@
 //   O_t[128 x 128d] += P_t[128 x 64] . V     8 x tcgen05.mma m128 n64 k16, A = P_t (bf16, written to shared memory by
 //                                            the softmax threads in the swizzled K-major layout), B = V MN-major
 // K/V pages are staged by TMA straight into the SWIZZLE_128B layout the UMMA descriptors describe (two boxes of
-// 64 d x 16 tokens per page, one per 128-byte half of the head dimension), three stages of 32 KiB. S is double-
-// buffered in TMEM (2 tiles x 2 x 64 columns) and P in shared memory, so Q.K^T of block j+1 and P.V of block j-1
+// 64 d x 16 tokens per page, one per 128-byte half of the head dimension), four stages of 32 KiB (a stage is held
+// from its load until P.V of its block completes, so four are needed to give a load two block-times to land). S is
+// double-buffered in TMEM (2 tiles x 2 x 64 columns), so Q.K^T of block j+1 and P.V of block j-1
 // run under the softmax of block j and the two tiles' softmax warpgroups alternate on the tensor core; O lives in
 // 2 x 128 more columns (512 in all) and is rescaled in TMEM only when a row maximum grows by more than 2^kTau.
 //
@@ -34,20 +35,20 @@ constexpr int kUpBlk = 64;             // KV tokens per block
 constexpr int kUpTiles = kUpBlk / kTileTokens;  // 16-token pages per block
 constexpr int kUpQHalf = 128 * 128;    // Q / P operand half: [128 rows][128 B] = 16 KiB
 constexpr int kUpKvHalf = kUpBlk * 128;  // K / V operand half: [64 tokens][128 B] = 8 KiB
-constexpr int kUpStages = 3;
+constexpr int kUpStages = 4;
 constexpr int kUpThreads = kUpQT * 128 + 64;
 constexpr uint32_t kUpTmemCols = 512;  // S[t][buf]: 64 columns at t * 128 + buf * 64; O[t]: 128 columns at 256 + t * 128
 
 struct UpSmem {
   alignas(1024) uint8_t q[kUpQT][2][kUpQHalf];     // A of Q.K^T: [tile][d half][row][64 d]
-  alignas(1024) uint8_t p[kUpQT][2][kUpQHalf];     // A of P.V, double-buffered: [tile][buffer][row][64 tokens]
+  alignas(1024) uint8_t p[kUpQT][kUpQHalf];        // A of P.V: [tile][row][64 tokens]
   alignas(1024) uint8_t k[kUpStages][2][kUpKvHalf];  // B of Q.K^T: [d half][token][64 d]
   alignas(1024) uint8_t v[kUpStages][2][kUpKvHalf];  // B of P.V (MN-major): [d half][token][64 d]
   alignas(8) uint64_t kv_full[kUpStages];
   alignas(8) uint64_t kv_empty[kUpStages];
   alignas(8) uint64_t s_full[kUpQT][2];
   alignas(8) uint64_t p_full[kUpQT];
-  alignas(8) uint64_t pv_done[kUpQT][2];  // P_t.V of block j has completed: barrier [t][j & 1] (a waiter is never more than one phase behind)
+  alignas(8) uint64_t pv_done[kUpQT];  // P_t.V of block j has completed (waited for once per block, in order)
   uint32_t tmem_base;
 };
 
@@ -107,8 +108,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       mbar_init(&sm.s_full[t][0], 1);
       mbar_init(&sm.s_full[t][1], 1);
       mbar_init(&sm.p_full[t], 128);
-      mbar_init(&sm.pv_done[t][0], 1);
-      mbar_init(&sm.pv_done[t][1], 1);
+      mbar_init(&sm.pv_done[t], 1);
     }
     fence_barrier_init();
     tma_prefetch_desc(&tm_k);
@@ -194,7 +194,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
         for (int t = 0; t < kUpQT; ++t) {
           mbar_wait(&sm.p_full[t], j & 1);
           tc_fence_after_sync();
-          const uint32_t p_addr = smem_u32(&sm.p[t][j & 1][0]);
+          const uint32_t p_addr = smem_u32(&sm.p[t][0]);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {  // KV tokens 16 kk .. 16 kk + 15
             const uint64_t da = umma_desc_sw128(p_addr + kk * 32, 16, 1024);
@@ -204,7 +204,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
                            umma_desc_sw128(v_addr + nh * kUpKvHalf + kk * 2048, kUpKvHalf, 1024), idesc_pv,
                            j > 0 || kk > 0);
           }
-          umma_commit(&sm.pv_done[t][j & 1]);
+          umma_commit(&sm.pv_done[t]);
         }
         umma_commit(&sm.kv_empty[j % kUpStages]);  // every MMA that read this stage has been issued before
       }
@@ -250,11 +250,15 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       const float alpha = (grow && m != -CUDART_INF_F) ? fast_exp2(m - m_new) : 1.f;
       m = m_new;
       const float mu = (m == -CUDART_INF_F) ? 0.f : m;
-      // ---- this P buffer was last read by P.V of block j - 2
-      if (j >= 2) mbar_wait(&sm.pv_done[t][buf], ((j >> 1) - 1) & 1);
+      // ---- the P buffer is read by P.V of block j - 1 (issued the moment that P was published, long done by now);
+      // the same completion also licenses the O rescale below
+      if (j >= 1) {
+        mbar_wait(&sm.pv_done[t], (j - 1) & 1);
+        tc_fence_after_sync();
+      }
       // ---- P = exp2(S * scale - m) as bf16 into the swizzled A-operand layout (one 128-byte row); row sum
       float sum = 0.f;
-      uint8_t* prow = &sm.p[t][buf][r * 128];
+      uint8_t* prow = &sm.p[t][r * 128];
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t pk[16];
@@ -287,8 +291,6 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       }
       // ---- lazy rescale of O in TMEM (warp-uniform: tcgen05.ld/st are warp-wide); needs P.V of block j - 1 done
       if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
-        mbar_wait(&sm.pv_done[t][buf ^ 1], ((j - 1) >> 1) & 1);
-        tc_fence_after_sync();
 #pragma unroll
         for (int c = 0; c < 4; c += 2) {
           tmem_ld32(tm_o + c * 32, x[0]);
@@ -312,7 +314,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     uint32_t x[32];
     const float inv = l > 0.f ? 1.f / l : 0.f;
     if (nblk > 0) {
-      mbar_wait(&sm.pv_done[t][(nblk - 1) & 1], ((nblk - 1) >> 1) & 1);
+      mbar_wait(&sm.pv_done[t], (nblk - 1) & 1);
       tc_fence_after_sync();
     }
     const int h = kvh * p.group + sub * kUpHeads + hh;
