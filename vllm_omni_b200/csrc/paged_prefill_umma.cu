@@ -144,25 +144,26 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       const int t0 = j * kUpTiles;
       const int nt = min(kUpTiles, ntiles - t0);
       if (lane == 0) mbar_arrive_expect_tx(&sm.kv_full[st], static_cast<uint32_t>(nt * 2 * kTileBytesBf16));
-      for (int ti = 0; ti < nt; ++ti) {
-        const int tile = t0 + ti;
-        const int page = tile >> p.tpp_shift;
-        if (page >= page0 + 32) {
-          page0 = page & ~31;
-          const int pg = page0 + lane;
-          ids = (pg << p.tpp_shift) < ntiles ? __ldg(p.block_table + static_cast<int64_t>(b) * p.bt_stride + pg) : 0;
-        }
-        const int blk = __shfl_sync(0xffffffffu, ids, page - page0);
-        if (lane == 0) {
-          const uint32_t bar = smem_u32(&sm.kv_full[st]);
-          const int slot0 = (tile & p.tpp_mask) * kTileTokens;
-          const uint32_t off = static_cast<uint32_t>(ti) * kHalfBytes;  // 16 rows of 128 B
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            tma_load_5d_half(smem_u32(&sm.k[st][half][0]) + off, &tm_k, bar, 0, slot0, half, kvh, blk, pol);
-            tma_load_5d_half(smem_u32(&sm.v[st][half][0]) + off, &tm_v, bar, 0, slot0, half, kvh, blk, pol);
-          }
-        }
+      __syncwarp();
+      // the block's 4 pages lie in one aligned group of 4 tiles, hence in one 32-page window of block ids
+      const int first_page = t0 >> p.tpp_shift;
+      if (first_page >= page0 + 32) {
+        page0 = first_page & ~31;
+        const int pg = page0 + lane;
+        ids = (pg << p.tpp_shift) < ntiles ? __ldg(p.block_table + static_cast<int64_t>(b) * p.bt_stride + pg) : 0;
+      }
+      // 16 lanes issue the block's 16 boxes at once: lane = page * 4 + (V ? 2 : 0) + d half
+      const int ti = (lane >> 2) & 3, half = lane & 1;
+      const int tile = t0 + min(ti, nt - 1);
+      const int blk = __shfl_sync(0xffffffffu, ids, (tile >> p.tpp_shift) - page0);
+      if (lane < 16 && ti < nt) {
+        const uint32_t bar = smem_u32(&sm.kv_full[st]);
+        const int slot0 = (tile & p.tpp_mask) * kTileTokens;
+        const uint32_t off = static_cast<uint32_t>(ti) * kHalfBytes;  // 16 rows of 128 B
+        if (lane & 2)
+          tma_load_5d_half(smem_u32(&sm.v[st][half][0]) + off, &tm_v, bar, 0, slot0, half, kvh, blk, pol);
+        else
+          tma_load_5d_half(smem_u32(&sm.k[st][half][0]) + off, &tm_k, bar, 0, slot0, half, kvh, blk, pol);
       }
     }
   } else if (warp == kMmaWarp) {
