@@ -170,7 +170,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, 64, false, false);     // S = Q.K^T, B K-major
-      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);   // O += P.V, B MN-major
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 128, false, true);  // O += P.V, B MN-major
       auto issue_qk = [&](int j) {
         const int st = j % kUpStages;
         mbar_wait(&sm.kv_full[st], (j / kUpStages) & 1);
@@ -197,14 +197,9 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
           tc_fence_after_sync();
           const uint32_t p_addr = smem_u32(&sm.p[t][0]);
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {  // KV tokens 16 kk .. 16 kk + 15
-            const uint64_t da = umma_desc_sw128(p_addr + kk * 32, 16, 1024);
-#pragma unroll
-            for (int nh = 0; nh < 2; ++nh)  // d halves: one 64-wide MN atom each
-              umma_bf16_ss(tmem + 256 + t * 128 + nh * 64, da,
-                           umma_desc_sw128(v_addr + nh * kUpKvHalf + kk * 2048, kUpKvHalf, 1024), idesc_pv,
-                           j > 0 || kk > 0);
-          }
+          for (int kk = 0; kk < 4; ++kk)  // KV tokens 16 kk .. 16 kk + 15; N = 128: the two 64-wide MN atoms (d halves)
+            umma_bf16_ss(tmem + 256 + t * 128, umma_desc_sw128(p_addr + kk * 32, 16, 1024),  // sit LBO = 8 KiB apart
+                         umma_desc_sw128(v_addr + kk * 2048, kUpKvHalf, 1024), idesc_pv, j > 0 || kk > 0);
           umma_commit(&sm.pv_done[t]);
         }
         umma_commit(&sm.kv_empty[j % kUpStages]);  // every MMA that read this stage has been issued before
