@@ -36,7 +36,8 @@ def test_library_builds_and_exports_every_declared_symbol(lib):
 
 def test_sass_is_blackwell_native():
     """The built library carries sm_100a code with TMA (UTMALDG), mbarrier (SYNCS), ldmatrix (LDSM),
-    tensor-core MMA (HMMA) and cp.async (LDGSTS) instructions."""
+    tensor-core MMA (HMMA), cp.async (LDGSTS) and tcgen05 (UTCHMMA = tcgen05.mma, UTCBAR = tcgen05.commit,
+    LDTM / STTM = tcgen05.ld / st) instructions."""
     import shutil
     import subprocess
     if shutil.which("cuobjdump") is None:
@@ -44,7 +45,7 @@ def test_sass_is_blackwell_native():
     build.build_library()
     out = subprocess.run(["cuobjdump", "-sass", str(build.LIB_PATH)], capture_output=True, text=True).stdout
     assert "sm_100a" in out
-    for op in ("UTMALDG", "SYNCS", "LDSM", "HMMA", "LDGSTS", "MOVM"):
+    for op in ("UTMALDG", "SYNCS", "LDSM", "HMMA", "LDGSTS", "MOVM", "UTCHMMA", "UTCBAR", "LDTM", "STTM"):
         assert op in out, f"{op} missing from SASS"
 
 

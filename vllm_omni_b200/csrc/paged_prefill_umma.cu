@@ -10,8 +10,10 @@
 //   S_t[128 x 64]  = Q_t[128 x 128d] . K^T   8 x tcgen05.mma m128 n64 k16, A and B K-major from shared memory
 //   P_t = exp2(S_t * scale - m) (causal / tail masked), row statistics in registers: thread r of warpgroup t owns
 //         row r (TMEM lane r)
-//   O_t[128 x 128d] += P_t[128 x 64] . V     8 x tcgen05.mma m128 n64 k16, A = P_t (bf16, written to shared memory by
-//                                            the softmax threads in the swizzled K-major layout), B = V MN-major
+//   O_t[128 x 128d] += P_t[128 x 64] . V     4 x tcgen05.mma m128 n128 k16, A = P_t read from TMEM (the softmax threads
+//                                            store it as bf16 pairs over the first 32 columns of the S buffer they
+//                                            just consumed), B = V MN-major from shared memory, both 64-wide d
+//                                            halves in one instruction through the descriptor's leading byte offset
 // K/V pages are staged by TMA straight into the SWIZZLE_128B layout the UMMA descriptors describe (two boxes of
 // 64 d x 16 tokens per page, one per 128-byte half of the head dimension), four stages of 32 KiB (a stage is held
 // from its load until P.V of its block completes, so four are needed to give a load two block-times to land). S is
@@ -24,6 +26,10 @@
 #include "kernels.h"
 #include "sk_math.cuh"
 #include "umma.cuh"
+
+#ifndef B200_UMMA_P_IN_TMEM
+#define B200_UMMA_P_IN_TMEM 1  // P as the TMEM A operand of P.V (0: through shared memory)
+#endif
 
 namespace b200 {
 
@@ -41,7 +47,9 @@ constexpr uint32_t kUpTmemCols = 512;  // S[t][buf]: 64 columns at t * 128 + buf
 
 struct UpSmem {
   alignas(1024) uint8_t q[kUpQT][2][kUpQHalf];     // A of Q.K^T: [tile][d half][row][64 d]
+#if !B200_UMMA_P_IN_TMEM
   alignas(1024) uint8_t p[kUpQT][kUpQHalf];        // A of P.V: [tile][row][64 tokens]
+#endif
   alignas(1024) uint8_t k[kUpStages][2][kUpKvHalf];  // B of Q.K^T: [d half][token][64 d]
   alignas(1024) uint8_t v[kUpStages][2][kUpKvHalf];  // B of P.V (MN-major): [d half][token][64 d]
   alignas(8) uint64_t kv_full[kUpStages];
@@ -195,11 +203,19 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
         for (int t = 0; t < kUpQT; ++t) {
           mbar_wait(&sm.p_full[t], j & 1);
           tc_fence_after_sync();
+#if B200_UMMA_P_IN_TMEM
+          const uint32_t p_tmem = tmem + t * 128 + (j & 1) * 64;  // P_t overwrote the first 32 columns of its S buffer
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)  // KV tokens 16 kk .. 16 kk + 15 = 8 TMEM columns of packed bf16 pairs
+            umma_bf16_ts(tmem + 256 + t * 128, p_tmem + kk * 8, umma_desc_sw128(v_addr + kk * 2048, kUpKvHalf, 1024),
+                         idesc_pv, j > 0 || kk > 0);
+#else
           const uint32_t p_addr = smem_u32(&sm.p[t][0]);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)  // KV tokens 16 kk .. 16 kk + 15; N = 128: the two 64-wide MN atoms (d halves)
             umma_bf16_ss(tmem + 256 + t * 128, umma_desc_sw128(p_addr + kk * 32, 16, 1024),  // sit LBO = 8 KiB apart
                          umma_desc_sw128(v_addr + kk * 2048, kUpKvHalf, 1024), idesc_pv, j > 0 || kk > 0);
+#endif
           umma_commit(&sm.pv_done[t]);
         }
         umma_commit(&sm.kv_empty[j % kUpStages]);  // every MMA that read this stage has been issued before
@@ -254,10 +270,18 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
       }
       // ---- P = exp2(S * scale - m) as bf16 into the swizzled A-operand layout (one 128-byte row); row sum
       float sum = 0.f;
+#if B200_UMMA_P_IN_TMEM
+      uint32_t pk2[32];
+#else
       uint8_t* prow = &sm.p[t][r * 128];
+#endif
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
+#if B200_UMMA_P_IN_TMEM
+        uint32_t* pk = pk2 + 16 * c;
+#else
         uint32_t pk[16];
+#endif
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
           float p0 = fast_exp2(fmaf(__uint_as_float(x[c][e]), scale, -mu));
@@ -269,11 +293,17 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
           sum += p0 + p1;
           pk[e >> 1] = pack_bf16x2(p0, p1);
         }
+#if !B200_UMMA_P_IN_TMEM
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4)
           *reinterpret_cast<uint4*>(prow + (((c * 4 + q4) ^ (r & 7)) << 4)) =
               make_uint4(pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2], pk[4 * q4 + 3]);
+#endif
       }
+#if B200_UMMA_P_IN_TMEM
+      tmem_st32(tm_s, pk2);  // A operand of P.V straight from TMEM: row r = lane r, 32 columns of bf16 pairs
+      tmem_st_wait();
+#endif
       l = l * alpha + sum;
       // ---- V rows past the end of the chunk's context hold whatever the page (or an earlier block) held: zero them
       // so that 0 x NaN cannot reach O. Both warpgroups do it (same zeros) because each publishes only its own P.
