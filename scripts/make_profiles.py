@@ -119,7 +119,7 @@ def sass():
     if not lib.exists():
         return
     out = subprocess.run(["cuobjdump", "-sass", str(lib)], capture_output=True, text=True).stdout
-    keys = ("UTMALDG", "UTMAPF", "HMMA", "LDSM", "MOVM", "SYNCS", "F2FP", "MUFU.EX2", "LDGSTS", "ATOMG", "UTCHMMA",
+    keys = ("UTMALDG", "UTMAPF", "HMMA", "LDSM", "MOVM", "SYNCS", "F2FP", "MUFU.EX2", "LDGSTS", "ATOMG", "UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTCATOMSWS", "MULTIMEM", "REDG",
             "ACQBULK", "LDG.E.128", "STG.E.128", "STG.E.64")
     cnt, name = collections.OrderedDict(), None
     for line in out.splitlines():
@@ -134,7 +134,8 @@ def sass():
                 cnt[name][tok.rstrip(";")] += 1
     lines = ["SASS mnemonic census of libb200attn.so (cuobjdump -sass, sm_100a). UTMALDG = TMA tensor load,",
              "SYNCS = mbarrier ops, HMMA.16816 = mma.sync tensor-core MMA, LDSM = ldmatrix, MOVM = movmatrix,",
-             "F2FP...E4M3.UNPACK = e4m3 -> f16 conversion.", ""]
+             "F2FP...E4M3.UNPACK = e4m3 -> f16 conversion, UTCHMMA = tcgen05.mma, UTCBAR = tcgen05.commit, LDTM / STTM =",
+             "tcgen05.ld / st (TMEM), UTCATOMSWS = TMEM allocation.", ""]
     for fn, c in cnt.items():
         dem = subprocess.run(["c++filt", fn], capture_output=True, text=True).stdout.strip() or fn
         lines.append(short(dem))
