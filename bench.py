@@ -299,7 +299,7 @@ def run_b200(args, wl):
         if args.replica_exchange == "peer":
             from vllm_omni_b200 import peer
             try:
-                ex = peer.PeerExchange.create(my_group, B, hq, d)
+                ex = peer.PeerExchange.create(my_group, B, hq, d, timeout_s=30.0)
                 ex.q.copy_(inp.q)                     # the qkv projection would write q here
                 ex_note = f"peer-memory gather/scatter kernels ({ex.mem.transport} mapping)"
             except Exception as exn:  # noqa: BLE001 - reported in the JSON line
@@ -328,7 +328,7 @@ def run_b200(args, wl):
         if args.allreduce == "peer":
             from vllm_omni_b200 import peer
             try:
-                ar = peer.PeerAllReduce.create(max_numel=hidden.numel())
+                ar = peer.PeerAllReduce.create(max_numel=hidden.numel(), timeout_s=30.0)
                 hidden = ar.input(hidden.shape)           # o_proj would write its partial sums here
                 hidden.zero_()
                 hidden_out = torch.empty(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")
