@@ -138,5 +138,5 @@ def test_peer_exchange_matches_replica_split_indexing(lib, R, batch):
             want = torch.stack([q[ex.b0:ex.b1] for q in qs], dim=1).reshape(n, R * hq, d)
             assert torch.equal(ex.q_grp[:n].cpu(), want), f"gather differs on rank {i}"
             assert torch.equal(ex.out.cpu(), qs[i].float().mul(2 + it).to(torch.bfloat16)), f"scatter differs on rank {i}"
-            off = (128 * 8 + 128) * 4
+            off = peer.ERROR_WORDS_OFFSET
             assert ex.mem.local[off: off + 16].view(torch.int32).tolist() == [0, 0, 0, 0]

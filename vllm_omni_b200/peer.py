@@ -15,7 +15,6 @@ caller decides (bench.py then reports NCCL and says so).
 from __future__ import annotations
 
 import ctypes as C
-import os
 
 import torch
 
@@ -25,6 +24,9 @@ ALGO_NAMES = {_lib.AR_AUTO: "auto", _lib.AR_ONESHOT: "oneshot", _lib.AR_TWOSHOT:
               _lib.AR_MULTIMEM: "multimem", _lib.AR_PUSH: "push", _lib.AR_PUSH2: "push2"}
 PUSH_MAX_BYTES = 1 << 20      # largest message the PUSH schedule is provisioned for (per slot)
 _ALIGN = 256
+# byte offset of the 4 error words inside a flag region: after [128 blocks][8 ranks] arrival slots and 128 epochs
+# (kPeerMaxBlocks / kPeerMaxRanks in csrc/kernels.h)
+ERROR_WORDS_OFFSET = (128 * 8 + 128) * 4
 
 
 class PeerSetupError(RuntimeError):
@@ -224,8 +226,7 @@ class PeerAllReduce:
 
     def error_words(self) -> list[int]:
         """[flag, block, peer, epoch] recorded by a kernel whose flag wait timed out (all 0 = none)."""
-        off = (128 * 8 + 128) * 4
-        return self.local[off: off + 16].view(torch.int32).tolist()
+        return self.local[ERROR_WORDS_OFFSET: ERROR_WORDS_OFFSET + 16].view(torch.int32).tolist()
 
     def all_reduce(self, x: torch.Tensor, out: torch.Tensor | None = None, algo: int = _lib.AR_AUTO) -> torch.Tensor:
         if not x.is_cuda or x.dtype != torch.bfloat16 or not x.is_contiguous():
