@@ -114,3 +114,40 @@ def test_replica_group_batch_split_equals_replication(batch):
     for rank, same, shape in res:
         assert same, f"rank {rank}: batch-split output differs from the replicated run"
         assert shape == (batch, 4, 128)
+
+
+def _peer_setup_worker(rank: int, world: int, port: int, q_out):
+    """No GPU here: every transport must fail, and every rank must learn that in the same round of the vote."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from vllm_omni_b200 import peer
+        try:
+            peer.PeerMemory.create(None, 4096, device="cpu")
+            res = "created"
+        except peer.PeerSetupError as e:
+            res = str(e)
+        q_out.put((rank, res))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_memory_setup_failure_is_agreed_by_all_ranks():
+    """bench.py falls back to NCCL only if EVERY rank gives up on peer memory: `PeerMemory.create` votes after each
+    transport, so a rank whose mapping failed cannot leave the others waiting inside a peer kernel. On this CPU box
+    both transports fail; both ranks must raise PeerSetupError naming both ('symm: ... | ipc: ...')."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_setup_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=180) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert set(got) == {0, 1}
+    for r, msg in got.items():
+        assert msg != "created" and "symm:" in msg and "ipc:" in msg and " | " in msg, (r, msg)
+    assert got[0] == got[1]
