@@ -37,6 +37,11 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n, bool a_mn_m
          (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 
+// the three encodings the prefill kernel issues (verified on B200 by the parity tests of paged_prefill_umma.cu)
+static_assert(umma_idesc_bf16(128, 128, false, false) == 0x08200490u, "m128 n128, A/B K-major");
+static_assert(umma_idesc_bf16(128, 64, false, false) == 0x08100490u, "m128 n64, A/B K-major");
+static_assert(umma_idesc_bf16(128, 128, false, true) == 0x08210490u, "m128 n128, B MN-major");
+
 // D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread on behalf of the CTA.
 __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                              bool accumulate) {
