@@ -3,7 +3,7 @@
 The cross-rank flag protocol is exercised on ONE device: `PeerAllReduce.local_ranks(world)` builds `world`
 'ranks' whose peer regions are plain allocations on cuda:0, each launched on its own stream, so the
 kernels wait for each other exactly as ranks on different GPUs do. (The real multi-process transports are
-covered by tests/test_gpu_peer_multi.py on a 2-GPU box and by `bench.py --gpus N`.)"""
+covered by scripts/peer_check.py under torchrun on 2, 4 and 8 GPUs and by `bench.py --gpus N`.)"""
 import pytest
 import torch
 
