@@ -39,9 +39,43 @@ def bits(t: torch.Tensor) -> np.ndarray:
     return t.detach().cpu().contiguous().view(torch.int16).numpy()
 
 
+PREFILL_CASES = {
+    # name: (seq_lens incl. the new tokens, new tokens per sequence, hq, hkv, seed): prefill, extend, single-token row
+    "prefill_32q4kv": ([130, 17, 64], [40, 17, 1], 32, 4, 21),
+    "prefill_16q2kv": ([48, 150], [48, 33], 16, 2, 22),
+}
+
+
+def prefill(out_dir: Path):
+    """vLLM's FLASH_ATTN backend call for max_query_len > 1 (flash_attn.py:758-819) on the same kind of cache."""
+    from vllm import _custom_ops as vops
+    from vllm.vllm_flash_attn import flash_attn_varlen_func
+    for name, (lens, q_lens, hq, hkv, seed) in PREFILL_CASES.items():
+        c = make_case(lens, hq=hq, hkv=hkv, seed=seed)
+        d, bs, nb = 128, c.block_size, c.num_blocks
+        kv = torch.zeros(2, nb, bs, hkv, d, dtype=torch.bfloat16, device="cuda")
+        one = torch.ones(1, dtype=torch.float32, device="cuda")
+        vops.reshape_and_cache_flash(c.hist_k.cuda(), c.hist_v.cuda(), kv[0], kv[1], c.slots.cuda(), "auto", one, one)
+        g = torch.Generator().manual_seed(seed + 100)
+        q = torch.randn(sum(q_lens), hq, d, generator=g).to(torch.bfloat16)
+        qsl = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32)
+        out = torch.empty_like(q, device="cuda")
+        flash_attn_varlen_func(q.cuda(), kv[0], kv[1], max_seqlen_q=max(q_lens), cu_seqlens_q=qsl.cuda(),
+                               max_seqlen_k=c.max_seq_len, seqused_k=c.seq_lens.cuda(), softmax_scale=c.scale,
+                               causal=True, block_table=c.block_table.cuda(), out=out, fa_version=2)
+        torch.cuda.synchronize()
+        np.savez_compressed(out_dir / f"vllm_{name}.npz", q=bits(q), cache_vllm=bits(kv), block_table=c.block_table.numpy(),
+                            seq_lens=c.seq_lens.numpy(), query_start_loc=qsl.numpy(), scale=np.float32(c.scale), hq=hq,
+                            hkv=hkv, seed=seed, out_fa2=bits(out))
+        print(f"{name}: wrote out_fa2")
+
+
 def main(out_dir: Path):
     out_dir.mkdir(parents=True, exist_ok=True)
     assert torch.cuda.is_available()
+    if "--prefill-only" in sys.argv:
+        return prefill(out_dir)
+    prefill(out_dir)
     from vllm import _custom_ops as vops
     for name, (lens, hq, hkv, seed) in CASES.items():
         c = make_case(lens, hq=hq, hkv=hkv, seed=seed)
@@ -88,4 +122,4 @@ def main(out_dir: Path):
 
 
 if __name__ == "__main__":
-    main(Path(sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/golden"))
+    main(Path(sys.argv[1] if len(sys.argv) > 1 and not sys.argv[1].startswith("--") else "gpurun_out/golden"))

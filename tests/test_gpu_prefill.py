@@ -135,3 +135,27 @@ def test_prefill_long_chunk_properties(lib):
                              S // 2, c.scale)
     torch.cuda.synchronize()
     assert torch.equal(out2, out[S // 2:])
+
+
+@pytest.mark.parametrize("name", ["vllm_prefill_32q4kv.npz", "vllm_prefill_16q2kv.npz"])
+def test_prefill_against_vllm_flash_attn_fixtures(lib, name):
+    """Committed outputs of vLLM's own FLASH_ATTN prefill call (FlashAttention-2 paged varlen,
+    tests/golden/gen_vllm_gpu_golden.py): both prefill kernels must agree with the oracle to 2e-3 and with the stock
+    kernel to a few bf16 roundings of the output scale."""
+    import numpy as np
+    from pathlib import Path
+    z = np.load(Path(__file__).resolve().parent / "golden" / name)
+    hq, hkv = int(z["hq"]), int(z["hkv"])
+    c = make_case(z["seq_lens"].tolist(), hq=hq, hkv=hkv, seed=int(z["seed"]))
+    q = torch.from_numpy(z["q"].copy()).view(torch.bfloat16)
+    qsl = torch.from_numpy(z["query_start_loc"].copy())
+    q_lens = (qsl[1:] - qsl[:-1]).tolist()
+    cache = cache_to_dev(c.kv_cache)
+    out = torch.full(q.shape, 7.0, dtype=torch.bfloat16, device="cuda")
+    ops.paged_prefill(q.cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl.cuda(), max(q_lens),
+                      float(z["scale"]), out=out)
+    torch.cuda.synchronize()
+    ref = oracle.ref_paged_prefill(q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, float(z["scale"]))
+    check(out, ref)
+    stock = torch.from_numpy(z["out_fa2"].copy()).view(torch.bfloat16).float()
+    assert float((out.cpu().float() - stock).abs().max()) <= 2 ** -6 * float(stock.abs().max())

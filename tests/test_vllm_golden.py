@@ -64,3 +64,24 @@ def test_decode_oracle_within_tolerance_of_vllm_stock_kernels(name):
     if len(present) == 2:                              # the two stock kernels agree with each other to bf16 rounding
         a, b = bf16(z[present[0]]).float(), bf16(z[present[1]]).float()
         assert float((a - b).abs().max()) <= 2 ** -7 * float(a.abs().max())
+
+
+PREFILL_FILES = ["vllm_prefill_32q4kv.npz", "vllm_prefill_16q2kv.npz"]
+
+
+@pytest.mark.parametrize("name", PREFILL_FILES)
+def test_prefill_oracle_within_tolerance_of_vllm_flash_attn(name):
+    """The causal varlen oracle (`ref_paged_prefill`) against vLLM's FLASH_ATTN call for max_query_len > 1
+    (FlashAttention-2 paged varlen, flash_attn.py:758-819) on prefill / extend / single-token rows."""
+    p = GOLDEN / name
+    assert p.exists(), f"{p} missing: run tests/golden/gen_vllm_gpu_golden.py on a GPU box with vLLM"
+    z = np.load(p)
+    c = make_case(z["seq_lens"].tolist(), hq=int(z["hq"]), hkv=int(z["hkv"]), seed=int(z["seed"]))
+    kv = bf16(z["cache_vllm"])
+    assert torch.equal(c.kv_cache.contiguous().view(torch.int16), kv.view(torch.int16))   # same cache as vLLM wrote
+    q = bf16(z["q"])
+    qsl = torch.from_numpy(z["query_start_loc"].copy())
+    ref = oracle.ref_paged_prefill(q, kv[0], kv[1], c.block_table, c.seq_lens, qsl, float(z["scale"]))
+    stock = bf16(z["out_fa2"])
+    e, l2 = excess_rel_err(stock, ref), kernel_rel_l2(stock, ref)
+    assert e <= 2e-3 and l2 <= 2e-3, (name, e, l2)
