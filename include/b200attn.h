@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 7
+#define B200ATTN_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -58,7 +58,20 @@ extern "C" {
 #define B200ATTN_VARIANT_TMA 1      /* persistent, TMA-staged pages, mbarrier ring       */
 #define B200ATTN_VARIANT_CPASYNC 2  /* one CTA per work item, cp.async-staged pages      */
 #define B200ATTN_VARIANT_STREAM 3   /* persistent, per-warp cp.async rings across items  */
-#define B200ATTN_VARIANT_STREAMK 4  /* persistent, equal tile chunks per warp (default)  */
+#define B200ATTN_VARIANT_STREAMK 4  /* persistent, equal tile chunks per warp + reduce launch (round-1 default) */
+#define B200ATTN_VARIANT_SK2 5      /* the same schedule, planned once per step, merge inside the kernel (default) */
+
+/* b200attn_paged_decode flags */
+#define B200ATTN_DECODE_PLANNED 1        /* b200attn_decode_plan was run on this workspace for exactly these
+                                            seq_lens / block_table / batch / head counts / block_size (once per
+                                            step; every layer of the step then skips the plan launch) */
+#define B200ATTN_DECODE_EARLY_KV_READ 2  /* the caller guarantees that, among this library's kernels still in
+                                            flight when the decode kernel starts (they release their dependents
+                                            early: programmatic dependent launch), the only KV-cache bytes being
+                                            written are the new token's slot of each decoded sequence, i.e. its
+                                            LAST 16-token tile — what a decode step's cache write does
+                                            (gpu_ar_model_runner.py:421-456 slot mappings). The kernel may then
+                                            stage all other KV tiles before griddepcontrol.wait. */
 
 B200ATTN_API int b200attn_abi_version(void);
 B200ATTN_API const char* b200attn_last_error(void); /* host string, thread-local */
@@ -141,12 +154,26 @@ B200ATTN_API size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t n
                                        int32_t head_size, int32_t max_splits);
 
 /*
- * One-time preparation of a decode workspace: zeroes its control words (the first 256 bytes:
- * the stream-K claim counter and finished-warp counter). Call once after allocating the
- * workspace (or allocate it zero-filled); the library leaves the control words zero after
- * every launch, so graphs can be replayed without re-initialising.
+ * One-time preparation of a decode workspace: zeroes its control area (the first 4 KiB:
+ * stream-K claim / arrival counters). Call once after allocating the workspace (or allocate it
+ * zero-filled); the library leaves the control area zero after every launch, so graphs can be
+ * replayed without re-initialising. A workspace must be at least 4 KiB.
  */
 B200ATTN_API int b200attn_workspace_init(void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Stream-K plan of one decode step (what FlashAttention's get_scheduler_metadata / FlashInfer's plan()
+ * do for the stock backends: vllm/v1/attention/backends/flash_attn.py:388-575): tiles prefix per
+ * sequence, the start position of every warp's chunk of the step's KV-tile stream and the block ids
+ * it starts with, written into `workspace`. One small launch per STEP; every layer's
+ * b200attn_paged_decode of that step then passes B200ATTN_DECODE_PLANNED with the same seq_lens,
+ * block_table, batch, head counts, block_size and workspace. Without the flag b200attn_paged_decode
+ * runs this launch itself before every decode kernel.
+ */
+B200ATTN_API int b200attn_decode_plan(
+    const int32_t* seq_lens, int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+    const int32_t* block_table, int64_t block_table_stride, int32_t block_size,
+    void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * Paged decode attention (query length 1 per sequence). Replaces the decode branch of
@@ -163,15 +190,15 @@ B200ATTN_API int b200attn_workspace_init(void* workspace, size_t workspace_bytes
  * fp8 caches are dequantised as float(e4m3) * scale[kvh or 0].
  * S_b == 0 => out row = 0, lse = -inf.
  *
- * Two launches: the split-K partial kernel (online softmax per KV range, fp32 partial
- * outputs + LSE into `workspace`) and the LSE-reduce kernel. KV ranges that cover a whole
- * sequence are written to `out` directly by the first kernel.
- *
  * Schedules: with num_splits == 0 and variant AUTO (what the backend uses) the KV tiles of
  * the whole step are cut into equal contiguous chunks, one per warp of a persistent grid
- * ("stream-K": no split count, balanced for ragged batches, needs batch <= 2048 and the
- * workspace of b200attn_decode_workspace_bytes; otherwise the fixed-split schedule is
- * used). With num_splits >= 1 every sequence is cut into that many equal KV ranges.
+ * ("stream-K", B200ATTN_VARIANT_SK2: no split count, balanced for ragged batches, any batch;
+ * needs block_size = 16 * 2^k and the workspace of b200attn_decode_workspace_bytes, otherwise the
+ * fixed-split schedule is used). ONE launch: a warp that leaves a partial (online softmax state of
+ * a KV range, fp32 output + LSE in `workspace`) counts it, and the last arriver of an item merges
+ * its partials by their LSE inside the kernel. With num_splits >= 1 (or an explicit fixed-split
+ * variant) every sequence is cut into that many equal KV ranges and a separate LSE-reduce kernel
+ * merges them (two launches).
  *
  * q:   bf16 [batch, num_q_heads, head_size], token stride given, head stride = head_size
  * out: bf16 [batch, num_q_heads, head_size], token stride given
@@ -182,6 +209,7 @@ B200ATTN_API int b200attn_workspace_init(void* workspace, size_t workspace_bytes
  * num_splits: 0 = automatic (stream-K, or the split heuristic for the fixed-split variants),
  *             else forced (1 = no split, no reduce launch)
  * variant: B200ATTN_VARIANT_*
+ * flags: B200ATTN_DECODE_* (0 = self-contained call, no assumption about what runs before it)
  */
 B200ATTN_API int b200attn_paged_decode(
     const void* q, int64_t q_stride_tok,
@@ -195,12 +223,13 @@ B200ATTN_API int b200attn_paged_decode(
     int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
     float softmax_scale, int32_t kv_dtype,
     const float* k_scale, const float* v_scale, int32_t scale_numel,
-    int32_t num_splits, int32_t variant,
+    int32_t num_splits, int32_t variant, int32_t flags,
     void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * The two launches of b200attn_paged_decode, exported separately for profiling sweeps.
- * `num_splits` must be >= 1 here unless variant is B200ATTN_VARIANT_STREAMK (which ignores it);
+ * `num_splits` must be >= 1 here unless variant is B200ATTN_VARIANT_STREAMK / _SK2 (which ignore it;
+ * with _SK2 "partial" is the whole operation and the reduce call does nothing);
  * AUTO means B200ATTN_VARIANT_STREAM. partial writes workspace (and `out` rows finished by a
  * single KV range); reduce merges the rows that were cut. Both calls must be given the same
  * batch, head counts, num_splits, variant and workspace.
@@ -217,7 +246,7 @@ B200ATTN_API int b200attn_paged_decode_partial(
     int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
     float softmax_scale, int32_t kv_dtype,
     const float* k_scale, const float* v_scale, int32_t scale_numel,
-    int32_t num_splits, int32_t variant,
+    int32_t num_splits, int32_t variant, int32_t flags,
     void* workspace, size_t workspace_bytes, void* stream);
 
 B200ATTN_API int b200attn_lse_reduce(

@@ -28,9 +28,18 @@ ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, hq, d, 1))
 out_ours = torch.empty(B, hq, d, dtype=torch.bfloat16, device="cuda")
 
 
-def ours(kc, vc, out):
-    ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len, inp.softmax_scale, out=out,
-                     kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale, v_scale=inp.v_scale, workspace=ws)
+def make_ours(variant, planned=False, early=False, write=False):
+    def fn(kc, vc, out):
+        if write:
+            ops.reshape_and_cache(inp.new_k, inp.new_v, kc, vc, inp.slot_mapping, wl.kv_cache_dtype, inp.k_scale,
+                                  inp.v_scale)
+        ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len, inp.softmax_scale, out=out,
+                         kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale, v_scale=inp.v_scale, workspace=ws,
+                         variant=variant, planned=planned, early_kv_read=early)
+    return fn
+
+
+ours = make_ours(ops.VARIANT_AUTO)
 
 
 def timed(fn, reps=7):
@@ -79,7 +88,16 @@ def report(name, fn, note=""):
 
 ours(caches[0][0], caches[0][1], out_ours)
 torch.cuda.synchronize()
-report("b200attn stream-K (this repo: decode + reduce)", ours)
+ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)  # the step's plan (planned modes)
+report("b200attn stream-K v2 (default call: plan launch + decode with the merge inside)", ours)
+report("b200attn stream-K v2, planned once per step", make_ours(ops.VARIANT_SK2, planned=True))
+report("b200attn stream-K v2, planned + early KV reads (what the backend passes)",
+       make_ours(ops.VARIANT_SK2, planned=True, early=True))
+report("b200attn stream-K v2, planned + early, cache write + decode per layer",
+       make_ours(ops.VARIANT_SK2, planned=True, early=True, write=True), note="two launches per layer")
+report("b200attn stream-K v1 (round 1: decode + reduce launch)", make_ours(ops.VARIANT_STREAMK))
+report("b200attn stream-K v1, cache write + decode + reduce per layer", make_ours(ops.VARIANT_STREAMK, write=True),
+       note="three launches per layer")
 
 fp8 = wl.fp8
 if fp8:

@@ -19,7 +19,7 @@ def declared_symbols() -> list[str]:
 def test_header_declares_the_expected_entry_points():
     syms = declared_symbols()
     for name in ("b200attn_reshape_and_cache", "b200attn_paged_decode", "b200attn_paged_decode_partial",
-                 "b200attn_lse_reduce", "b200attn_decode_workspace_bytes", "b200attn_abi_version",
+                 "b200attn_lse_reduce", "b200attn_decode_workspace_bytes", "b200attn_abi_version", "b200attn_decode_plan",
                  "b200attn_last_error", "b200attn_paged_prefill", "b200attn_gather_kv"):
         assert name in syms
 
@@ -69,15 +69,26 @@ def test_split_heuristic_is_pure_host_arithmetic(lib):
 def test_workspace_bytes_formula(lib):
     f = lib.b200attn_decode_workspace_bytes
     assert f(0, 32, 128, 4) == 0
-    # max(fixed-split need, stream-K need); without a GPU the stream-K part assumes 148 SMs x 12 warps
-    # layout: 256 B of control words, partial O rows, partial LSEs (+ stream-K: the tiles-prefix plan)
+    # max over the schedules; without a GPU the stream-K parts assume 148 SMs x 12 warps.
+    # Every layout starts with a 4 KiB control area; then partial O rows and partial LSEs.
+    ctrl = 4096
     rows = 64 * 32 * 8
-    fixed = 256 + rows * 128 * 4 + rows * 4 + 256
-    # stream-K: two partial slots per chunk; one static chunk per warp (+1), no claimed chunks by default
+    fixed = ctrl + rows * 128 * 4 + rows * 4 + 256
+    # stream-K v1: two partial slots per chunk (one chunk per warp, +1), then the tiles-prefix plan
     sk_rows = 2 * (148 * 12 + 1) * 8
-    sk = 256 + sk_rows * 128 * 4 + sk_rows * 4 + ((64 + 1 + 3) // 4 * 4) * 4 + 256
-    assert f(64, 32, 128, 8) == max(fixed, sk)
-    assert f(1, 8, 128, 1) == 256 + sk_rows * 128 * 4 + sk_rows * 4 + 4 * 4 + 256
+
+    def sk1(batch):
+        return ctrl + sk_rows * 129 * 4 + ((batch + 1 + 3) // 4 * 4) * 4 + 256
+
+    # stream-K v2 (default): warp partials + two CTA partials per CTA, then the plan
+    # (header 16 | desc 4 x warps | ids 32 x warps | cum batch + 1)
+    def sk2(batch):
+        g_rows = 2 * (148 + 1) * 8
+        plan = 16 + 36 * 148 * 12 + batch + 1
+        return ctrl + (sk_rows + g_rows) * 129 * 4 + (plan + 4) * 4 + 256
+
+    assert f(64, 32, 128, 8) == max(fixed, sk1(64), sk2(64))
+    assert f(1, 8, 128, 1) == sk2(1)
 
 
 def test_zero_token_calls_are_noops_without_a_gpu(lib):

@@ -17,7 +17,7 @@ from vllm_omni_b200 import _lib, layout, ops, workloads
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-3
-VARIANTS = [ops.VARIANT_STREAMK, ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
+VARIANTS = [ops.VARIANT_SK2, ops.VARIANT_STREAMK, ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
 
 
 def run_device(c, variant=ops.VARIANT_AUTO, num_splits=0, want_lse=True, cache_dev=None, q_dev=None):
@@ -161,7 +161,7 @@ def test_abi_errors_surface_as_exceptions(lib):
     c = make_case([100], hq=8, hkv=2, seed=1)
     cache = cache_to_dev(c.kv_cache)
     q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
-    tiny = ops.DecodeWorkspace("cuda", 256)
+    tiny = ops.DecodeWorkspace("cuda", 4096)
     tiny.ensure = lambda n: None  # defeat the auto-grow: the C side must refuse
     with pytest.raises(_lib.B200AttnError, match="EWORKSPACE"):
         ops.paged_decode(q, cache[0], cache[1], bt, sl, 100, c.scale, num_splits=4, workspace=tiny)
@@ -224,7 +224,7 @@ def test_full_size_properties_cfg3(lib, ragged):
                                                    inp.max_seq_len, inp.softmax_scale, lse=lse,
                                                    num_splits=s, variant=variant), lse)
     torch.cuda.synchronize()
-    base, base_lse = outs[(ops.VARIANT_STREAMK, 0)]
+    base, base_lse = outs[(ops.VARIANT_SK2, 0)]
     assert torch.isfinite(base.float()).all()
     # (1) the two staging variants agree (different warp counts => different merge order)
     for v in VARIANTS[1:]:
@@ -269,8 +269,9 @@ def test_fp8_decode_vs_oracle_small(lib, lens, per_head):
 @pytest.mark.parametrize("hq,hkv", [(32, 4), (28, 4), (16, 2), (4, 1), (4, 4), (16, 1), (24, 2)])
 def test_fp8_decode_gqa_group_shapes(lib, hq, hkv):
     c = make_case([200, 77, 16, 1000], hq=hq, hkv=hkv, seed=hq * 10 + hkv + 1, fp8=True)
-    out, lse = run_device(c, ops.VARIANT_STREAMK, 0)
-    check(c, out, lse)
+    for variant in (ops.VARIANT_SK2, ops.VARIANT_STREAMK):
+        out, lse = run_device(c, variant, 0)
+        check(c, out, lse)
 
 
 def test_fp8_masked_tail_and_block_sizes(lib):
@@ -342,3 +343,107 @@ def test_decode_against_vllm_stock_kernel_fixtures(lib, name, variant):
     for key in ("out_fa2", "out_trtllm"):
         stock = torch.from_numpy(z[key].copy()).view(torch.bfloat16).float()
         assert float((out.cpu().float() - stock).abs().max()) <= 2 ** -7 * float(stock.abs().max()), key
+
+
+# ------------------------------------------------------------------------------------------------
+# Stream-K v2 (the default): plan once per step, early KV reads under programmatic dependent launch,
+# CTA-cooperative two-level merge inside the kernel.
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("fp8", [False, True])
+@pytest.mark.parametrize("hq,hkv,lens", [
+    (8, 1, [20000]),                      # one sequence on the whole grid: an item cut into hundreds of pieces
+    (32, 4, [33000]),
+    (4, 1, [3000, 9000, 1]),              # TP8-shard shape, items spanning several CTAs
+    (16, 1, [5000, 4097]),                # two head sub-groups per KV head
+])
+def test_sk2_items_cut_into_many_pieces(lib, hq, hkv, lens, fp8):
+    c = make_case(lens, hq=hq, hkv=hkv, seed=len(lens) + hq, fp8=fp8)
+    for _ in range(2):  # second launch: the arrival counters must have been left at zero by the first
+        out, lse = run_device(c, ops.VARIANT_SK2, 0)
+        check(c, out, lse)
+
+
+def test_sk2_batch_beyond_2048_and_many_items_per_cta(lib):
+    """3000 short sequences (the round-1 stream-K plan lived in shared memory: batch <= 2048), several cut
+    items per CTA, empty sequences in between."""
+    g = torch.Generator().manual_seed(11)
+    lens = torch.randint(0, 70, (3000,), generator=g).tolist()
+    c = make_case(lens, hq=8, hkv=2, seed=77)
+    out, lse = run_device(c, ops.VARIANT_SK2, 0)
+    check(c, out, lse)
+    c8 = make_case(lens[:2500], hq=8, hkv=2, seed=78, fp8=True)
+    out, lse = run_device(c8, ops.VARIANT_AUTO, 0)
+    check(c8, out, lse)
+
+
+def test_sk2_workspace_shared_with_other_variants(lib):
+    """One workspace serves SK2, the round-1 stream-K and a fixed-split kernel in turn: nobody but SK2 touches
+    its arrival counters."""
+    c = make_case([700, 1300, 5, 4000], hq=8, hkv=2, seed=31)
+    cache = cache_to_dev(c.kv_cache)
+    q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
+    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(4, 8, 128, 8))
+    for variant, splits in ((ops.VARIANT_SK2, 0), (ops.VARIANT_STREAMK, 0), (ops.VARIANT_STREAM, 8),
+                            (ops.VARIANT_SK2, 0), (ops.VARIANT_TMA, 4), (ops.VARIANT_SK2, 0)):
+        out = torch.full((4, 8, 128), 3.0, dtype=torch.bfloat16, device="cuda")
+        ops.paged_decode(q, cache[0], cache[1], bt, sl, c.max_seq_len, c.scale, out=out, num_splits=splits,
+                         variant=variant, workspace=ws)
+        check(c, out, None)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+@pytest.mark.parametrize("fp8", [False, True])
+def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8):
+    """A decode step as the backend runs it: ONE plan launch, then per layer cache write -> decode with
+    B200ATTN_DECODE_PLANNED | _EARLY_KV_READ, all launches chained by programmatic dependent launch. Every
+    layer's output must see the token its own cache write stored (the tile a sequence ends in is only loaded
+    after griddepcontrol.wait)."""
+    L = 6
+    lens = [4096, 1, 16, 17, 2049, 800, 4095, 33]
+    cases = [make_case(lens, hq=16, hkv=2, seed=200 + l, fp8=fp8) for l in range(L)]
+    B = len(lens)
+    bt, sl = cases[0].block_table.cuda(), cases[0].seq_lens.cuda()
+    for c in cases[1:]:
+        assert torch.equal(c.block_table, cases[0].block_table)
+    ks, vs = to_dev(cases[0].k_scale), to_dev(cases[0].v_scale)
+    caches = [cache_to_dev(c.kv_cache) for c in cases]
+    g = torch.Generator().manual_seed(5)
+    new_k = [torch.randn(B, 2, 128, generator=g).to(torch.bfloat16) for _ in range(L)]
+    new_v = [torch.randn(B, 2, 128, generator=g).to(torch.bfloat16) for _ in range(L)]
+    last = workloads.slots_of_positions(cases[0].block_table, torch.arange(B), cases[0].seq_lens.long() - 1, 16)
+    new_k_d, new_v_d, last_d = [x.cuda() for x in new_k], [x.cuda() for x in new_v], last.cuda()
+    qs = [c.q.cuda() for c in cases]
+    outs = [torch.zeros(B, 16, 128, dtype=torch.bfloat16, device="cuda") for _ in range(L)]
+    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, 16, 128, 1))
+    kvd = cases[0].kv_cache_dtype
+
+    def step():
+        ops.decode_plan(sl, bt, B, 16, 2, 16, ws)
+        for l in range(L):
+            ops.reshape_and_cache(new_k_d[l], new_v_d[l], caches[l][0], caches[l][1], last_d, kvd, ks, vs)
+            ops.paged_decode(qs[l], caches[l][0], caches[l][1], bt, sl, max(lens), cases[l].scale, out=outs[l],
+                             kv_cache_dtype=kvd, k_scale=ks, v_scale=vs, workspace=ws, planned=True,
+                             early_kv_read=True)
+
+    if graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            step()
+        for o in outs:
+            o.zero_()
+        gr.replay()
+        gr.replay()
+    else:
+        step()
+    torch.cuda.synchronize()
+    for l in range(L):
+        c = cases[l]
+        oracle.ref_reshape_and_cache(new_k[l], new_v[l], c.kv_cache[0], c.kv_cache[1], last, fp8, c.k_scale, c.v_scale)
+        assert torch.equal(caches[l].cpu().view(torch.uint8), c.kv_cache.view(torch.uint8)), f"layer {l}: slot writes"
+        check(c, outs[l], None)

@@ -12,7 +12,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 PEER_FLAG_BYTES = 8192
 AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH, AR_PUSH2 = 0, 1, 2, 3, 4, 5
 KV_BF16 = 0
@@ -22,6 +22,9 @@ VARIANT_TMA = 1
 VARIANT_CPASYNC = 2
 VARIANT_STREAM = 3
 VARIANT_STREAMK = 4
+VARIANT_SK2 = 5
+DECODE_PLANNED = 1
+DECODE_EARLY_KV_READ = 2
 
 ERRORS = {1: "EINVAL", 2: "EUNSUPPORTED", 3: "EWORKSPACE", 4: "EDRIVER"}
 
@@ -53,7 +56,7 @@ _DECODE_ARGS = [
     _i32, _i32, _i32, _i32,          # Hq, Hkv, head_size, block_size
     _f32, _i32,                      # softmax_scale, kv_dtype
     _vp, _vp, _i32,                  # k_scale, v_scale, scale_numel
-    _i32, _i32,                      # num_splits, variant
+    _i32, _i32, _i32,                # num_splits, variant, flags
     _vp, _sz, _vp,                   # workspace, bytes, stream
 ]
 SIGNATURES: dict[str, tuple] = {
@@ -79,6 +82,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200attn_decode_num_splits": (_i32, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
     "b200attn_workspace_init": (C.c_int, [_vp, _sz, _vp]),
+    "b200attn_decode_plan": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i64, _i32, _vp, _sz, _vp]),
     "b200attn_debug_set_trace": (None, [_vp]),
     "b200attn_debug_sk_schedule": (None, [_i64, _i32, _i32, C.POINTER(_i64)]),
     "b200attn_paged_decode": (C.c_int, _DECODE_ARGS),

@@ -243,7 +243,13 @@ int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64
 
 // stream-K workspace: 2 partial slots per warp of the persistent grid (O rows then LSE), then the
 // tiles-prefix plan.
-constexpr size_t kWsCtrlBytes = 256;
+// Control area at the head of every decode workspace, zeroed once by b200attn_workspace_init and left
+// zero by every kernel: [0, 256) stream-K v1 words, [256, ...) the arrival counters of stream-K v2
+// (one word per CTA of the persistent grid). No variant writes anything else here, so one workspace can
+// serve different variants in turn.
+constexpr size_t kWsCtrlBytes = 4096;
+constexpr size_t kWsSk2CntOff = 256;
+constexpr int kSk2MaxCtas = static_cast<int>((kWsCtrlBytes - kWsSk2CntOff) / 4) - 1;
 size_t fixed_workspace_bytes(int batch, int num_q_heads, int head_size, int splits) {
   const size_t rows = static_cast<size_t>(batch) * num_q_heads * splits;
   return kWsCtrlBytes + rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
@@ -269,6 +275,31 @@ size_t sk_workspace_bytes(int batch, int sms) {
   const size_t rows = sk_part_rows(sms);
   return kWsCtrlBytes + rows * kHeadDim * sizeof(float) + rows * sizeof(float) +
          ((static_cast<size_t>(batch) + 1 + 3) / 4 * 4) * sizeof(int32_t) + 256;
+}
+
+// stream-K v2 (paged_decode_sk2.cu) workspace: [control | part_o | gpart_o | part_lse | gpart_lse | plan]
+size_t sk2_part_rows(int nw) { return static_cast<size_t>(2) * (static_cast<size_t>(nw) + 1) * kHeadsPerItem; }
+size_t sk2_workspace_bytes(int batch, int sms) {
+  const int nw = sms * decode_sk2_warps();
+  const size_t rows = sk2_part_rows(nw), grows = sk2_part_rows(sms);
+  return kWsCtrlBytes + (rows + grows) * (kHeadDim + 1) * sizeof(float) +
+         (sk2_plan_ints(batch, nw) + 4) * sizeof(int32_t) + 256;
+}
+struct Sk2Layout {
+  float *part_o, *part_lse, *gpart_o, *gpart_lse;
+  int32_t *cnt2, *plan;
+};
+Sk2Layout sk2_layout(void* workspace, int sms) {
+  const size_t rows = sk2_part_rows(sms * decode_sk2_warps()), grows = sk2_part_rows(sms);
+  uint8_t* base = static_cast<uint8_t*>(workspace);
+  Sk2Layout l;
+  l.cnt2 = reinterpret_cast<int32_t*>(base + kWsSk2CntOff);
+  l.part_o = reinterpret_cast<float*>(base + kWsCtrlBytes);
+  l.gpart_o = l.part_o + rows * kHeadDim;
+  l.part_lse = l.gpart_o + grows * kHeadDim;
+  l.gpart_lse = l.part_lse + rows;
+  l.plan = reinterpret_cast<int32_t*>(l.gpart_lse + grows);
+  return l;
 }
 
 thread_local unsigned long long* g_trace = nullptr;
@@ -463,7 +494,9 @@ size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads, i
   int sms = cached_num_sms();
   if (sms <= 0) sms = 148;
   const size_t sk = sk_workspace_bytes(max_batch, sms);
-  return fixed > sk ? fixed : sk;
+  const size_t sk2 = sk2_workspace_bytes(max_batch, sms);
+  const size_t m = fixed > sk ? fixed : sk;
+  return m > sk2 ? m : sk2;
 }
 
 static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t q_stride_tok,
@@ -474,7 +507,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
                        int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
                        int32_t head_size, int32_t block_size, float softmax_scale, int32_t kv_dtype,
                        const float* k_scale, const float* v_scale, int32_t scale_numel,
-                       int32_t num_splits, int32_t variant, void* workspace, size_t workspace_bytes,
+                       int32_t num_splits, int32_t variant, int32_t flags, void* workspace, size_t workspace_bytes,
                        void* stream_v) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   if (batch < 0) return fail(B200ATTN_EINVAL, "batch < 0");
@@ -493,11 +526,30 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
 
   if (num_splits < 0 || num_splits > kMaxSplits)
     return fail(B200ATTN_EINVAL, "num_splits %d out of [0, %d]", num_splits, kMaxSplits);
-  if (variant < B200ATTN_VARIANT_AUTO || variant > B200ATTN_VARIANT_STREAMK)
+  if (variant < B200ATTN_VARIANT_AUTO || variant > B200ATTN_VARIANT_SK2)
     return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
-  // schedule: stream-K (equal tile chunks per warp, no split count) unless the caller asks for a
-  // fixed split count or a fixed-split kernel
-  bool use_sk = variant == B200ATTN_VARIANT_STREAMK || (variant == B200ATTN_VARIANT_AUTO && num_splits == 0);
+  if (flags & ~(B200ATTN_DECODE_PLANNED | B200ATTN_DECODE_EARLY_KV_READ))
+    return fail(B200ATTN_EINVAL, "unknown decode flags 0x%x", flags);
+  // schedule: stream-K v2 (equal tile chunks per warp, no split count, merge inside the kernel) unless the
+  // caller asks for a fixed split count or another kernel
+  bool use_sk2 = variant == B200ATTN_VARIANT_SK2 || (variant == B200ATTN_VARIANT_AUTO && num_splits == 0);
+  if (use_sk2) {
+    const int tpp = block_size / kTileTokens;
+    const bool fits = workspace != nullptr && tpp > 0 && (tpp & (tpp - 1)) == 0 &&
+                      sk2_workspace_bytes(batch, sms) <= workspace_bytes && sms <= kSk2MaxCtas &&
+                      (reinterpret_cast<uintptr_t>(workspace) % 16) == 0;
+    if (!fits) {
+      if (variant == B200ATTN_VARIANT_SK2 || (flags & B200ATTN_DECODE_PLANNED))
+        return fail(B200ATTN_EWORKSPACE,
+                    "stream-K needs block_size = 16 * 2^k and a 16-byte aligned workspace of %zu B (got %zu)",
+                    sk2_workspace_bytes(batch, sms), workspace_bytes);
+      use_sk2 = false;  // AUTO: fall back to the fixed-split schedule
+    }
+  }
+  if (use_sk2) variant = B200ATTN_VARIANT_SK2;
+  if ((flags & B200ATTN_DECODE_PLANNED) && !use_sk2)
+    return fail(B200ATTN_EINVAL, "B200ATTN_DECODE_PLANNED is only meaningful for the stream-K schedule");
+  bool use_sk = variant == B200ATTN_VARIANT_STREAMK;
   if (use_sk) {
     const int tpp = block_size / kTileTokens;
     const bool fits = batch <= kSkMaxBatch && workspace != nullptr && tpp > 0 && (tpp & (tpp - 1)) == 0 &&
@@ -516,7 +568,13 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   float* part_o = nullptr;
   float* part_lse = nullptr;
   int32_t* plan_cum = nullptr;
-  if (use_sk) {
+  Sk2Layout sk2{};
+  if (use_sk2) {
+    num_splits = 1;
+    sk2 = sk2_layout(workspace, sms);
+    part_o = sk2.part_o;
+    part_lse = sk2.part_lse;
+  } else if (use_sk) {
     num_splits = 1;
     const size_t rows = sk_part_rows(sms);
     part_o = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + kWsCtrlBytes);
@@ -563,6 +621,11 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   p.sk_ctrl = static_cast<int32_t*>(workspace);
   p.sk_dyn_shift = use_sk ? sk_dyn_shift() : 0;
   p.trace = g_trace;
+  p.sk2_plan = sk2.plan;
+  p.gpart_o = sk2.gpart_o;
+  p.gpart_lse = sk2.gpart_lse;
+  p.cnt2 = sk2.cnt2;
+  p.flags = 0;
   const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
   if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
   p.total_items = static_cast<int32_t>(items);
@@ -577,10 +640,10 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
     const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
     if (fp8) {
-      if (variant != B200ATTN_VARIANT_STREAMK)
+      if (variant != B200ATTN_VARIANT_STREAMK && variant != B200ATTN_VARIANT_SK2)
         return fail(B200ATTN_EUNSUPPORTED,
-                    "fp8 KV decode is built for the stream-K schedule only (variant AUTO/STREAMK, num_splits 0, "
-                    "batch <= %d, block_size = 16 * 2^k)", kSkMaxBatch);
+                    "fp8 KV decode is built for the stream-K schedule only (variant AUTO/SK2/STREAMK, num_splits 0, "
+                    "block_size = 16 * 2^k, workspace of b200attn_decode_workspace_bytes)");
       if (k_scale == nullptr || v_scale == nullptr) return fail(B200ATTN_EINVAL, "fp8 cache needs scales");
       if (scale_numel != 1 && scale_numel != num_kv_heads)
         return fail(B200ATTN_EINVAL, "scale_numel %d must be 1 or num_kv_heads", scale_numel);
@@ -600,7 +663,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     for (int sh = 0; sh < 16; ++sh)
       if ((1 << sh) == p.tiles_per_page) p.tpp_shift = sh;
     p.tpp_mask = p.tiles_per_page - 1;
-    if (variant == B200ATTN_VARIANT_STREAMK && p.tpp_shift < 0) {
+    if ((variant == B200ATTN_VARIANT_STREAMK || variant == B200ATTN_VARIANT_SK2) && p.tpp_shift < 0) {
       // block sizes that are not 16 * 2^k go through the fixed-split kernel
       return fail(B200ATTN_EUNSUPPORTED, "stream-K needs block_size = 16 * 2^k (got %d)", block_size);
     }
@@ -627,6 +690,27 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       e = launch_decode_cpasync(p, stream);
     } else if (variant == B200ATTN_VARIANT_STREAM) {
       e = launch_decode_stream(p, static_cast<int>(items < sms ? items : sms), stream);
+    } else if (variant == B200ATTN_VARIANT_SK2) {
+      const CUtensorMap *mk = nullptr, *mv = nullptr;
+      if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
+                               num_kv_heads, block_size, fp8, &mk))
+        return rc;
+      const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
+      if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
+                               num_kv_heads, block_size, fp8, &mv))
+        return rc;
+      const int warps = decode_sk2_warps();
+      const bool pdl = env_flag("B200ATTN_PDL", true);
+      if (!(flags & B200ATTN_DECODE_PLANNED)) {
+        // no plan of this step in the workspace: make it now; the decode kernel then waits for it first
+        if (cudaError_t pe = launch_sk2_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms * warps, block_table,
+                                             block_table_stride, p.tiles_per_page, p.tpp_shift, sk2.plan, stream))
+          return cuda_fail(pe, "decode plan launch");
+        p.flags |= kSk2FlagWaitFirst;
+      }
+      if ((flags & B200ATTN_DECODE_EARLY_KV_READ) && env_flag("B200ATTN_EARLY_KV_READ", true))
+        p.flags |= kSk2FlagEarlyKvRead;
+      e = launch_decode_sk2(tm_k, *mv, p, fp8, sms, pdl, stream);
     } else if (variant == B200ATTN_VARIANT_STREAMK) {
       const CUtensorMap *mk = nullptr, *mv = nullptr;
       if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
@@ -664,13 +748,13 @@ int b200attn_paged_decode(const void* q, int64_t q_stride_tok, const void* k_cac
                           int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
                           int32_t head_size, int32_t block_size, float softmax_scale,
                           int32_t kv_dtype, const float* k_scale, const float* v_scale,
-                          int32_t scale_numel, int32_t num_splits, int32_t variant, void* workspace,
-                          size_t workspace_bytes, void* stream) {
+                          int32_t scale_numel, int32_t num_splits, int32_t variant, int32_t flags,
+                          void* workspace, size_t workspace_bytes, void* stream) {
   return decode_impl(true, true, q, q_stride_tok, k_cache, v_cache, cache_stride_block,
                      cache_stride_slot, cache_stride_head, num_blocks, out, out_stride_tok, lse,
                      block_table, block_table_stride, seq_lens, batch, max_seq_len, num_q_heads,
                      num_kv_heads, head_size, block_size, softmax_scale, kv_dtype, k_scale, v_scale,
-                     scale_numel, num_splits, variant, workspace, workspace_bytes, stream);
+                     scale_numel, num_splits, variant, flags, workspace, workspace_bytes, stream);
 }
 
 int b200attn_paged_decode_partial(const void* q, int64_t q_stride_tok, const void* k_cache,
@@ -682,29 +766,57 @@ int b200attn_paged_decode_partial(const void* q, int64_t q_stride_tok, const voi
                                   int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size,
                                   int32_t block_size, float softmax_scale, int32_t kv_dtype,
                                   const float* k_scale, const float* v_scale, int32_t scale_numel,
-                                  int32_t num_splits, int32_t variant, void* workspace,
+                                  int32_t num_splits, int32_t variant, int32_t flags, void* workspace,
                                   size_t workspace_bytes, void* stream) {
-  if (variant != B200ATTN_VARIANT_STREAMK && num_splits < 1)
+  if (variant != B200ATTN_VARIANT_STREAMK && variant != B200ATTN_VARIANT_SK2 && num_splits < 1)
     return fail(B200ATTN_EINVAL, "partial needs an explicit num_splits >= 1");
   if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_STREAM;
   return decode_impl(true, false, q, q_stride_tok, k_cache, v_cache, cache_stride_block,
                      cache_stride_slot, cache_stride_head, num_blocks, out, out_stride_tok, lse,
                      block_table, block_table_stride, seq_lens, batch, max_seq_len, num_q_heads,
                      num_kv_heads, head_size, block_size, softmax_scale, kv_dtype, k_scale, v_scale,
-                     scale_numel, num_splits, variant, workspace, workspace_bytes, stream);
+                     scale_numel, num_splits, variant, flags, workspace, workspace_bytes, stream);
 }
 
 int b200attn_lse_reduce(void* out, int64_t out_stride_tok, float* lse, const int32_t* seq_lens,
                         int32_t batch, int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
                         int32_t head_size, int32_t num_splits, int32_t variant, const void* workspace,
                         size_t workspace_bytes, void* stream) {
+  if (variant == B200ATTN_VARIANT_SK2) return 0;  // the merge runs inside the decode kernel
   if (variant != B200ATTN_VARIANT_STREAMK && num_splits < 1)
     return fail(B200ATTN_EINVAL, "reduce needs an explicit num_splits >= 1");
   if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_STREAM;
   return decode_impl(false, true, nullptr, 0, nullptr, nullptr, 0, 0, 0, 0, out, out_stride_tok, lse,
                      nullptr, 0, seq_lens, batch, max_seq_len, num_q_heads, num_kv_heads, head_size, 16,
-                     1.f, B200ATTN_KV_BF16, nullptr, nullptr, 1, num_splits, variant,
+                     1.f, B200ATTN_KV_BF16, nullptr, nullptr, 1, num_splits, variant, 0,
                      const_cast<void*>(workspace), workspace_bytes, stream);
+}
+
+int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                         const int32_t* block_table, int64_t block_table_stride, int32_t block_size,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  if (batch < 0) return fail(B200ATTN_EINVAL, "batch < 0");
+  if (batch == 0) return 0;
+  if (seq_lens == nullptr || block_table == nullptr) return fail(B200ATTN_EINVAL, "null seq_lens/block_table");
+  if (num_q_heads <= 0 || num_kv_heads <= 0 || (num_q_heads % num_kv_heads) != 0)
+    return fail(B200ATTN_EINVAL, "num_q_heads %d not a multiple of num_kv_heads %d", num_q_heads, num_kv_heads);
+  const int sms = cached_num_sms();
+  if (sms <= 0) return cuda_fail(cudaGetLastError(), "device query");
+  const int tpp = block_size / kTileTokens;
+  int shift = -1;
+  for (int sh = 0; sh < 16; ++sh)
+    if ((1 << sh) == tpp && tpp * kTileTokens == block_size) shift = sh;
+  if (shift < 0) return fail(B200ATTN_EUNSUPPORTED, "stream-K needs block_size = 16 * 2^k (got %d)", block_size);
+  if (workspace == nullptr || (reinterpret_cast<uintptr_t>(workspace) % 16) ||
+      sk2_workspace_bytes(batch, sms) > workspace_bytes || sms > kSk2MaxCtas)
+    return fail(B200ATTN_EWORKSPACE, "decode plan needs a 16-byte aligned workspace of %zu B (got %zu)",
+                sk2_workspace_bytes(batch, sms), workspace_bytes);
+  const int group = num_q_heads / num_kv_heads;
+  const int subgroups = (group + kHeadsPerItem - 1) / kHeadsPerItem;
+  const Sk2Layout l = sk2_layout(workspace, sms);
+  cudaError_t e = launch_sk2_plan(seq_lens, batch, num_kv_heads * subgroups, sms * decode_sk2_warps(), block_table,
+                                  block_table_stride, tpp, shift, l.plan, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "decode plan launch");
 }
 
 int b200attn_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {

@@ -24,6 +24,10 @@ constexpr int kSkDepth = 2;        // stream-K: ring stages per warp (8 KiB each
 constexpr int kSkDynPerWarp = 4;   // stream-K: dynamic (claimed) chunks per warp on average, at most
 constexpr int kSkClaimLead = 2;    // stream-K: tiles left in the front's chunk when the next one is claimed
 constexpr int kSkDynShiftDefault = 0;  // stream-K: dynamic share of the stream = 1 / 2^shift (0 = all static)
+constexpr int kSk2PlanHdrInts = 16;     // stream-K v2 plan header (int32 words), see paged_decode_sk2.cu
+constexpr int kSk2PlanMagic = 0x534b3250;  // "SK2P"
+constexpr int kSk2FlagWaitFirst = 1;    // griddepcontrol.wait before the plan is read (plan made by the previous kernel)
+constexpr int kSk2FlagEarlyKvRead = 2;  // KV tiles other than a sequence's last may be loaded before the wait
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -59,6 +63,12 @@ struct DecodeParams {
   int32_t* sk_ctrl;      // stream-K only: {claim counter, finished-warp counter}, zero between launches
   int32_t sk_dyn_shift;  // stream-K only: dynamic share of the stream = 1 / 2^shift (0 = all static)
   unsigned long long* trace;  // debug: per-warp {entry, static end, end} globaltimer stamps, or null
+  // stream-K v2 (paged_decode_sk2.cu)
+  const int32_t* sk2_plan;  // header | desc[nw] | ids[nw][32] | cum[batch + 1]
+  float* gpart_o;           // CTA partials of the two-level merge: slot 2 * cta + {0: item entering, 1: item leaving}
+  float* gpart_lse;
+  int32_t* cnt2;            // arrival counters of items that cross CTA boundaries, by first CTA; zero between launches
+  int32_t flags;            // kSk2Flag*
 };
 
 // Stream-K schedule, computed identically by the decode and the reduce kernel from the tile total:

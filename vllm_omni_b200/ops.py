@@ -9,7 +9,10 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from ._lib import KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check  # noqa: F401
+from ._lib import (DECODE_EARLY_KV_READ, DECODE_PLANNED, KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC,  # noqa: F401
+                   VARIANT_SK2, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check)
+
+WORKSPACE_MIN_BYTES = 4096  # control area (arrival / claim counters), see b200attn_workspace_init
 
 _FP8_NAMES = ("fp8", "fp8_e4m3")
 
@@ -178,13 +181,13 @@ def decode_workspace_bytes(max_batch: int, num_q_heads: int, head_size: int, max
 
 
 class DecodeWorkspace:
-    """Caller-owned split-K scratch (control words, partial outputs + LSE), grown on demand outside
-    graphs. The control words (first 256 bytes) are zeroed once per allocation through
-    `b200attn_workspace_init`; the library keeps them zero between launches."""
+    """Caller-owned split-K scratch (control area, partial outputs + LSE, the step's stream-K plan), grown
+    on demand outside graphs. The control area (first 4 KiB) is zeroed once per allocation through
+    `b200attn_workspace_init`; the library keeps it zero between launches."""
 
     def __init__(self, device: torch.device | str = "cuda", nbytes: int = 0):
         self.device = torch.device(device)
-        self._alloc(max(nbytes, 256))
+        self._alloc(max(nbytes, WORKSPACE_MIN_BYTES))
 
     def _alloc(self, nbytes: int) -> None:
         self.buf = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
@@ -209,7 +212,7 @@ class DecodeWorkspace:
 
 
 def _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_len, softmax_scale,
-                 kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace):
+                 kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace, flags=0):
     _need_cuda(q, k_cache, v_cache, out, lse, block_table, seq_lens)
     code = kv_dtype_code(kv_cache_dtype)
     fp8 = code == KV_FP8_E4M3
@@ -244,7 +247,26 @@ def _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_l
             out.data_ptr(), out.stride(0), lse.data_ptr() if lse is not None else None,
             block_table.data_ptr(), block_table.stride(0), seq_lens.data_ptr(), batch,
             int(max_seq_len), hq, hkv, d, bs, float(softmax_scale), code, ks, vs, sn,
-            int(num_splits), int(variant), ws_ptr, ws_bytes, _stream())
+            int(num_splits), int(variant), int(flags), ws_ptr, ws_bytes, _stream())
+
+
+def decode_plan(seq_lens: torch.Tensor, block_table: torch.Tensor, batch: int, num_q_heads: int,
+                num_kv_heads: int, block_size: int, workspace: DecodeWorkspace) -> None:
+    """Stream-K plan of one decode step (one small launch per STEP, not per layer): every
+    `paged_decode(..., planned=True)` of the step must be given the same seq_lens / block_table /
+    batch / head counts / block size and this workspace."""
+    lib = _lib.load()
+    _need_cuda(seq_lens, block_table)
+    if block_table.dtype != torch.int32 or block_table.ndim != 2 or block_table.stride(1) != 1:
+        raise ValueError("block_table must be int32 [B, max_blocks] with contiguous rows")
+    if seq_lens.dtype != torch.int32 or not seq_lens.is_contiguous():
+        raise ValueError("seq_lens must be contiguous int32")
+    if block_table.shape[0] < batch or seq_lens.numel() < batch:
+        raise ValueError("block_table/seq_lens shorter than the batch")
+    workspace.ensure(decode_workspace_bytes(batch, num_q_heads, 128, 1))
+    check("b200attn_decode_plan", lib.b200attn_decode_plan(
+        seq_lens.data_ptr(), int(batch), int(num_q_heads), int(num_kv_heads), block_table.data_ptr(),
+        block_table.stride(0), int(block_size), workspace.ptr, workspace.nbytes, _stream()))
 
 
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
@@ -253,8 +275,13 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                  lse: torch.Tensor | None = None, kv_cache_dtype: str | int = "auto",
                  k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None,
                  num_splits: int = 0, variant: int = VARIANT_AUTO,
-                 workspace: DecodeWorkspace | None = None) -> torch.Tensor:
-    """Split-K paged decode attention (query length 1). Writes `out` in place and returns it."""
+                 workspace: DecodeWorkspace | None = None, planned: bool = False,
+                 early_kv_read: bool = False) -> torch.Tensor:
+    """Paged decode attention (query length 1). Writes `out` in place and returns it.
+
+    planned: `decode_plan` was run for this step on `workspace` (skips the per-call plan launch).
+    early_kv_read: see B200ATTN_DECODE_EARLY_KV_READ in include/b200attn.h (the caller's cache write of this
+    step only touched the last token of each sequence)."""
     lib = _lib.load()
     if out is None:
         out = torch.empty_like(q)
@@ -262,13 +289,16 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     if batch == 0:
         return out
     if workspace is None:
+        if planned:
+            raise ValueError("planned=True needs the workspace decode_plan() was run on")
         workspace = DecodeWorkspace(q.device)
-    if num_splits != 1 or variant == VARIANT_STREAMK:
+    if num_splits != 1 or variant in (VARIANT_STREAMK, VARIANT_SK2):
         s = num_splits if num_splits > 0 else decode_num_splits(
             batch, hq, k_cache.shape[2], max_seq_len)
         workspace.ensure(decode_workspace_bytes(batch, hq, d, s))
+    flags = (DECODE_PLANNED if planned else 0) | (DECODE_EARLY_KV_READ if early_kv_read else 0)
     args = _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_len,
-                        softmax_scale, kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace)
+                        softmax_scale, kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace, flags)
     check("b200attn_paged_decode", lib.b200attn_paged_decode(*args))
     return out
 
