@@ -59,7 +59,8 @@ extern "C" {
 #define B200ATTN_VARIANT_CPASYNC 2  /* one CTA per work item, cp.async-staged pages      */
 #define B200ATTN_VARIANT_STREAM 3   /* persistent, per-warp cp.async rings across items  */
 #define B200ATTN_VARIANT_STREAMK 4  /* persistent, equal tile chunks per warp + reduce launch (round-1 default) */
-#define B200ATTN_VARIANT_SK2 5      /* the same schedule, planned once per step, merge inside the kernel (default) */
+#define B200ATTN_VARIANT_SK2 5      /* the same schedule planned once per step, chunk sizes follow the SMs' measured
+                                       rates, plan-driven reduce launch (default) */
 
 /* b200attn_paged_decode flags */
 #define B200ATTN_DECODE_PLANNED 1        /* b200attn_decode_plan was run on this workspace for exactly these
@@ -154,10 +155,10 @@ B200ATTN_API size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t n
                                        int32_t head_size, int32_t max_splits);
 
 /*
- * One-time preparation of a decode workspace: zeroes its control area (the first 4 KiB:
+ * One-time preparation of a decode workspace: zeroes its control area (the first 16 KiB:
  * stream-K claim / arrival counters). Call once after allocating the workspace (or allocate it
  * zero-filled); the library leaves the control area zero after every launch, so graphs can be
- * replayed without re-initialising. A workspace must be at least 4 KiB.
+ * replayed without re-initialising. A workspace must be at least 16 KiB.
  */
 B200ATTN_API int b200attn_workspace_init(void* workspace, size_t workspace_bytes, void* stream);
 
@@ -194,11 +195,17 @@ B200ATTN_API int b200attn_decode_plan(
  * the whole step are cut into equal contiguous chunks, one per warp of a persistent grid
  * ("stream-K", B200ATTN_VARIANT_SK2: no split count, balanced for ragged batches, any batch;
  * needs block_size = 16 * 2^k and the workspace of b200attn_decode_workspace_bytes, otherwise the
- * fixed-split schedule is used). ONE launch: a warp that leaves a partial (online softmax state of
- * a KV range, fp32 output + LSE in `workspace`) counts it, and the last arriver of an item merges
- * its partials by their LSE inside the kernel. With num_splits >= 1 (or an explicit fixed-split
- * variant) every sequence is cut into that many equal KV ranges and a separate LSE-reduce kernel
- * merges them (two launches).
+ * fixed-split schedule is used). Two launches: the decode kernel (online softmax per chunk, fp32
+ * partial outputs + LSE into `workspace`; items that lie inside one chunk are written to `out`
+ * directly) and the separate LSE-reduce kernel that merges the partials of the items a chunk
+ * boundary cut. With num_splits >= 1 (or an explicit fixed-split variant) every sequence is cut
+ * into that many equal KV ranges instead.
+ *
+ * Determinism: the stream-K chunk sizes follow per-SM streaming rates that the library measures
+ * over the first launches on a workspace (8 plan launches by default, B200ATTN_SK2_CALIB=n; 0 =
+ * equal shares) and then freezes: from then on the output is a deterministic function of the
+ * inputs; before that, and between different workspaces, results can differ in the last bf16 bit
+ * (a different but equally valid summation order).
  *
  * q:   bf16 [batch, num_q_heads, head_size], token stride given, head stride = head_size
  * out: bf16 [batch, num_q_heads, head_size], token stride given
@@ -228,8 +235,7 @@ B200ATTN_API int b200attn_paged_decode(
 
 /*
  * The two launches of b200attn_paged_decode, exported separately for profiling sweeps.
- * `num_splits` must be >= 1 here unless variant is B200ATTN_VARIANT_STREAMK / _SK2 (which ignore it;
- * with _SK2 "partial" is the whole operation and the reduce call does nothing);
+ * `num_splits` must be >= 1 here unless variant is B200ATTN_VARIANT_STREAMK / _SK2 (which ignore it);
  * AUTO means B200ATTN_VARIANT_STREAM. partial writes workspace (and `out` rows finished by a
  * single KV range); reduce merges the rows that were cut. Both calls must be given the same
  * batch, head counts, num_splits, variant and workspace.

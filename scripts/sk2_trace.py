@@ -1,8 +1,9 @@
 #!/usr/bin/env python
 """Per-warp timeline of the stream-K v2 decode kernel (b200attn_debug_set_trace): for every warp the
-%globaltimer stamps {entry, first stage landed, end of streaming, merges done} of ONE isolated launch
-(device idle before it), plus CUDA-event timings of the launch modes. Usage: sk2_trace.py [workload] [layers]"""
+%globaltimer stamps {entry, first stage landed, end of streaming, merges done} and the SM id of isolated
+launches (device idle before each). Usage: sk2_trace.py [workload] [layers] [tp] [launches]"""
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -14,8 +15,10 @@ from vllm_omni_b200 import _lib, ops, workloads
 wl_name = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
 L = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 tp = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+launches = int(sys.argv[4]) if len(sys.argv) > 4 else 3
+contig = os.environ.get("CONTIG", "0") == "1"
 wl = workloads.WORKLOADS[wl_name]
-inp = workloads.make_decode_inputs(wl, "cuda", num_layers=L, tp_size=tp, rank=0)
+inp = workloads.make_decode_inputs(wl, "cuda", num_layers=L, tp_size=tp, rank=0, contiguous_blocks=contig)
 caches = [ops.split_kv_cache(c) for c in inp.kv_caches]
 B, hq, hkv, d = wl.batch, inp.shard.num_q_heads, inp.shard.num_kv_heads, wl.head_size
 out = torch.empty(B, hq, d, dtype=torch.bfloat16, device="cuda")
@@ -24,7 +27,7 @@ lib = _lib.load()
 sms = ops.num_sms()
 W = 12
 nw = sms * W
-trace = torch.zeros(nw * 4, dtype=torch.int64, device="cuda")
+trace = torch.zeros(nw * 8, dtype=torch.int64, device="cuda")
 ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)
 
 
@@ -34,25 +37,51 @@ def run(kc, vc, planned=True, early=True):
                      variant=ops.VARIANT_SK2, planned=planned, early_kv_read=early)
 
 
-for i in range(3):
-    run(*caches[i % L])
-torch.cuda.synchronize()
-lib.b200attn_debug_set_trace(trace.data_ptr())
-run(*caches[3 % L])
-torch.cuda.synchronize()
-lib.b200attn_debug_set_trace(None)
-t = trace.view(nw, 4).cpu().double()
-t0 = t[:, 0].min()
-cols = [(t[:, i] - t0) / 1e3 for i in range(4)]
-
-
 def mmm(x):
     return [round(x.min().item(), 2), round(x.mean().item(), 2), round(x.max().item(), 2)]
 
 
-sm_end = cols[2].view(sms, W).max(dim=1).values
-sm_first_end = cols[2].view(sms, W).min(dim=1).values
-print(json.dumps({"workload": wl_name, "tp": tp, "kv_bytes": inp.kv_bytes_per_layer,
-                  "entry_us": mmm(cols[0]), "first_landed_us": mmm(cols[1]), "stream_end_us": mmm(cols[2]),
-                  "merge_end_us": mmm(cols[3]), "sm_stream_end_us": mmm(sm_end),
-                  "spread_within_sm_us": mmm(sm_end - sm_first_end)}), flush=True)
+calib_steps = int(os.environ.get("CALIB_STEPS", "12"))
+for i in range(calib_steps):  # a "step" = plan + L layers; the SM weights settle over the first 8 plans
+    ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)
+    for kc, vc in caches:
+        run(kc, vc)
+torch.cuda.synchronize()
+# Sk2Ctrl (csrc/decode_common.cuh) at byte 256: claimed[2][512], finished[2], calib_updates, pad, weight[512], ...
+ctrl = ws.buf[256:256 + 4 * (1024 + 4 + 512 * 3)].view(torch.int32)
+w = ctrl[1028: 1028 + sms].view(torch.float32).cpu()
+print(json.dumps({"calib_updates": int(ctrl[1026]), "weight_min_mean_max_x_sms":
+                  [round(float(w.min()) * sms, 3), round(float(w.mean()) * sms, 3), round(float(w.max()) * sms, 3)]}), flush=True)
+per_sm = []
+for rep in range(launches):
+    lib.b200attn_debug_set_trace(trace.data_ptr())
+    run(*caches[(3 + rep) % L])
+    torch.cuda.synchronize()
+    lib.b200attn_debug_set_trace(None)
+    t = trace.view(nw, 8).cpu().double()
+    t0 = t[:, 0].min()
+    cols = [(t[:, i] - t0) / 1e3 for i in range(4)]
+    smid = t[:, 4].long()
+    # per SM (by hardware id): last warp's end of streaming
+    end_by_sm = torch.zeros(int(smid.max()) + 1)
+    end_by_sm.scatter_reduce_(0, smid, cols[2].float(), reduce="amax")
+    first_by_sm = torch.full((int(smid.max()) + 1,), 1e9)
+    first_by_sm.scatter_reduce_(0, smid, cols[2].float(), reduce="amin")
+    used = torch.zeros(int(smid.max()) + 1, dtype=torch.bool)
+    used[smid] = True
+    per_sm.append(end_by_sm)
+    print(json.dumps({"workload": wl_name, "tp": tp, "launch": rep, "kv_bytes": inp.kv_bytes_per_layer,
+                      "interleave": os.environ.get("B200ATTN_SK2_DEBUG_INTERLEAVE", "0"), "contiguous_blocks": contig,
+                      "smid_max": int(smid.max()), "sms_used": int(used.sum()),
+                      "entry_us": mmm(cols[0]), "first_landed_us": mmm(cols[1]), "stream_end_us": mmm(cols[2]),
+                      "merge_end_us": mmm(cols[3]), "sm_stream_end_us": mmm(end_by_sm[used]),
+                      "spread_within_sm_us": mmm((end_by_sm - first_by_sm)[used])}), flush=True)
+if launches >= 2:
+    a = torch.stack(per_sm)
+    c = torch.corrcoef(a)
+    print(json.dumps({"sm_end_correlation_between_launches": [[round(float(x), 3) for x in r] for r in c],
+                      "slowest_sms_launch0": torch.topk(a[0], 8).indices.tolist(),
+                      "slowest_sms_launch1": torch.topk(a[1], 8).indices.tolist(),
+                      "fastest_sms_launch0": torch.topk(-a[0], 8).indices.tolist(),
+                      "fastest_sms_launch1": torch.topk(-a[1], 8).indices.tolist(),
+                      "sm_end_launch0_by_smid": [round(float(x), 1) for x in a[0]]}), flush=True)

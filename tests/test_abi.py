@@ -70,8 +70,8 @@ def test_workspace_bytes_formula(lib):
     f = lib.b200attn_decode_workspace_bytes
     assert f(0, 32, 128, 4) == 0
     # max over the schedules; without a GPU the stream-K parts assume 148 SMs x 12 warps.
-    # Every layout starts with a 4 KiB control area; then partial O rows and partial LSEs.
-    ctrl = 4096
+    # Every layout starts with a 16 KiB control area; then partial O rows and partial LSEs.
+    ctrl = 16384
     rows = 64 * 32 * 8
     fixed = ctrl + rows * 128 * 4 + rows * 4 + 256
     # stream-K v1: two partial slots per chunk (one chunk per warp, +1), then the tiles-prefix plan
@@ -80,15 +80,15 @@ def test_workspace_bytes_formula(lib):
     def sk1(batch):
         return ctrl + sk_rows * 129 * 4 + ((batch + 1 + 3) // 4 * 4) * 4 + 256
 
-    # stream-K v2 (default): warp partials + two CTA partials per CTA, then the plan
-    # (header 16 | desc 4 x warps | ids 32 x warps | cum batch + 1)
-    def sk2(batch):
-        g_rows = 2 * (148 + 1) * 8
-        plan = 16 + 36 * 148 * 12 + batch + 1
-        return ctrl + (sk_rows + g_rows) * 129 * 4 + (plan + 4) * 4 + 256
+    # stream-K v2 (default): warp partials, then the plan (header 16 | chunk starts warps + 1 | desc 4 x warps |
+    # ids 32 x warps | cum batch + 1 | first/last chunk per item, items <= batch x query heads)
+    def sk2(batch, hq):
+        nw = 148 * 12
+        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 36 * nw + ((batch + 1 + 3) // 4 * 4) + 2 * batch * hq
+        return ctrl + sk_rows * 129 * 4 + (plan + 4) * 4 + 256
 
-    assert f(64, 32, 128, 8) == max(fixed, sk1(64), sk2(64))
-    assert f(1, 8, 128, 1) == sk2(1)
+    assert f(64, 32, 128, 8) == max(fixed, sk1(64), sk2(64, 32))
+    assert f(1, 8, 128, 1) == sk2(1, 8)
 
 
 def test_zero_token_calls_are_noops_without_a_gpu(lib):

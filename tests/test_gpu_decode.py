@@ -161,7 +161,7 @@ def test_abi_errors_surface_as_exceptions(lib):
     c = make_case([100], hq=8, hkv=2, seed=1)
     cache = cache_to_dev(c.kv_cache)
     q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
-    tiny = ops.DecodeWorkspace("cuda", 4096)
+    tiny = ops.DecodeWorkspace("cuda", 16384)
     tiny.ensure = lambda n: None  # defeat the auto-grow: the C side must refuse
     with pytest.raises(_lib.B200AttnError, match="EWORKSPACE"):
         ops.paged_decode(q, cache[0], cache[1], bt, sl, 100, c.scale, num_splits=4, workspace=tiny)
@@ -226,9 +226,10 @@ def test_full_size_properties_cfg3(lib, ragged):
     torch.cuda.synchronize()
     base, base_lse = outs[(ops.VARIANT_SK2, 0)]
     assert torch.isfinite(base.float()).all()
-    # (1) the two staging variants agree (different warp counts => different merge order)
+    # (1) the staging variants agree (different chunking => different merge order). Two independent bf16
+    # roundings of the same value are 2.3e-3 apart in rel-L2, plus each kernel's own P-rounding noise (~1.3e-3)
     for v in VARIANTS[1:]:
-        assert rel_l2(outs[(v, 0)][0], base) < 3e-3
+        assert rel_l2(outs[(v, 0)][0], base) < 3.6e-3
         assert torch.allclose(outs[(v, 0)][1], base_lse, atol=2e-3)
     # (2) split count does not change the result beyond bf16 rounding
     assert rel_l2(outs[(ops.VARIANT_STREAM, 1)][0], base) < 6e-3

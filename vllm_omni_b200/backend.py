@@ -108,6 +108,8 @@ class B200AttentionMetadata:
     decode_num_splits: int
     workspace: ops.DecodeWorkspace
     causal: bool = True
+    # the step's stream-K plan is in `workspace` (made once by the builder; every layer's decode skips its own)
+    decode_planned: bool = False
 
 
 class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadata]):
@@ -142,9 +144,16 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
               fast_build: bool = False) -> B200AttentionMetadata:
         cam = common_attn_metadata
         nd, np_, ndt, npt = split_decodes_and_prefills(cam, decode_threshold=1)
-        # 0 = the library's default schedule (stream-K: equal KV-tile chunks per warp of a persistent
-        # grid, nothing to choose on the host; falls back to fixed splits sized to the workspace)
+        # 0 = the library's default schedule (stream-K: KV-tile chunks per warp of a persistent grid, nothing
+        # to choose on the host; falls back to fixed splits sized to the workspace)
         splits = 0
+        planned = False
+        if nd > 0:
+            # one plan launch per step instead of one per layer (what FlashAttention's scheduler metadata /
+            # FlashInfer's plan() are to the stock builders, flash_attn.py:388-575); no host sync
+            ops.decode_plan(cam.seq_lens, cam.block_table_tensor, nd, self.num_heads_q, self.num_heads_kv,
+                            self.block_size, self.workspace)
+            planned = True
         pqsl, pmax = None, 0
         if np_ > 0:
             pqsl = cam.query_start_loc[nd:] - ndt
@@ -156,7 +165,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             block_table=cam.block_table_tensor, slot_mapping=cam.slot_mapping, num_decodes=nd,
             num_decode_tokens=ndt, num_prefills=np_, num_prefill_tokens=npt,
             prefill_query_start_loc=pqsl, prefill_max_query_len=pmax, decode_num_splits=splits,
-            workspace=self.workspace, causal=cam.causal)
+            workspace=self.workspace, causal=cam.causal, decode_planned=planned)
 
 
 def _batch_sizes(max_num_seqs: int):
@@ -281,10 +290,13 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
                                  workspace=self._split_ws)
             rs.scatter_out(out_grp, nd, out=out[:ndt])
         elif nd > 0:
+            # early_kv_read: the only KV bytes this step's cache write touched in a decoded sequence are its
+            # newest token's (vLLM writes slot_mapping = position seq_len - 1 for a decode), see b200attn.h
             ops.paged_decode(q[:ndt], k_cache, v_cache, md.block_table, md.seq_lens, md.max_seq_len,
                              self.scale, out=out[:ndt], kv_cache_dtype=self._kv_code,
                              k_scale=k_scale, v_scale=v_scale, num_splits=md.decode_num_splits,
-                             workspace=md.workspace)
+                             workspace=md.workspace, planned=md.decode_planned and md.decode_num_splits == 0,
+                             early_kv_read=True)
         if md.num_prefills > 0:
             n = md.num_actual_tokens
             ops.paged_prefill(q[ndt:n], k_cache, v_cache, md.block_table[nd:], md.seq_lens[nd:],

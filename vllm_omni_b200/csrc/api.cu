@@ -243,13 +243,13 @@ int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64
 
 // stream-K workspace: 2 partial slots per warp of the persistent grid (O rows then LSE), then the
 // tiles-prefix plan.
-// Control area at the head of every decode workspace, zeroed once by b200attn_workspace_init and left
-// zero by every kernel: [0, 256) stream-K v1 words, [256, ...) the arrival counters of stream-K v2
-// (one word per CTA of the persistent grid). No variant writes anything else here, so one workspace can
-// serve different variants in turn.
-constexpr size_t kWsCtrlBytes = 4096;
-constexpr size_t kWsSk2CntOff = 256;
-constexpr int kSk2MaxCtas = static_cast<int>((kWsCtrlBytes - kWsSk2CntOff) / 4) - 1;
+// Control area at the head of every decode workspace, zeroed once by b200attn_workspace_init; counters in
+// it are left at zero by every kernel: [0, 256) stream-K v1 words, [256, ...) Sk2Ctrl of stream-K v2
+// (arrival counters, chunk-group claims, per-SM rates and weights). No variant writes anything else here,
+// so one workspace can serve different variants in turn.
+constexpr size_t kWsCtrlBytes = 16384;
+constexpr size_t kWsSk2CtrlOff = 256;
+static_assert(kWsSk2CtrlOff + sizeof(Sk2Ctrl) <= kWsCtrlBytes, "control area too small for Sk2Ctrl");
 size_t fixed_workspace_bytes(int batch, int num_q_heads, int head_size, int splits) {
   const size_t rows = static_cast<size_t>(batch) * num_q_heads * splits;
   return kWsCtrlBytes + rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
@@ -279,26 +279,33 @@ size_t sk_workspace_bytes(int batch, int sms) {
 
 // stream-K v2 (paged_decode_sk2.cu) workspace: [control | part_o | gpart_o | part_lse | gpart_lse | plan]
 size_t sk2_part_rows(int nw) { return static_cast<size_t>(2) * (static_cast<size_t>(nw) + 1) * kHeadsPerItem; }
-size_t sk2_workspace_bytes(int batch, int sms) {
+size_t sk2_workspace_bytes(int batch, int num_q_heads, int sms) {
   const int nw = sms * decode_sk2_warps();
-  const size_t rows = sk2_part_rows(nw), grows = sk2_part_rows(sms);
-  return kWsCtrlBytes + (rows + grows) * (kHeadDim + 1) * sizeof(float) +
-         (sk2_plan_ints(batch, nw) + 4) * sizeof(int32_t) + 256;
+  const size_t rows = sk2_part_rows(nw);
+  // head-groups per sequence <= query heads (one per kv head and 8-head sub-group)
+  return kWsCtrlBytes + rows * (kHeadDim + 1) * sizeof(float) +
+         (sk2_plan_ints(batch, nw, num_q_heads) + 4) * sizeof(int32_t) + 256;
 }
 struct Sk2Layout {
-  float *part_o, *part_lse, *gpart_o, *gpart_lse;
-  int32_t *cnt2, *plan;
+  float *part_o, *part_lse;
+  int32_t* plan;
+  Sk2Ctrl* ctrl;
 };
+int sk2_calib_max() {  // weight updates before the SM weights are frozen (0 = uniform shares, never calibrate)
+  const char* v = getenv("B200ATTN_SK2_CALIB");
+  if (v == nullptr || *v == '\0') return kSk2CalibUpdatesDefault;
+  const int x = atoi(v);
+  return x < 0 ? 0 : x;
+}
+thread_local int g_sk2_parity = 0;
 Sk2Layout sk2_layout(void* workspace, int sms) {
-  const size_t rows = sk2_part_rows(sms * decode_sk2_warps()), grows = sk2_part_rows(sms);
+  const size_t rows = sk2_part_rows(sms * decode_sk2_warps());
   uint8_t* base = static_cast<uint8_t*>(workspace);
   Sk2Layout l;
-  l.cnt2 = reinterpret_cast<int32_t*>(base + kWsSk2CntOff);
+  l.ctrl = reinterpret_cast<Sk2Ctrl*>(base + kWsSk2CtrlOff);
   l.part_o = reinterpret_cast<float*>(base + kWsCtrlBytes);
-  l.gpart_o = l.part_o + rows * kHeadDim;
-  l.part_lse = l.gpart_o + grows * kHeadDim;
-  l.gpart_lse = l.part_lse + rows;
-  l.plan = reinterpret_cast<int32_t*>(l.gpart_lse + grows);
+  l.part_lse = l.part_o + rows * kHeadDim;
+  l.plan = reinterpret_cast<int32_t*>(l.part_lse + rows);
   return l;
 }
 
@@ -494,7 +501,7 @@ size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads, i
   int sms = cached_num_sms();
   if (sms <= 0) sms = 148;
   const size_t sk = sk_workspace_bytes(max_batch, sms);
-  const size_t sk2 = sk2_workspace_bytes(max_batch, sms);
+  const size_t sk2 = sk2_workspace_bytes(max_batch, num_q_heads, sms);
   const size_t m = fixed > sk ? fixed : sk;
   return m > sk2 ? m : sk2;
 }
@@ -536,13 +543,13 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   if (use_sk2) {
     const int tpp = block_size / kTileTokens;
     const bool fits = workspace != nullptr && tpp > 0 && (tpp & (tpp - 1)) == 0 &&
-                      sk2_workspace_bytes(batch, sms) <= workspace_bytes && sms <= kSk2MaxCtas &&
+                      sk2_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes && sms <= kSk2MaxGroups &&
                       (reinterpret_cast<uintptr_t>(workspace) % 16) == 0;
     if (!fits) {
       if (variant == B200ATTN_VARIANT_SK2 || (flags & B200ATTN_DECODE_PLANNED))
         return fail(B200ATTN_EWORKSPACE,
                     "stream-K needs block_size = 16 * 2^k and a 16-byte aligned workspace of %zu B (got %zu)",
-                    sk2_workspace_bytes(batch, sms), workspace_bytes);
+                    sk2_workspace_bytes(batch, num_q_heads, sms), workspace_bytes);
       use_sk2 = false;  // AUTO: fall back to the fixed-split schedule
     }
   }
@@ -622,9 +629,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   p.sk_dyn_shift = use_sk ? sk_dyn_shift() : 0;
   p.trace = g_trace;
   p.sk2_plan = sk2.plan;
-  p.gpart_o = sk2.gpart_o;
-  p.gpart_lse = sk2.gpart_lse;
-  p.cnt2 = sk2.cnt2;
+  p.sk2_ctrl = sk2.ctrl;
   p.flags = 0;
   const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
   if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
@@ -699,17 +704,19 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
                                num_kv_heads, block_size, fp8, &mv))
         return rc;
-      const int warps = decode_sk2_warps();
       const bool pdl = env_flag("B200ATTN_PDL", true);
       if (!(flags & B200ATTN_DECODE_PLANNED)) {
         // no plan of this step in the workspace: make it now; the decode kernel then waits for it first
-        if (cudaError_t pe = launch_sk2_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms * warps, block_table,
-                                             block_table_stride, p.tiles_per_page, p.tpp_shift, sk2.plan, stream))
+        if (cudaError_t pe = launch_sk2_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms, block_table,
+                                             block_table_stride, p.tiles_per_page, p.tpp_shift, sk2.plan, sk2.ctrl,
+                                             sk2_calib_max(), stream))
           return cuda_fail(pe, "decode plan launch");
         p.flags |= kSk2FlagWaitFirst;
       }
       if ((flags & B200ATTN_DECODE_EARLY_KV_READ) && env_flag("B200ATTN_EARLY_KV_READ", true))
         p.flags |= kSk2FlagEarlyKvRead;
+      if (env_flag("B200ATTN_SK2_DEBUG_INTERLEAVE", false)) p.flags |= kSk2FlagDebugInterleave;
+      if ((g_sk2_parity ^= 1) != 0) p.flags |= kSk2FlagParity;  // consecutive launches alternate their claim words
       e = launch_decode_sk2(tm_k, *mv, p, fp8, sms, pdl, stream);
     } else if (variant == B200ATTN_VARIANT_STREAMK) {
       const CUtensorMap *mk = nullptr, *mv = nullptr;
@@ -726,7 +733,11 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     }
     if (e != cudaSuccess) return cuda_fail(e, "paged_decode partial launch");
   }
-  if (run_reduce && use_sk) {
+  if (run_reduce && use_sk2) {
+    const bool pdl = run_partial && env_flag("B200ATTN_PDL", true);
+    cudaError_t e = launch_sk2_reduce(p, sms, pdl, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "sk2_reduce launch");
+  } else if (run_reduce && use_sk) {
     const bool pdl = run_partial && env_flag("B200ATTN_PDL", true);
     cudaError_t e = launch_streamk_reduce(p, sms, pdl, stream);
     if (e != cudaSuccess) return cuda_fail(e, "streamk_reduce launch");
@@ -782,7 +793,6 @@ int b200attn_lse_reduce(void* out, int64_t out_stride_tok, float* lse, const int
                         int32_t batch, int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
                         int32_t head_size, int32_t num_splits, int32_t variant, const void* workspace,
                         size_t workspace_bytes, void* stream) {
-  if (variant == B200ATTN_VARIANT_SK2) return 0;  // the merge runs inside the decode kernel
   if (variant != B200ATTN_VARIANT_STREAMK && num_splits < 1)
     return fail(B200ATTN_EINVAL, "reduce needs an explicit num_splits >= 1");
   if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_STREAM;
@@ -808,14 +818,14 @@ int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_h
     if ((1 << sh) == tpp && tpp * kTileTokens == block_size) shift = sh;
   if (shift < 0) return fail(B200ATTN_EUNSUPPORTED, "stream-K needs block_size = 16 * 2^k (got %d)", block_size);
   if (workspace == nullptr || (reinterpret_cast<uintptr_t>(workspace) % 16) ||
-      sk2_workspace_bytes(batch, sms) > workspace_bytes || sms > kSk2MaxCtas)
+      sk2_workspace_bytes(batch, num_q_heads, sms) > workspace_bytes || sms > kSk2MaxGroups)
     return fail(B200ATTN_EWORKSPACE, "decode plan needs a 16-byte aligned workspace of %zu B (got %zu)",
-                sk2_workspace_bytes(batch, sms), workspace_bytes);
+                sk2_workspace_bytes(batch, num_q_heads, sms), workspace_bytes);
   const int group = num_q_heads / num_kv_heads;
   const int subgroups = (group + kHeadsPerItem - 1) / kHeadsPerItem;
   const Sk2Layout l = sk2_layout(workspace, sms);
-  cudaError_t e = launch_sk2_plan(seq_lens, batch, num_kv_heads * subgroups, sms * decode_sk2_warps(), block_table,
-                                  block_table_stride, tpp, shift, l.plan, static_cast<cudaStream_t>(stream));
+  cudaError_t e = launch_sk2_plan(seq_lens, batch, num_kv_heads * subgroups, sms, block_table, block_table_stride, tpp,
+                                  shift, l.plan, l.ctrl, sk2_calib_max(), static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "decode plan launch");
 }
 

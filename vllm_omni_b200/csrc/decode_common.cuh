@@ -28,8 +28,26 @@ constexpr int kSk2PlanHdrInts = 16;     // stream-K v2 plan header (int32 words)
 constexpr int kSk2PlanMagic = 0x534b3250;  // "SK2P"
 constexpr int kSk2FlagWaitFirst = 1;    // griddepcontrol.wait before the plan is read (plan made by the previous kernel)
 constexpr int kSk2FlagEarlyKvRead = 2;  // KV tiles other than a sequence's last may be loaded before the wait
+constexpr int kSk2FlagParity = 8;        // launch parity: consecutive launches on a stream alternate their claim words
+constexpr int kSk2MaxGroups = 512;      // CTAs of the persistent grid (= SMs) the control area has room for
+constexpr int kSk2CalibMinTiles = 96;   // an SM's rate is only trusted if it streamed at least this many tiles
+constexpr float kSk2CalibGain = 0.7f;   // share of the measured rate in a weight update
+constexpr int kSk2CalibUpdatesDefault = 8;  // weight updates before the weights are frozen (B200ATTN_SK2_CALIB)
+constexpr int kSk2FlagDebugInterleave = 4;  // debug: chunk c on CTA c % grid (timeline experiments; no merge, wrong output)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+
+// Control words of stream-K v2 at byte offset 256 of a decode workspace; all zero after
+// b200attn_workspace_init, counters left at zero by every launch.
+struct Sk2Ctrl {
+  int32_t claimed[2][kSk2MaxGroups];  // chunk group claimed in the launch of parity 0 / 1
+  int32_t finished[2];                // CTAs of the launch that are done
+  int32_t calib_updates;              // weight updates made so far
+  int32_t pad;
+  float weight[kSk2MaxGroups];        // share of the tile stream per SM (0 everywhere: uniform)
+  int32_t stat_tiles[kSk2MaxGroups];  // last launch: tiles the CTA on this SM streamed ...
+  int32_t stat_cycles[kSk2MaxGroups]; // ... and the cycles it took
+};
 
 struct DecodeParams {
   const __nv_bfloat16* q;
@@ -64,10 +82,8 @@ struct DecodeParams {
   int32_t sk_dyn_shift;  // stream-K only: dynamic share of the stream = 1 / 2^shift (0 = all static)
   unsigned long long* trace;  // debug: per-warp {entry, static end, end} globaltimer stamps, or null
   // stream-K v2 (paged_decode_sk2.cu)
-  const int32_t* sk2_plan;  // header | desc[nw] | ids[nw][32] | cum[batch + 1]
-  float* gpart_o;           // CTA partials of the two-level merge: slot 2 * cta + {0: item entering, 1: item leaving}
-  float* gpart_lse;
-  int32_t* cnt2;            // arrival counters of items that cross CTA boundaries, by first CTA; zero between launches
+  const int32_t* sk2_plan;  // layout in paged_decode_sk2.cu
+  Sk2Ctrl* sk2_ctrl;
   int32_t flags;            // kSk2Flag*
 };
 

@@ -23,14 +23,17 @@ cudaError_t launch_decode_streamk(const CUtensorMap& tm_k, const CUtensorMap& tm
                                   int grid, bool pdl, cudaStream_t stream);
 cudaError_t launch_streamk_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream);
 size_t decode_streamk_smem_bytes(bool fp8);
-// stream-K v2: plan once per step + one decode kernel with the merge inside (paged_decode_sk2.cu)
-cudaError_t launch_sk2_plan(const int32_t* seq_lens, int batch, int hs_count, int nw, const int32_t* block_table,
-                            int64_t bt_stride, int tiles_per_page, int tpp_shift, int32_t* plan, cudaStream_t stream);
+// stream-K v2: plan once per step, rate-aware chunk groups, plan-driven reduce kernel (paged_decode_sk2.cu)
+cudaError_t launch_sk2_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, const int32_t* block_table,
+                            int64_t bt_stride, int tiles_per_page, int tpp_shift, int32_t* plan, Sk2Ctrl* ctrl,
+                            int calib_max, cudaStream_t stream);
+size_t sk2_ctrl_bytes();
 cudaError_t launch_decode_sk2(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, bool fp8,
                               int grid, bool pdl, cudaStream_t stream);
 size_t decode_sk2_smem_bytes(bool fp8);
 int decode_sk2_warps();
-size_t sk2_plan_ints(int batch, int nw);
+size_t sk2_plan_ints(int batch, int nw, int hs_count);
+cudaError_t launch_sk2_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream);
 size_t decode_tma_smem_bytes();
 size_t decode_cpasync_smem_bytes();
 

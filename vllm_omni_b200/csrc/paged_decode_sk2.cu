@@ -19,12 +19,14 @@
 //    griddepcontrol.wait and only waits before (a) loading q, (b) issuing the last tile of a
 //    sequence, (c) its first global store. In a chain write -> decode -> write -> decode the next
 //    layer's first stages stream while the previous layer's stragglers finish.
-//  * No second launch. After its streaming loop the CTA merges the partials its own W consecutive chunks
-//    left (sk2_cta_merge: every thread folds one (head, 4 columns) unit with all loads in flight); an item
-//    that crosses CTA boundaries is counted per CTA and the LAST CTA to arrive folds the CTA partials.
-//    Two short levels whatever the number of pieces (TP4/TP8 shards cut an item into 29-57 pieces, one
-//    32k sequence on the whole grid into hundreds), and the cold path runs after the loop, so it cannot
-//    raise the register pressure of the loop.
+//  * SMs do not stream at equal rates under a saturated HBM (a property of where an SM sits: the same SM
+//    pairs finish 30 % later than the fastest in every launch), so the chunk group a CTA runs is the one of
+//    the SM it sits on, sized by the plan kernel in proportion to the rate that SM achieved before.
+//  * The separate log-sum-exp reduce kernel (sk2_reduce_kernel) is plan-driven too: which chunks cut an item
+//    is in the plan, so its CTAs (launched early, programmatic dependent launch) have their piece lists
+//    before the decode kernel ends and need one round of loads after it. (Merging inside the decode kernel
+//    — CTA-cooperative, last-arriver across CTAs — was built and measured: its chain of dependent L2 round
+//    trips at the very end of the kernel cost 8 us against 3.4 us for the pre-launched reduce kernel.)
 //
 // Replaces the decode branch of the reference's stock backends
 // (vllm/v1/attention/backends/flashinfer.py:1694-1822, flash_attn.py:758-819) and their split-KV
@@ -35,13 +37,26 @@
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------------
-// Plan layout (int32 words): header | desc[nw][4] | ids[nw][32] | cum[batch + 1]
+// Plan layout (int32 words): header | cstart[nw + 1] | desc[nw][4] | ids[nw][32] | cum[batch + 1] | item_w[items][2]
+//   cstart[c]  first stream position (tile x head-group) of chunk c; chunk c = CTA group c / W, warp c % W
+//   desc[c]    {sequence, head-group, tile, tiles of the sequence} at cstart[c]
+//   ids[c]     the 32 block ids of the page window chunk c starts in
+//   cum[b]     exclusive prefix of tiles per sequence
+//   item_w[i]  first and last chunk that hold tiles of item i = sequence * hs_count + head-group (reduce kernel)
 // ------------------------------------------------------------------------------------------------
-__host__ __device__ __forceinline__ int64_t sk2_plan_desc_off() { return kSk2PlanHdrInts; }
-__host__ __device__ __forceinline__ int64_t sk2_plan_ids_off(int nw) { return kSk2PlanHdrInts + 4ll * nw; }
-__host__ __device__ __forceinline__ int64_t sk2_plan_cum_off(int nw) { return kSk2PlanHdrInts + 36ll * nw; }
+__host__ __device__ __forceinline__ int64_t sk2_plan_cstart_off() { return kSk2PlanHdrInts; }
+__host__ __device__ __forceinline__ int64_t sk2_plan_desc_off(int nw) { return kSk2PlanHdrInts + ((nw + 1 + 3) & ~3); }
+__host__ __device__ __forceinline__ int64_t sk2_plan_ids_off(int nw) { return sk2_plan_desc_off(nw) + 4ll * nw; }
+__host__ __device__ __forceinline__ int64_t sk2_plan_cum_off(int nw) { return sk2_plan_desc_off(nw) + 36ll * nw; }
 
-size_t sk2_plan_ints(int batch, int nw) { return static_cast<size_t>(sk2_plan_cum_off(nw)) + batch + 1; }
+__host__ __device__ __forceinline__ int64_t sk2_plan_itemw_off(int nw, int batch) {
+  return sk2_plan_cum_off(nw) + ((batch + 1 + 3) & ~3);
+}
+
+size_t sk2_plan_ints(int batch, int nw, int hs_count) {
+  return static_cast<size_t>(sk2_plan_itemw_off(nw, batch)) + 2ull * batch * hs_count;
+}
+size_t sk2_ctrl_bytes() { return sizeof(Sk2Ctrl); }
 
 struct Sk2Pos {
   int b;     // sequence
@@ -50,20 +65,84 @@ struct Sk2Pos {
   int n;     // tiles of sequence b
 };
 
-// One CTA. Phase 1: exclusive prefix of tiles per sequence. Phase 2: start position of every
-// chunk. Phase 3: the 32 block ids of the page window each chunk starts in.
+// Chunk that holds stream position t: the last c in [0, nw) with cstart[c] <= t (empty chunks share their
+// successor's start, so the last one is the chunk that really holds t).
+__device__ __forceinline__ int sk2_chunk_of(const int32_t* cstart, int nw, int t) {
+  int lo = 0, hi = nw;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (cstart[mid] <= t) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// One CTA, once per step.
+//  Phase 0: SM weights. SMs do not stream at equal rates under a saturated HBM — a property of where an SM
+//           sits (the same SM pairs finish 30 % later than the fastest in every launch, profiles/README.md) —
+//           so CTA group g, which is run by the CTA on SM g, gets a share of the stream proportional to the
+//           rate that SM achieved in the previous launches (tiles / cycles, recorded by the decode kernel).
+//           The weights are frozen after `calib_max` updates: from then on a launch is a deterministic
+//           function of its inputs.
+//  Phase 1: exclusive prefix of tiles per sequence. Phase 2: chunk starts (group range cut into W equal
+//           chunks) and their positions. Phase 3: the 32 block ids of the page window each chunk starts in.
+constexpr int kSk2PlanSmemBatch = 4096;  // cum[] of batches up to this size is searched in shared memory
+
+__device__ __forceinline__ float sk2_block_sum(float v, float* s_red, int tid) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  __syncthreads();  // s_red may still be read from the previous call
+  if ((tid & 31) == 0) s_red[tid >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int w = 0; w < 32; ++w) t += s_red[w];
+  return t;
+}
+
 __global__ void __launch_bounds__(1024)
-sk2_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, int nw,
+sk2_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, int groups, int warps,
                 const int32_t* __restrict__ block_table, int64_t bt_stride, int tiles_per_page, int tpp_shift,
-                int32_t* __restrict__ plan) {
+                int32_t* __restrict__ plan, Sk2Ctrl* __restrict__ ctrl, int calib_max) {
   __shared__ int s_warp[32];
+  __shared__ float s_red[32];
   __shared__ int s_carry;
+  __shared__ float s_w[kSk2MaxGroups];
+  __shared__ int s_gstart[kSk2MaxGroups + 1];
+  __shared__ int s_cum[kSk2PlanSmemBatch + 1];
+  __shared__ int s_cstart[kSk2MaxGroups * 12 + 1];
+  const int nw = groups * warps;
+  int32_t* cstart = plan + sk2_plan_cstart_off();
   int32_t* cum = plan + sk2_plan_cum_off(nw);
-  int4* desc = reinterpret_cast<int4*>(plan + sk2_plan_desc_off());
+  int4* desc = reinterpret_cast<int4*>(plan + sk2_plan_desc_off(nw));
   int32_t* ids = plan + sk2_plan_ids_off(nw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_carry = 0;
-  __syncthreads();
+  // ---- phase 0: weights (thread g <-> SM g)
+  {
+    const bool have = tid < groups;
+    const int tiles = have ? ctrl->stat_tiles[tid] : 0, cyc = have ? ctrl->stat_cycles[tid] : 0;
+    const float w_raw = have ? ctrl->weight[tid] : 0.f;
+    const float rate = (tiles >= kSk2CalibMinTiles && cyc > 0) ? static_cast<float>(tiles) / static_cast<float>(cyc) : 0.f;
+    const int missing = __syncthreads_or(have && rate == 0.f);  // some SM has no (or too little) history
+    const bool upd = !missing && ctrl->calib_updates < calib_max;
+    const float rsum = sk2_block_sum(rate, s_red, tid), wsum = sk2_block_sum(w_raw, s_red, tid);
+    const float w_old = wsum > 0.f ? w_raw / wsum : 1.f / groups;
+    float w = upd ? (1.f - kSk2CalibGain) * w_old + kSk2CalibGain * rate / rsum : w_old;
+    if (!have) w = 0.f;
+    const float norm = sk2_block_sum(w, s_red, tid);
+    w /= norm;
+    if (have) {
+      s_w[tid] = w;
+      if (upd) {
+        ctrl->weight[tid] = w;
+        ctrl->stat_tiles[tid] = 0;  // a history is used once
+        ctrl->stat_cycles[tid] = 0;
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && upd) ctrl->calib_updates += 1;
+  }
+  // ---- phase 1
   for (int base = 0; base < batch; base += 1024) {
     const int i = base + tid;
     const int s = i < batch ? max(0, seq_lens[i]) : 0;
@@ -79,44 +158,69 @@ sk2_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     int wbase = 0;
     for (int w = 0; w < warp; ++w) wbase += s_warp[w];
     const int carry = s_carry;
-    if (i < batch) cum[i] = carry + wbase + incl - t;
+    if (i < batch) {
+      cum[i] = carry + wbase + incl - t;
+      if (i < kSk2PlanSmemBatch) s_cum[i] = carry + wbase + incl - t;
+    }
     __syncthreads();
     if (tid == 1023) s_carry = carry + wbase + incl;
     __syncthreads();
   }
   const int tiles = s_carry;
-  if (tid == 0) cum[batch] = tiles;
-  const int64_t total = static_cast<int64_t>(tiles) * hs_count;
-  const int64_t ts64 = (total + nw - 1) / nw;
-  const int ts = static_cast<int>(ts64 < 1 ? 1 : ts64);
+  if (static_cast<int64_t>(tiles) * hs_count > 0x7fffffffll) __trap();  // stream positions are 32-bit
+  const int total = tiles * hs_count;
+  const bool cum_in_smem = batch <= kSk2PlanSmemBatch;
+  const int32_t* cum_r = cum_in_smem ? s_cum : cum;
   if (tid == 0) {
-    plan[0] = static_cast<int32_t>(total & 0xffffffffll);
-    plan[1] = static_cast<int32_t>(total >> 32);
-    plan[2] = ts;
+    cum[batch] = tiles;
+    if (cum_in_smem) s_cum[batch] = tiles;
+    plan[0] = total;
+    plan[1] = groups;
+    plan[2] = warps;
     plan[3] = nw;
     plan[4] = batch;
     plan[5] = hs_count;
     plan[6] = tpp_shift;
     plan[7] = kSk2PlanMagic;
+    // group ranges: cumulative weights; every group gets at least one position while there are any, so the
+    // non-empty groups are a prefix of the grid
+    double acc = 0.0;
+    s_gstart[0] = 0;
+    for (int g = 0; g < groups; ++g) {
+      acc += s_w[g];
+      int e = static_cast<int>(acc * total + 0.5);
+      e = min(max(e, s_gstart[g] + 1), total);
+      s_gstart[g + 1] = g + 1 == groups ? total : e;
+    }
   }
-  __syncthreads();  // cum[] is read back below (same CTA: visible after the barrier)
-  for (int gw = tid; gw < nw; gw += 1024) {
-    const int64_t g0 = static_cast<int64_t>(gw) * ts;
+  __syncthreads();  // cum[] and s_gstart[] are read below
+  // ---- phase 2
+  for (int c = tid; c <= nw; c += 1024) {
+    const int g = c / warps, w = c % warps;
+    // a group's range is cut into `warps` chunks, the first (len % warps) one position longer: the non-empty
+    // chunks are a prefix of the group as well
+    const int gs = s_gstart[min(g, groups)], ge = s_gstart[min(g + 1, groups)];
+    const int q = (ge - gs) / warps, r = (ge - gs) % warps;
+    const int g0 = c == nw ? total : gs + w * q + min(w, r);
+    cstart[c] = g0;
+    s_cstart[c] = g0;
+    if (c == nw) break;
     int4 d = make_int4(batch, 0, 0, 1);
     if (g0 < total) {
-      const int key = static_cast<int>(g0 / hs_count);  // cum[b] <= key < cum[b+1]
+      const int key = g0 / hs_count;  // cum[b] <= key < cum[b+1]
       int lo = 0, hi = batch;
       while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
-        if (cum[mid] <= key) lo = mid; else hi = mid;
+        if (cum_r[mid] <= key) lo = mid; else hi = mid;
       }
-      const int n = cum[lo + 1] - cum[lo];
-      const int r = static_cast<int>(g0 - static_cast<int64_t>(cum[lo]) * hs_count);
-      d = make_int4(lo, r / n, r % n, n);
+      const int n = cum_r[lo + 1] - cum_r[lo];
+      const int rem = g0 - cum_r[lo] * hs_count;
+      d = make_int4(lo, rem / n, rem % n, n);
     }
-    desc[gw] = d;
+    desc[c] = d;
   }
   __syncthreads();
+  // ---- phase 3
   for (int idx = tid; idx < nw * 32; idx += 1024) {
     const int4 d = desc[idx >> 5];
     const int page0 = (d.z >> tpp_shift) & ~31;
@@ -124,186 +228,148 @@ sk2_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     const int pg = page0 + (idx & 31);
     ids[idx] = (d.x < batch && pg < pages) ? block_table[static_cast<int64_t>(d.x) * bt_stride + pg] : 0;
   }
+  // ---- phase 4: the chunks that cut each item
+  int2* item_w = reinterpret_cast<int2*>(plan + sk2_plan_itemw_off(nw, batch));
+  for (int it = tid; it < batch * hs_count; it += 1024) {
+    const int b = it / hs_count, hs = it % hs_count;
+    const int c0 = cum_r[b], n = cum_r[b + 1] - c0;
+    int2 w = make_int2(0, -1);
+    if (n > 0) {
+      const int t0 = c0 * hs_count + hs * n;
+      w = make_int2(sk2_chunk_of(s_cstart, nw, t0), sk2_chunk_of(s_cstart, nw, t0 + n - 1));
+    }
+    item_w[it] = w;
+  }
 }
 
-cudaError_t launch_sk2_plan(const int32_t* seq_lens, int batch, int hs_count, int nw, const int32_t* block_table,
-                            int64_t bt_stride, int tiles_per_page, int tpp_shift, int32_t* plan, cudaStream_t stream) {
-  sk2_plan_kernel<<<1, 1024, 0, stream>>>(seq_lens, batch, hs_count, nw, block_table, bt_stride, tiles_per_page,
-                                          tpp_shift, plan);
+cudaError_t launch_sk2_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, const int32_t* block_table,
+                            int64_t bt_stride, int tiles_per_page, int tpp_shift, int32_t* plan, Sk2Ctrl* ctrl,
+                            int calib_max, cudaStream_t stream) {
+  sk2_plan_kernel<<<1, 1024, 0, stream>>>(seq_lens, batch, hs_count, groups, decode_sk2_warps(), block_table, bt_stride,
+                                          tiles_per_page, tpp_shift, plan, ctrl, calib_max);
   return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------------
-// Merge of partials by their LSE (the merge_attn_states formula), by the whole CTA, after its
-// streaming loop. A partial is 8 heads x 128 floats + 8 LSEs; thread (head, 4 columns) folds the K
-// pieces of one job with every load in flight at once (one L2 round trip per job).
-//
-// Level 1 — pieces inside this CTA's W consecutive chunks. Job 0: the item the CTA's first chunk
-// started inside (pieces: head slots 2c of chunks cfirst ..). Job 1 + w: the item warp w's chunk
-// ended inside (pieces: tail slot 2c + 1 of that chunk, then head slots of the chunks after it).
-// An item that lies entirely inside the CTA's chunks is finished here; one that crosses a CTA
-// boundary leaves a CTA partial in gpart slot 2 * cta + (job 0 ? 0 : 1).
-// Level 2 — an item that crosses CTA boundaries is counted once per CTA on cnt2[first CTA]; the CTA
-// that arrives last folds the CTA partials (slot 2 * C0 + 1, then 2 * C for the CTAs after it).
+// The separate log-sum-exp reduce kernel: merge of the partials left by chunk boundaries (the
+// merge_attn_states formula). One CTA of 8 warps per (sequence, kv head, head sub-group) item; a partial
+// is one contiguous 4 KiB block (8 heads x 128 floats) plus 8 LSEs, so warp w folds the pieces
+// k = w, w + 8, ... of all 8 heads with 8 independent 512 B loads in flight per piece, and the 8 warps are
+// folded through shared memory. The item's piece list comes from the plan (first / last chunk, chunk
+// starts), read BEFORE griddepcontrol.wait. Items finished by a single warp were already written by it;
+// rows of empty sequences are zeroed here.
 // ------------------------------------------------------------------------------------------------
-struct Sk2Job {
-  int count;       // pieces (0 = no job)
-  int first_slot;  // partial slot of piece 0; piece k > 0 lives in slot 2 * (c_start + k)
-  int c_start;
-  int dst;         // -1 final row, else gpart slot
-  int b, hs;
-};
+constexpr int kSk2ReduceWarps = 8;
 
-template <int KMAX>
-__device__ __forceinline__ void sk2_fold(const DecodeParams& p, const float* src_o, const float* src_lse, int count,
-                                         int first_slot, int c_start, int dst, int b, int hs, int hh, int col) {
-  float m = -CUDART_INF_F, den = 0.f;
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int k0 = 0; k0 < count; k0 += KMAX) {
-    float l[KMAX];
-    float4 o[KMAX];
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-      const bool on = k0 + k < count;
-      const int64_t row = (static_cast<int64_t>(k0 + k == 0 ? first_slot : 2 * (c_start + k0 + k))) * kHeadsPerItem + hh;
-      l[k] = on ? __ldcg(src_lse + row) : -CUDART_INF_F;
-      o[k] = on ? __ldcg(reinterpret_cast<const float4*>(src_o + row * kHeadDim + col * 4))
-                : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    float mn = m;
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k) mn = fmaxf(mn, l[k]);
-    if (mn == -CUDART_INF_F) continue;  // nothing but empty partials so far
-    const float a = fast_exp2((m - mn) * kLog2e);  // 0 when m = -inf
-    acc.x *= a, acc.y *= a, acc.z *= a, acc.w *= a;
-    den *= a;
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-      const float w = fast_exp2((l[k] - mn) * kLog2e);  // 0 for -inf
-      acc.x = fmaf(o[k].x, w, acc.x);
-      acc.y = fmaf(o[k].y, w, acc.y);
-      acc.z = fmaf(o[k].z, w, acc.z);
-      acc.w = fmaf(o[k].w, w, acc.w);
-      den += w;
-    }
-    m = mn;
+__global__ void __launch_bounds__(kSk2ReduceWarps * 32)
+sk2_reduce_kernel(__nv_bfloat16* __restrict__ out, int64_t out_stride_tok, float* __restrict__ lse, int batch,
+                  int num_q_heads, int group, int subgroups, int num_kv_heads, int nw,
+                  const float* __restrict__ part_o, const float* __restrict__ part_lse,
+                  const int32_t* __restrict__ plan) {
+  __shared__ float s_acc[kSk2ReduceWarps][kHeadsPerItem][kHeadDim];
+  __shared__ float s_max[kSk2ReduceWarps][kHeadsPerItem];
+  __shared__ float s_den[kSk2ReduceWarps][kHeadsPerItem];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int hs_count = num_kv_heads * subgroups;
+  const int item = blockIdx.x;
+  const int b = item / hs_count, hs = item % hs_count;
+  const int kvh = hs / subgroups, sub = hs % subgroups;
+  const int heads_here = min(kHeadsPerItem, group - sub * kHeadsPerItem);
+  const int h_first = kvh * group + sub * kHeadsPerItem;  // first query head of the item
+  // the plan is not written by the kernels this launch depends on: read it while they still run
+  const int32_t* cstart = plan + sk2_plan_cstart_off();
+  const int2 w = __ldg(reinterpret_cast<const int2*>(plan + sk2_plan_itemw_off(nw, batch)) + item);
+  const int pieces = w.y - w.x + 1;  // chunks from the first to the last that hold tiles of the item
+  // which of this warp's pieces really exist (a group's trailing chunks may be empty): lane i <-> piece warp + 8 i
+  bool mine = false;
+  {
+    const int k = warp + kSk2ReduceWarps * lane;
+    if (k < pieces) mine = __ldg(cstart + w.x + k + 1) > __ldg(cstart + w.x + k);
   }
-  const float inv = den > 0.f ? 1.f / den : 0.f;
-  const float lse = den > 0.f ? m + logf(den) : -CUDART_INF_F;
-  const float4 v = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
-  if (dst >= 0) {
-    const int64_t row = static_cast<int64_t>(dst) * kHeadsPerItem + hh;
-    *reinterpret_cast<float4*>(p.gpart_o + row * kHeadDim + col * 4) = v;
-    if (col == 0) p.gpart_lse[row] = lse;
-  } else {
-    const int kvh = hs / p.subgroups, sub = hs % p.subgroups;
-    const int head_in_group = sub * kHeadsPerItem + hh;
-    if (head_in_group < p.group) {
-      const int h = kvh * p.group + head_in_group;
-      uint2 pk;
-      pk.x = pack_bf16x2(v.x, v.y);
-      pk.y = pack_bf16x2(v.z, v.w);
-      *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(b) * p.out_stride_tok + static_cast<int64_t>(h) * kHeadDim +
-                                col * 4) = pk;
-      if (p.lse != nullptr && col == 0) p.lse[static_cast<int64_t>(b) * p.num_q_heads + h] = lse;
+  const uint32_t live = __ballot_sync(0xffffffffu, mine);
+  griddep_wait();
+  griddep_launch_dependents();
+  if (pieces <= 0) {  // empty sequence: zero rows, LSE = -inf
+    if (warp < heads_here) {
+      const int h = h_first + warp;
+      *reinterpret_cast<uint2*>(out + static_cast<int64_t>(b) * out_stride_tok + static_cast<int64_t>(h) * kHeadDim +
+                                lane * 4) = make_uint2(0u, 0u);
+      if (lse != nullptr && lane == 0) lse[static_cast<int64_t>(b) * num_q_heads + h] = -CUDART_INF_F;
     }
+    return;
   }
-}
+  if (pieces == 1) return;  // finished by one warp
 
-template <int W>
-__device__ __noinline__ void sk2_cta_merge(const DecodeParams& p, const int32_t* plan, int ts, int64_t total,
-                                           const int4* s_tail) {
-  __shared__ Sk2Job s_job[W + 1];
-  __shared__ int s_valid[W + 1];
-  __shared__ int s_nvalid;
-  __shared__ int s_l2[2][4];  // {first CTA, CTAs, b, hs} of the (at most two) items crossing this CTA's boundaries
-  __shared__ int s_l2_last[2];
-  const int tid = threadIdx.x;
-  const int hs_count = p.num_kv_heads * p.subgroups;
-  const int nw = gridDim.x * W;
-  const int32_t* cum = plan + sk2_plan_cum_off(nw);
-  const int cfirst = blockIdx.x * W, clast = cfirst + W - 1;
-  if (tid < 2) {
-    s_l2[tid][1] = 0;
-    s_l2_last[tid] = 0;
+  float4 acc[kHeadsPerItem];
+  float den[kHeadsPerItem], m[kHeadsPerItem];
+#pragma unroll
+  for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+    acc[hh] = make_float4(0.f, 0.f, 0.f, 0.f);
+    den[hh] = 0.f;
+    m[hh] = -CUDART_INF_F;
   }
-  __syncthreads();  // also: every partial this CTA stored is visible to the whole CTA from here on
-  if (tid <= W) {
-    Sk2Job j;
-    j.count = 0;
-    j.first_slot = j.c_start = j.dst = j.b = j.hs = 0;
-    int b = -1, hs = 0, n = 1;
-    if (tid == 0) {
-      const int4 d = __ldg(reinterpret_cast<const int4*>(plan + sk2_plan_desc_off()) + cfirst);
-      if (static_cast<int64_t>(cfirst) * ts < total && d.z > 0) b = d.x, hs = d.y, n = d.w;
-    } else {
-      const int4 t = s_tail[tid - 1];
-      if (t.x >= 0) b = t.x, hs = t.y, n = t.z;
+  for (int i = 0; warp + kSk2ReduceWarps * i < pieces; ++i) {
+    const int k = warp + kSk2ReduceWarps * i;
+    const bool on = i < 32 ? ((live >> i) & 1u) != 0
+                           : __ldg(cstart + w.x + k + 1) > __ldg(cstart + w.x + k);  // (more than 256 pieces: rare)
+    if (!on) continue;
+    const int64_t r0 = (2ll * (w.x + k) + (k == 0 ? 1 : 0)) * kHeadsPerItem;
+    const float ls = lane < kHeadsPerItem ? part_lse[r0 + lane] : 0.f;
+    float4 o[kHeadsPerItem];
+#pragma unroll
+    for (int hh = 0; hh < kHeadsPerItem; ++hh)
+      o[hh] = *reinterpret_cast<const float4*>(part_o + (r0 + hh) * kHeadDim + lane * 4);
+#pragma unroll
+    for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+      const float l = __shfl_sync(0xffffffffu, ls, hh);
+      if (l == -CUDART_INF_F) continue;  // empty partial
+      const float mn = fmaxf(m[hh], l);
+      const float a = fast_exp2((m[hh] - mn) * kLog2e);  // 0 when m = -inf
+      const float wgt = fast_exp2((l - mn) * kLog2e);
+      acc[hh].x = fmaf(o[hh].x, wgt, acc[hh].x * a);
+      acc[hh].y = fmaf(o[hh].y, wgt, acc[hh].y * a);
+      acc[hh].z = fmaf(o[hh].z, wgt, acc[hh].z * a);
+      acc[hh].w = fmaf(o[hh].w, wgt, acc[hh].w * a);
+      den[hh] = fmaf(den[hh], a, wgt);
+      m[hh] = mn;
     }
-    if (b >= 0) {
-      const int64_t t0 = static_cast<int64_t>(__ldg(cum + b)) * hs_count + static_cast<int64_t>(hs) * n;
-      const int w0 = static_cast<int>(t0 / ts), w1 = static_cast<int>((t0 + n - 1) / ts);
-      j.c_start = tid == 0 ? cfirst : cfirst + tid - 1;
-      j.count = min(w1, clast) - j.c_start + 1;
-      j.first_slot = 2 * j.c_start + (tid == 0 ? 0 : 1);
-      j.b = b;
-      j.hs = hs;
-      const bool final_here = tid > 0 && w1 <= clast;
-      j.dst = final_here ? -1 : 2 * static_cast<int>(blockIdx.x) + (tid == 0 ? 0 : 1);
-      if (!final_here) {
-        const int which = tid == 0 ? 0 : 1;
-        s_l2[which][0] = w0 / W;
-        s_l2[which][1] = w1 / W - w0 / W + 1;
-        s_l2[which][2] = b;
-        s_l2[which][3] = hs;
-      }
-    }
-    s_job[tid] = j;
   }
-  __syncthreads();
-  if (tid == 0) {
-    int nv = 0;
-    for (int j = 0; j <= W; ++j)
-      if (s_job[j].count > 0) s_valid[nv++] = j;
-    s_nvalid = nv;
-  }
-  __syncthreads();
-  const int nv = s_nvalid;
-  if (nv == 0) return;
-  // ---- level 1
-  for (int u = tid; u < nv * 256; u += W * 32) {
-    const Sk2Job j = s_job[s_valid[u >> 8]];
-    sk2_fold<W>(p, p.part_o, p.part_lse, j.count, j.first_slot, j.c_start, j.dst, j.b, j.hs, (u >> 5) & 7, u & 31);
-  }
-  if (s_l2[0][1] == 0 && s_l2[1][1] == 0) return;  // no item of this CTA crosses a CTA boundary
-  // ---- level 2: count this CTA on the crossing items; the last arriver folds the CTA partials
-  __threadfence();
-  __syncthreads();
-  if (tid < 2 && s_l2[tid][1] > 0) {
-    const int old = atomicAdd(p.cnt2 + s_l2[tid][0], 1);
-    if (old == s_l2[tid][1] - 1) {
-      p.cnt2[s_l2[tid][0]] = 0;  // left at zero for the next launch
-      s_l2_last[tid] = 1;
+#pragma unroll
+  for (int hh = 0; hh < kHeadsPerItem; ++hh) {
+    *reinterpret_cast<float4*>(&s_acc[warp][hh][lane * 4]) = acc[hh];
+    if (lane == 0) {
+      s_den[warp][hh] = den[hh];
+      s_max[warp][hh] = m[hh];
     }
   }
   __syncthreads();
-#pragma unroll 1
-  for (int t = 0; t < 2; ++t) {
-    if (!s_l2_last[t]) continue;
-    __threadfence();
-    const int c0 = s_l2[t][0];
-    if (tid < 256)
-      sk2_fold<8>(p, p.gpart_o, p.gpart_lse, s_l2[t][1], 2 * c0 + 1, c0, -1, s_l2[t][2], s_l2[t][3], (tid >> 5) & 7,
-                  tid & 31);
-  }
-}
-
-// Rows of empty sequences (seq_len <= 0, e.g. CUDA-graph padding): zero output, LSE = -inf.
-__device__ __noinline__ void sk2_zero_rows(const DecodeParams& p, int b, int lane) {
-  for (int h = 0; h < p.num_q_heads; ++h) {
-    *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(b) * p.out_stride_tok + static_cast<int64_t>(h) * kHeadDim +
-                              lane * 4) = make_uint2(0u, 0u);
-    if (p.lse != nullptr && lane == 0) p.lse[static_cast<int64_t>(b) * p.num_q_heads + h] = -CUDART_INF_F;
+  // ---- fold the 8 warps: warp = head, lane = 4 output columns
+  if (warp < heads_here) {
+    float mfin = s_max[0][warp];
+#pragma unroll
+    for (int ww = 1; ww < kSk2ReduceWarps; ++ww) mfin = fmaxf(mfin, s_max[ww][warp]);
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    float dsum = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < kSk2ReduceWarps; ++ww) {
+      const float mw = s_max[ww][warp];
+      const float sc_w = (mw == -CUDART_INF_F) ? 0.f : fast_exp2((mw - mfin) * kLog2e);
+      const float4 v = *reinterpret_cast<const float4*>(&s_acc[ww][warp][lane * 4]);
+      a.x = fmaf(v.x, sc_w, a.x);
+      a.y = fmaf(v.y, sc_w, a.y);
+      a.z = fmaf(v.z, sc_w, a.z);
+      a.w = fmaf(v.w, sc_w, a.w);
+      dsum = fmaf(s_den[ww][warp], sc_w, dsum);
+    }
+    const float inv = dsum > 0.f ? 1.f / dsum : 0.f;
+    const int h = h_first + warp;
+    uint2 pk;
+    pk.x = pack_bf16x2(a.x * inv, a.y * inv);
+    pk.y = pack_bf16x2(a.z * inv, a.w * inv);
+    *reinterpret_cast<uint2*>(out + static_cast<int64_t>(b) * out_stride_tok + static_cast<int64_t>(h) * kHeadDim +
+                              lane * 4) = pk;
+    if (lse != nullptr && lane == 0)
+      lse[static_cast<int64_t>(b) * num_q_heads + h] = dsum > 0.f ? mfin + logf(dsum) : -CUDART_INF_F;
   }
 }
 
@@ -311,7 +377,8 @@ template <int W, int D, int SB>
 struct Sk2Smem {
   alignas(1024) uint8_t ring[W][D][SB];  // SB = bytes of one stage (K tile + V tile)
   alignas(8) uint64_t bar[W][D];         // "stage landed" mbarriers, one per ring slot
-  alignas(16) int4 tail[W];              // per warp: the item its chunk ended inside {b, hs, n} (b < 0: none)
+  long long t0;                          // clock64 at CTA start (the SM's rate is recorded at the end)
+  int group;                             // chunk group this CTA claimed
 };
 
 __device__ __forceinline__ void sk2_advance(const int32_t* cum, int batch, int hs_count, Sk2Pos& it) {
@@ -352,18 +419,49 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int nw = gridDim.x * W;
-  const int gw = blockIdx.x * W + warp;
-  if (p.trace != nullptr && lane == 0) p.trace[gw * 4 + 0] = sk2_globaltimer();  // debug: entry stamp
+  // ---- which chunk group this CTA runs: the one of the SM it sits on (the plan sized group g for SM g), claimed
+  // with one atomic so that every group is run exactly once whatever the block scheduler did (two CTAs on one
+  // SM one after the other, an SM id beyond the grid): a CTA whose own group is taken scans for a free one.
+  // Claim words of two consecutive launches (which may overlap under programmatic dependent launch) are kept
+  // apart by the launch parity; the last CTA to finish re-arms the words of its launch.
+  Sk2Ctrl* const ctrl = p.sk2_ctrl;
+  const int parity = (p.flags & kSk2FlagParity) ? 1 : 0;
+  const int G = static_cast<int>(gridDim.x);
+  uint32_t smid;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  const int g_spec = (p.flags & kSk2FlagDebugInterleave) ? static_cast<int>(blockIdx.x)
+                                                         : static_cast<int>(smid % static_cast<uint32_t>(G));
+  if (threadIdx.x == 0) {
+    int g = g_spec;
+    if (!(p.flags & kSk2FlagDebugInterleave) && atomicCAS(&ctrl->claimed[parity][g], 0, 1) != 0) {
+      for (int k = 1; k <= G; ++k) {
+        const int gg = (g + k) % G;
+        if (atomicCAS(&ctrl->claimed[parity][gg], 0, 1) == 0) {
+          g = gg;
+          break;
+        }
+      }
+    }
+    sm.group = g;
+  }
   bool waited = false;
-  if (p.flags & kSk2FlagWaitFirst) {  // the plan was written by the kernel right before this one
+  // griddepcontrol.wait; the SM's rate (recorded for the plan kernel) is measured from here, so the time a CTA
+  // that started early spends waiting for the previous kernel does not count against its SM
+  auto wait_for_prior = [&]() {
     griddep_wait();
     waited = true;
-  }
-  // ---- the warp's work: one round of independent loads
+    if (threadIdx.x == 0) sm.t0 = clock64();
+  };
+  if (p.flags & kSk2FlagWaitFirst) wait_for_prior();  // the plan was written by the kernel right before this one
+  // ---- the warp's work: one round of independent loads, issued for the group the CTA will almost always get
+  // (its own SM's) while thread 0's claim is in flight
   const int32_t* plan = p.sk2_plan;
   const int4 hdr = __ldg(reinterpret_cast<const int4*>(plan));
   const int4 hdr2 = __ldg(reinterpret_cast<const int4*>(plan) + 1);
-  const int4 d4 = __ldg(reinterpret_cast<const int4*>(plan + sk2_plan_desc_off()) + gw);
+  // chunk of this warp; debug flag: chunks interleaved over the CTAs (timeline experiments only: the merge is skipped)
+  int gw = (p.flags & kSk2FlagDebugInterleave) ? warp * G + static_cast<int>(blockIdx.x) : g_spec * W + warp;
+  int4 d4 = __ldg(reinterpret_cast<const int4*>(plan + sk2_plan_desc_off(nw)) + gw);
+  int g_begin = __ldg(plan + sk2_plan_cstart_off() + gw), g_end = __ldg(plan + sk2_plan_cstart_off() + gw + 1);
   int ids = __ldg(plan + sk2_plan_ids_off(nw) + gw * 32 + lane);
   const int32_t* cum = plan + sk2_plan_cum_off(nw);
   if (lane == 0) {
@@ -375,17 +473,27 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       tma_prefetch_desc(&tm_v);
     }
   }
-  __syncwarp();
+  __syncthreads();
+  const int group = sm.group;
+  if (group != g_spec) {  // rare: this CTA runs another SM's group
+    gw = group * W + warp;
+    d4 = __ldg(reinterpret_cast<const int4*>(plan + sk2_plan_desc_off(nw)) + gw);
+    g_begin = __ldg(plan + sk2_plan_cstart_off() + gw);
+    g_end = __ldg(plan + sk2_plan_cstart_off() + gw + 1);
+    ids = __ldg(plan + sk2_plan_ids_off(nw) + gw * 32 + lane);
+  }
+  if (p.trace != nullptr && lane == 0) {  // debug: entry stamp, SM id
+    p.trace[gw * 8 + 0] = sk2_globaltimer();
+    p.trace[gw * 8 + 4] = smid;
+  }
   // the next kernel of the chain may start its own prologue (it cannot get an SM before this CTA exits)
   griddep_launch_dependents();
 
   const int hs_count = p.num_kv_heads * p.subgroups;
-  const int64_t total = (static_cast<int64_t>(hdr.y) << 32) | static_cast<uint32_t>(hdr.x);
-  const int ts = hdr.z;
-  if (hdr.w != nw || hdr2.x != p.batch || hdr2.y != hs_count || hdr2.z != p.tpp_shift || hdr2.w != kSk2PlanMagic)
+  if (hdr.y != static_cast<int>(gridDim.x) || hdr.z != W || hdr.w != nw || hdr2.x != p.batch || hdr2.y != hs_count ||
+      hdr2.z != p.tpp_shift || hdr2.w != kSk2PlanMagic)
     __trap();  // the plan in the workspace was made for another launch shape: fail loudly
-  const int64_t g0 = static_cast<int64_t>(gw) * ts;
-  const int cnt = static_cast<int>(max(static_cast<int64_t>(0), min(static_cast<int64_t>(ts), total - g0)));
+  const int cnt = g_end - g_begin;
   const bool early = (p.flags & kSk2FlagEarlyKvRead) != 0;
 
   const SkLane sl = sk_make_lane(lane);
@@ -414,7 +522,6 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = qf_n[kk][0] = qf_n[kk][1] = 0u;
   float scale = p.scale_log2, scale_n = p.scale_log2;
   int slen = 0, slen_n = 0;
-  int tail_b = -1, tail_hs = 0, tail_n = 0;  // the item this chunk ends inside, if it leaves a partial there
   WarpState st;
   state_reset(st);
 
@@ -454,8 +561,7 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       if (!waited && (!early || pf.tile + 1 == pf.n)) {
         // without the early-read contract every KV byte may still be in flight; with it only the tile that
         // holds the new token's slot
-        griddep_wait();
-        waited = true;
+        wait_for_prior();
         if (q_deferred) {
           load_q_next();
           q_deferred = false;
@@ -486,8 +592,7 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       pf_fresh = (pf.tile == 0);
     }
     if (q_deferred) {  // the first stages are in flight: now wait for the previous kernel and fetch q
-      griddep_wait();
-      waited = true;
+      wait_for_prior();
       load_q_next();
       q_deferred = false;
     }
@@ -506,7 +611,7 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
 
     // ================= math on the oldest stage =================
     mbar_wait(&sm.bar[warp][cslot], cphase);
-    if (p.trace != nullptr && cs_left == cnt && lane == 0) p.trace[gw * 4 + 1] = sk2_globaltimer();  // first stage landed
+    if (p.trace != nullptr && cs_left == cnt && lane == 0) p.trace[gw * 8 + 1] = sk2_globaltimer();  // first stage landed
     const bool item_done = (cs.tile + 1 == cs.n);
     {
       const int valid = item_done ? slen - cs.tile * kTileTokens : kTileTokens;
@@ -526,11 +631,6 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       sk_store<FP8>(p, st, cs.b, cs.hs, whole, piece, reinterpret_cast<float*>(sm.ring[warp][cslot]), lane);
       fence_proxy_async_smem();  // the slot was written through the generic proxy; TMA refills it next
       __syncwarp();
-      if (!whole && seg_start == 0) {  // cut at the chunk end (a segment with seg_start > 0 is the head piece)
-        tail_b = cs.b;
-        tail_hs = cs.hs;
-        tail_n = cs.n;
-      }
       state_reset(st);
       seg_start = 0;
       have_item = false;
@@ -543,20 +643,30 @@ paged_decode_sk2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   }
 
   // every warp waits before it exits, so a completed grid implies its predecessors completed
-  if (!waited) griddep_wait();
-  for (int b = gw; b < p.batch; b += nw)
-    if (__ldg(p.seq_lens + b) <= 0) sk2_zero_rows(p, b, lane);
-  // ---- merge of the partials (sk2_cta_merge): after the streaming loop, so none of the loop's state is live
-  // across it; nothing is lost by merging late: every other piece of an item is finished at the end of its
-  // own warp's chunk as well.
-  if (lane == 0) sm.tail[warp] = make_int4(tail_b, tail_hs, tail_n, 0);
+  if (!waited) wait_for_prior();
   if (p.trace != nullptr && lane == 0) {  // debug: end of this warp's streaming
     const uint64_t t_end = sk2_globaltimer();
-    if (cnt == 0) p.trace[gw * 4 + 1] = t_end;
-    p.trace[gw * 4 + 2] = t_end;
+    if (cnt == 0) p.trace[gw * 8 + 1] = t_end;
+    p.trace[gw * 8 + 2] = t_end;
+    p.trace[gw * 8 + 3] = t_end;
   }
-  sk2_cta_merge<W>(p, plan, ts, total, sm.tail);
-  if (p.trace != nullptr && lane == 0) p.trace[gw * 4 + 3] = sk2_globaltimer();  // debug: merges done
+  if (p.flags & kSk2FlagDebugInterleave) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    // what this SM achieved (the plan kernel turns it into the SM's share of the next steps' streams) ...
+    if (smid < static_cast<uint32_t>(kSk2MaxGroups)) {
+      const int32_t* cstart = plan + sk2_plan_cstart_off();
+      ctrl->stat_tiles[smid] = __ldg(cstart + group * W + W) - __ldg(cstart + group * W);
+      ctrl->stat_cycles[smid] = static_cast<int>(min(static_cast<long long>(0x7fffffff), clock64() - sm.t0));
+    }
+    // ... and the last CTA of the launch re-arms the claim words of its parity
+    __threadfence();
+    if (atomicAdd(&ctrl->finished[parity], 1) == G - 1) {
+      for (int g = 0; g < G; ++g) ctrl->claimed[parity][g] = 0;
+      ctrl->finished[parity] = 0;
+      __threadfence();
+    }
+  }
 }
 
 // Warps per CTA: 12 = 3 per SM sub-partition, the most that still leaves each thread the ~168 registers the
@@ -602,6 +712,22 @@ cudaError_t launch_decode_sk2(const CUtensorMap& tm_k, const CUtensorMap& tm_v, 
                       kSk2Warps * 32, tm_k, tm_v, p, grid, pdl, stream);
   return sk2_launch(paged_decode_sk2_kernel<kSk2Warps, kSk2Depth, false>, &dev[0], decode_sk2_smem_bytes(false),
                     kSk2Warps * 32, tm_k, tm_v, p, grid, pdl, stream);
+}
+
+cudaError_t launch_sk2_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(p.batch * p.num_kv_heads * p.subgroups));
+  cfg.blockDim = dim3(kSk2ReduceWarps * 32);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, sk2_reduce_kernel, p.out, p.out_stride_tok, p.lse, p.batch, p.num_q_heads, p.group,
+                            p.subgroups, p.num_kv_heads, grid_decode * kSk2Warps, static_cast<const float*>(p.part_o),
+                            static_cast<const float*>(p.part_lse), p.sk2_plan);
 }
 
 }  // namespace b200

@@ -22,10 +22,15 @@ import torch
 class HostStepRunner:
     def __init__(self, impl, metadata, kv_caches: list[torch.Tensor], batch: int, num_q_heads: int,
                  num_kv_heads: int, head_size: int, slot_mapping: torch.Tensor,
-                 k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None, after_layer=None):
+                 k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None, after_layer=None,
+                 plan_per_step: bool = False):
         dev = kv_caches[0].device
         self.impl, self.md, self.kv_caches, self.slot_mapping = impl, metadata, kv_caches, slot_mapping
         self.after_layer = after_layer  # e.g. the o_proj all-reduce of a tensor-parallel layer
+        # one stream-K plan launch per step, as B200AttentionMetadataBuilder.build does for a scheduler step
+        self.plan_per_step = plan_per_step and metadata.num_decodes > 0
+        metadata.decode_planned = self.plan_per_step
+        self.block_size = kv_caches[0].shape[-3] if kv_caches[0].ndim == 5 else None
         one = torch.ones(1, dtype=torch.float32, device=dev)
         self.layer = types.SimpleNamespace(_k_scale=one if k_scale is None else k_scale,
                                            _v_scale=one if v_scale is None else v_scale)
@@ -51,6 +56,10 @@ class HostStepRunner:
         out_free = [torch.cuda.Event() for _ in range(2)]
         self.s_in.wait_stream(cur)
         self.s_out.wait_stream(cur)
+        if self.plan_per_step:
+            from . import ops
+            md = self.md
+            ops.decode_plan(md.seq_lens, md.block_table, md.num_decodes, hq, hkv, self.block_size, md.workspace)
         with torch.cuda.stream(self.s_in):
             self.dev_in[0].copy_(host_qkv[0], non_blocking=True)
             in_ready[0].record(self.s_in)

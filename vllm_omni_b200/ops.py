@@ -12,7 +12,7 @@ from . import _lib
 from ._lib import (DECODE_EARLY_KV_READ, DECODE_PLANNED, KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC,  # noqa: F401
                    VARIANT_SK2, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check)
 
-WORKSPACE_MIN_BYTES = 4096  # control area (arrival / claim counters), see b200attn_workspace_init
+WORKSPACE_MIN_BYTES = 16384  # control area (arrival / claim counters), see b200attn_workspace_init
 
 _FP8_NAMES = ("fp8", "fp8_e4m3")
 
@@ -182,7 +182,7 @@ def decode_workspace_bytes(max_batch: int, num_q_heads: int, head_size: int, max
 
 class DecodeWorkspace:
     """Caller-owned split-K scratch (control area, partial outputs + LSE, the step's stream-K plan), grown
-    on demand outside graphs. The control area (first 4 KiB) is zeroed once per allocation through
+    on demand outside graphs. The control area (first 16 KiB) is zeroed once per allocation through
     `b200attn_workspace_init`; the library keeps it zero between launches."""
 
     def __init__(self, device: torch.device | str = "cuda", nbytes: int = 0):
@@ -306,12 +306,13 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
 def paged_decode_partial(q, k_cache, v_cache, block_table, seq_lens, max_seq_len, softmax_scale,
                          out, num_splits: int, workspace: DecodeWorkspace,
                          lse=None, kv_cache_dtype="auto", k_scale=None, v_scale=None,
-                         variant: int = VARIANT_AUTO) -> None:
+                         variant: int = VARIANT_AUTO, planned: bool = False, early_kv_read: bool = False) -> None:
     """First launch only (profiling sweeps): split-K partial kernel."""
     lib = _lib.load()
     workspace.ensure(decode_workspace_bytes(q.shape[0], q.shape[1], q.shape[2], num_splits))
+    flags = (DECODE_PLANNED if planned else 0) | (DECODE_EARLY_KV_READ if early_kv_read else 0)
     args = _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_len,
-                        softmax_scale, kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace)
+                        softmax_scale, kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace, flags)
     check("b200attn_paged_decode_partial", lib.b200attn_paged_decode_partial(*args))
 
 
