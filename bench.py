@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: global batch = workload batch x N (per-GPU KV bytes fixed up to the "
                          "KV-head count); strong: global batch fixed (the other one is reported under `extras`)")
-    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 TMA, 2 cp.async, 3 stream, 4 stream-K v1, 5 stream-K v2")
+    ap.add_argument("--variant", type=int, default=0, help="0 auto, 1 TMA, 2 cp.async, 3 stream, 4 stream-K v1, 5 stream-K v2, 6 cooperative stream-K (default)")
     ap.add_argument("--splits", type=int, default=0, help="0 = heuristic")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -84,7 +84,7 @@ def peaks():
 def kernel_sources_sha() -> str:
     """sha256 over the decode kernel sources: a committed ncu capture is only quoted while it matches."""
     h = hashlib.sha256()
-    for name in ("paged_decode_sk2.cu", "sk_math.cuh", "decode_common.cuh", "ptx.cuh"):
+    for name in ("paged_decode_sk3.cu", "sk_math.cuh", "decode_common.cuh", "ptx.cuh"):
         h.update((ROOT / "vllm_omni_b200" / "csrc" / name).read_bytes())
     return h.hexdigest()[:16]
 
@@ -384,10 +384,10 @@ class Arm:
             self.kv_bytes = int(inp.seq_lens[b0:b1].sum().item()) * 2 * hkv * d * (1 if wl.fp8 else 2)
         self.dB = int(self.dq.shape[0])
         # schedule: stream-K (no split count) unless a split count or a fixed-split variant is asked for
-        self.streamk = args.variant in (ops.VARIANT_STREAMK, ops.VARIANT_SK2) or (
+        self.streamk = args.variant in (ops.VARIANT_STREAMK, ops.VARIANT_SK2, ops.VARIANT_SK3) or (
             args.variant == ops.VARIANT_AUTO and args.splits == 0)
-        self.variant = (args.variant or ops.VARIANT_SK2) if self.streamk else (args.variant or ops.VARIANT_STREAM)
-        self.planned = self.variant == ops.VARIANT_SK2
+        self.variant = (args.variant or ops.VARIANT_SK3) if self.streamk else (args.variant or ops.VARIANT_STREAM)
+        self.planned = self.variant in (ops.VARIANT_SK2, ops.VARIANT_SK3)
         self.splits = 0 if self.streamk else (args.splits or ops.decode_num_splits(B, hq, hkv, inp.max_seq_len))
         self.ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(max(self.dB, 1), self.dhq, d, max(self.splits, 1)))
         self.hidden = torch.zeros(B, wl.hidden_size, dtype=torch.bfloat16, device="cuda")  # o_proj output stand-in
@@ -409,9 +409,10 @@ class Arm:
                     self.ar = None
                     self.ar_note = f"nccl all_reduce (peer-memory setup failed: {type(exc).__name__}: {str(exc)[:200]})"
                     log(self.ar_note)
-        # our kernels only (not NCCL / copies): plan + L x (cache write + decode + reduce [+ all-reduce] [+ 2 exchanges])
-        per_layer = 2 + (1 if (self.splits > 1 or self.streamk) else 0) + (1 if self.ar is not None else 0) + (
-            2 if self.ex is not None else 0)
+        # our kernels only (not NCCL / copies): plan + L x (cache write + decode [+ reduce] [+ all-reduce] [+ 2 exchanges]);
+        # the cooperative stream-K kernel folds its partials itself (no reduce launch)
+        reduce = (self.splits > 1) if not self.streamk else self.variant != ops.VARIANT_SK3
+        per_layer = 2 + (1 if reduce else 0) + (1 if self.ar is not None else 0) + (2 if self.ex is not None else 0)
         self.launches_per_step = L * per_layer + (1 if self.planned and self.dB > 0 else 0)
 
     # ---- pieces of the step
@@ -434,7 +435,7 @@ class Arm:
         if self.dB == 0:
             return
         v = self.variant if variant is None else variant
-        pl = (self.planned if planned is None else planned) and v == ops.VARIANT_SK2
+        pl = (self.planned if planned is None else planned) and v in (ops.VARIANT_SK2, ops.VARIANT_SK3)
         ops.paged_decode(self.dq, kc, vc, self.dbt, self.dsl, inp.max_seq_len, inp.softmax_scale,
                          out=self.dout if out is None else out, kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
                          v_scale=inp.v_scale, num_splits=self.splits if splits is None else splits, variant=v,
@@ -670,13 +671,16 @@ def run_b200(args, wl):
     from vllm_omni_b200 import ops
     kname = {1: "paged_decode_tma_kernel + lse_reduce_kernel", 2: "paged_decode_cpasync_kernel + lse_reduce_kernel",
              3: "paged_decode_stream_kernel + lse_reduce_kernel", 4: "paged_decode_streamk_kernel + streamk_reduce_kernel",
-             5: "paged_decode_sk2_kernel + sk2_reduce_kernel"}[arm.variant]
+             5: "paged_decode_sk2_kernel + sk2_reduce_kernel",
+             6: "paged_decode_sk3_kernel (partials folded inside the kernel: no reduce launch)"}[arm.variant]
     roofline = {
         "bound": "hbm", "kernel": kname,
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "traffic_note": traffic_note, "peak_source": peak_src, "algorithmic_bytes_per_launch": kv_bytes,
         "kernel_avg_us": full_avg_ms * 1e3, "kernel_median_us": full_med_ms * 1e3,
-        "kernel_avg_note": "decode + LSE-reduce launches (SURVEY 8d: t_kernel = partial + reduce), max over ranks",
+        "kernel_avg_note": ("the complete decode of a layer (SURVEY 8d: t_kernel = partial + reduce; this kernel folds "
+                            "its partials itself, there is no reduce launch), max over ranks" if arm.variant == 6 else
+                            "decode + LSE-reduce launches (SURVEY 8d: t_kernel = partial + reduce), max over ranks"),
         "decode_only_us": part_avg_ms * 1e3,
         "achieved_decode_only": kv_bytes / (part_avg_ms * 1e-3) / 1e9 if part_avg_ms > 0 else 0.0,
         "kernel_share_of_step": full_avg_ms * L / ms_per_step, "frac_of_8TBps": achieved / 8000.0,

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 8
+#define B200ATTN_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -60,7 +60,10 @@ extern "C" {
 #define B200ATTN_VARIANT_STREAM 3   /* persistent, per-warp cp.async rings across items  */
 #define B200ATTN_VARIANT_STREAMK 4  /* persistent, equal tile chunks per warp + reduce launch (round-1 default) */
 #define B200ATTN_VARIANT_SK2 5      /* the same schedule planned once per step, chunk sizes follow the SMs' measured
-                                       rates, plan-driven reduce launch (default) */
+                                       rates, plan-driven reduce launch (round 2 comparison arm) */
+#define B200ATTN_VARIANT_SK3 6      /* cooperative stream-K (default): teams of warps walk an item together and fold
+                                       their states in shared memory; items cut by a team boundary are folded by
+                                       their owner through an arrival counter — no reduce launch */
 
 /* b200attn_paged_decode flags */
 #define B200ATTN_DECODE_PLANNED 1        /* b200attn_decode_plan was run on this workspace for exactly these
@@ -386,6 +389,19 @@ B200ATTN_API int b200attn_peer_free(void* ptr);
  * stream-K decode launches records its {entry, static-chunk end, end} %globaltimer stamps.
  */
 B200ATTN_API void b200attn_debug_set_trace(void* device_buffer);
+
+/*
+ * Debug / test aid: force the team size (warps that share an item: 1, 2, 3, 4, 6 or 12) the next
+ * cooperative stream-K plans of this thread use; 0 restores the plan kernel's own rule (from the
+ * step's average item length). Results do not depend on it beyond fp32 summation order.
+ */
+B200ATTN_API void b200attn_debug_set_team(int32_t warps);
+
+/* Byte offset, inside a decode workspace, of the plan b200attn_decode_plan writes for (batch, num_q_heads)
+ * on the current device (int32 words: header 16 {positions, CTAs G, team size T, teams, batch, head groups,
+ * 0, magic, teams per CTA} | team starts [12 G + 1, padded to 4] | team descriptors [12 G][4] | team info
+ * [12 G][4] | warp descriptors [12 G][4] | tiles prefix [batch + 1]); tests read the plan back through it. */
+B200ATTN_API size_t b200attn_debug_plan_offset(int32_t batch, int32_t num_q_heads);
 
 /*
  * The stream-K schedule for `total_tiles` KV tiles on `num_warps` warps (pure host arithmetic,

@@ -95,13 +95,15 @@ def report(name, fn, note="", pre=None):
 ours(caches[0][0], caches[0][1], out_ours)
 torch.cuda.synchronize()
 ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)  # the step's plan (planned modes)
-report("b200attn stream-K v2 (default call: plan launch + decode with the merge inside)", ours)
-report("b200attn stream-K v2, planned once per step", make_ours(ops.VARIANT_SK2, planned=True), pre=plan_step,
+report("b200attn cooperative stream-K (default call: plan launch + decode, nothing planned ahead)", ours)
+report("b200attn cooperative stream-K, planned once per step", make_ours(ops.VARIANT_SK3, planned=True), pre=plan_step,
        note=f"one plan launch per {L} layers inside the timed graph")
-report("b200attn stream-K v2, planned + early KV reads (what the backend passes)",
+report("b200attn cooperative stream-K, planned + early KV reads (what the backend passes)",
+       make_ours(ops.VARIANT_SK3, planned=True, early=True), pre=plan_step)
+report("b200attn cooperative stream-K, planned + early, cache write + decode per layer",
+       make_ours(ops.VARIANT_SK3, planned=True, early=True, write=True), note="two launches per layer", pre=plan_step)
+report("b200attn stream-K v2 (round 2 first half: per-warp chunks + reduce launch), planned + early",
        make_ours(ops.VARIANT_SK2, planned=True, early=True), pre=plan_step)
-report("b200attn stream-K v2, planned + early, cache write + decode per layer",
-       make_ours(ops.VARIANT_SK2, planned=True, early=True, write=True), note="two launches per layer", pre=plan_step)
 report("b200attn stream-K v1 (round 1: decode + reduce launch)", make_ours(ops.VARIANT_STREAMK))
 report("b200attn stream-K v1, cache write + decode + reduce per layer", make_ours(ops.VARIANT_STREAMK, write=True),
        note="three launches per layer")

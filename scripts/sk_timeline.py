@@ -1,7 +1,7 @@
 #!/usr/bin/env python
-"""Per-warp timeline of the stream-K v2 decode kernel (b200attn_debug_set_trace): for every warp the
+"""Per-warp timeline of the stream-K decode kernels (VARIANT=6 cooperative, default; VARIANT=5 second generation) (b200attn_debug_set_trace): for every warp the
 %globaltimer stamps {entry, first stage landed, end of streaming, merges done} and the SM id of isolated
-launches (device idle before each). Usage: sk2_trace.py [workload] [layers] [tp] [launches]"""
+launches (device idle before each). Usage: sk_timeline.py [workload] [layers] [tp] [launches]"""
 import json
 import os
 import sys
@@ -17,6 +17,7 @@ L = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 tp = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 launches = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 contig = os.environ.get("CONTIG", "0") == "1"
+variant = int(os.environ.get("VARIANT", "6"))
 wl = workloads.WORKLOADS[wl_name]
 inp = workloads.make_decode_inputs(wl, "cuda", num_layers=L, tp_size=tp, rank=0, contiguous_blocks=contig)
 caches = [ops.split_kv_cache(c) for c in inp.kv_caches]
@@ -34,7 +35,7 @@ ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)
 def run(kc, vc, planned=True, early=True):
     ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len, inp.softmax_scale, out=out,
                      kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale, v_scale=inp.v_scale, workspace=ws,
-                     variant=ops.VARIANT_SK2, planned=planned, early_kv_read=early)
+                     variant=variant, planned=planned, early_kv_read=early)
 
 
 def mmm(x):
@@ -70,7 +71,7 @@ for rep in range(launches):
     used = torch.zeros(int(smid.max()) + 1, dtype=torch.bool)
     used[smid] = True
     per_sm.append(end_by_sm)
-    print(json.dumps({"workload": wl_name, "tp": tp, "launch": rep, "kv_bytes": inp.kv_bytes_per_layer,
+    print(json.dumps({"workload": wl_name, "variant": variant, "tp": tp, "launch": rep, "kv_bytes": inp.kv_bytes_per_layer,
                       "interleave": os.environ.get("B200ATTN_SK2_DEBUG_INTERLEAVE", "0"), "contiguous_blocks": contig,
                       "smid_max": int(smid.max()), "sms_used": int(used.sum()),
                       "entry_us": mmm(cols[0]), "first_landed_us": mmm(cols[1]), "stream_end_us": mmm(cols[2]),

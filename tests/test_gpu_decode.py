@@ -17,7 +17,7 @@ from vllm_omni_b200 import _lib, layout, ops, workloads
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-3
-VARIANTS = [ops.VARIANT_SK2, ops.VARIANT_STREAMK, ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
+VARIANTS = [ops.VARIANT_SK3, ops.VARIANT_SK2, ops.VARIANT_STREAMK, ops.VARIANT_STREAM, ops.VARIANT_TMA, ops.VARIANT_CPASYNC]
 
 
 def run_device(c, variant=ops.VARIANT_AUTO, num_splits=0, want_lse=True, cache_dev=None, q_dev=None):
@@ -161,7 +161,7 @@ def test_abi_errors_surface_as_exceptions(lib):
     c = make_case([100], hq=8, hkv=2, seed=1)
     cache = cache_to_dev(c.kv_cache)
     q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
-    tiny = ops.DecodeWorkspace("cuda", 16384)
+    tiny = ops.DecodeWorkspace("cuda", ops.WORKSPACE_MIN_BYTES)
     tiny.ensure = lambda n: None  # defeat the auto-grow: the C side must refuse
     with pytest.raises(_lib.B200AttnError, match="EWORKSPACE"):
         ops.paged_decode(q, cache[0], cache[1], bt, sl, 100, c.scale, num_splits=4, workspace=tiny)
@@ -224,7 +224,7 @@ def test_full_size_properties_cfg3(lib, ragged):
                                                    inp.max_seq_len, inp.softmax_scale, lse=lse,
                                                    num_splits=s, variant=variant), lse)
     torch.cuda.synchronize()
-    base, base_lse = outs[(ops.VARIANT_SK2, 0)]
+    base, base_lse = outs[(VARIANTS[0], 0)]
     assert torch.isfinite(base.float()).all()
     # (1) the staging variants agree (different chunking => different merge order). Two independent bf16
     # roundings of the same value are 2.3e-3 apart in rel-L2, plus each kernel's own P-rounding noise (~1.3e-3)
@@ -270,7 +270,7 @@ def test_fp8_decode_vs_oracle_small(lib, lens, per_head):
 @pytest.mark.parametrize("hq,hkv", [(32, 4), (28, 4), (16, 2), (4, 1), (4, 4), (16, 1), (24, 2)])
 def test_fp8_decode_gqa_group_shapes(lib, hq, hkv):
     c = make_case([200, 77, 16, 1000], hq=hq, hkv=hkv, seed=hq * 10 + hkv + 1, fp8=True)
-    for variant in (ops.VARIANT_SK2, ops.VARIANT_STREAMK):
+    for variant in (ops.VARIANT_SK3, ops.VARIANT_SK2, ops.VARIANT_STREAMK):
         out, lse = run_device(c, variant, 0)
         check(c, out, lse)
 
@@ -357,10 +357,11 @@ def test_decode_against_vllm_stock_kernel_fixtures(lib, name, variant):
     (4, 1, [3000, 9000, 1]),              # TP8-shard shape, items spanning several CTAs
     (16, 1, [5000, 4097]),                # two head sub-groups per KV head
 ])
-def test_sk2_items_cut_into_many_pieces(lib, hq, hkv, lens, fp8):
+@pytest.mark.parametrize("variant", [ops.VARIANT_SK3, ops.VARIANT_SK2])
+def test_sk2_items_cut_into_many_pieces(lib, hq, hkv, lens, fp8, variant):
     c = make_case(lens, hq=hq, hkv=hkv, seed=len(lens) + hq, fp8=fp8)
-    for _ in range(2):  # second launch: the arrival counters must have been left at zero by the first
-        out, lse = run_device(c, ops.VARIANT_SK2, 0)
+    for _ in range(3):  # later launches: the arrival counters must have been left at zero by the earlier ones
+        out, lse = run_device(c, variant, 0)
         check(c, out, lse)
 
 
@@ -370,8 +371,9 @@ def test_sk2_batch_beyond_2048_and_many_items_per_cta(lib):
     g = torch.Generator().manual_seed(11)
     lens = torch.randint(0, 70, (3000,), generator=g).tolist()
     c = make_case(lens, hq=8, hkv=2, seed=77)
-    out, lse = run_device(c, ops.VARIANT_SK2, 0)
-    check(c, out, lse)
+    for variant in (ops.VARIANT_SK3, ops.VARIANT_SK2):
+        out, lse = run_device(c, variant, 0)
+        check(c, out, lse)
     c8 = make_case(lens[:2500], hq=8, hkv=2, seed=78, fp8=True)
     out, lse = run_device(c8, ops.VARIANT_AUTO, 0)
     check(c8, out, lse)
@@ -384,17 +386,19 @@ def test_sk2_workspace_shared_with_other_variants(lib):
     cache = cache_to_dev(c.kv_cache)
     q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
     ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(4, 8, 128, 8))
-    for variant, splits in ((ops.VARIANT_SK2, 0), (ops.VARIANT_STREAMK, 0), (ops.VARIANT_STREAM, 8),
-                            (ops.VARIANT_SK2, 0), (ops.VARIANT_TMA, 4), (ops.VARIANT_SK2, 0)):
+    for variant, splits in ((ops.VARIANT_SK3, 0), (ops.VARIANT_SK2, 0), (ops.VARIANT_STREAMK, 0), (ops.VARIANT_STREAM, 8),
+                            (ops.VARIANT_SK3, 0), (ops.VARIANT_SK2, 0), (ops.VARIANT_TMA, 4), (ops.VARIANT_SK3, 0),
+                            (ops.VARIANT_SK2, 0)):
         out = torch.full((4, 8, 128), 3.0, dtype=torch.bfloat16, device="cuda")
         ops.paged_decode(q, cache[0], cache[1], bt, sl, c.max_seq_len, c.scale, out=out, num_splits=splits,
                          variant=variant, workspace=ws)
         check(c, out, None)
 
 
+@pytest.mark.parametrize("variant", [ops.VARIANT_SK3, ops.VARIANT_SK2])
 @pytest.mark.parametrize("graph", [False, True])
 @pytest.mark.parametrize("fp8", [False, True])
-def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8):
+def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8, variant):
     """A decode step as the backend runs it: ONE plan launch, then per layer cache write -> decode with
     B200ATTN_DECODE_PLANNED | _EARLY_KV_READ, all launches chained by programmatic dependent launch. Every
     layer's output must see the token its own cache write stored (the tile a sequence ends in is only loaded
@@ -424,7 +428,7 @@ def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8):
             ops.reshape_and_cache(new_k_d[l], new_v_d[l], caches[l][0], caches[l][1], last_d, kvd, ks, vs)
             ops.paged_decode(qs[l], caches[l][0], caches[l][1], bt, sl, max(lens), cases[l].scale, out=outs[l],
                              kv_cache_dtype=kvd, k_scale=ks, v_scale=vs, workspace=ws, planned=True,
-                             early_kv_read=True)
+                             early_kv_read=True, variant=variant)
 
     if graph:
         side = torch.cuda.Stream()
@@ -448,3 +452,72 @@ def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8):
         oracle.ref_reshape_and_cache(new_k[l], new_v[l], c.kv_cache[0], c.kv_cache[1], last, fp8, c.k_scale, c.v_scale)
         assert torch.equal(caches[l].cpu().view(torch.uint8), c.kv_cache.view(torch.uint8)), f"layer {l}: slot writes"
         check(c, outs[l], None)
+
+
+# ------------------------------------------------------------------------------------------------
+# Cooperative stream-K (the default): teams of T warps share an item. Every team size must give the
+# oracle's result on shapes that put whole items, cut items (two pieces, many pieces), items shorter
+# than a team, empty sequences and head sub-groups in one launch.
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("team", [0, 1, 2, 3, 4, 6, 12])
+@pytest.mark.parametrize("fp8", [False, True])
+def test_sk3_team_sizes(lib, team, fp8):
+    cases = [
+        make_case([4096, 1, 16, 17, 2049, 800, 4095, 33, 0, 5], hq=16, hkv=2, seed=300 + team, fp8=fp8),
+        make_case([20000], hq=8, hkv=1, seed=310 + team, fp8=fp8),
+        make_case([3000, 9000, 1], hq=16, hkv=1, seed=320 + team, fp8=fp8),
+    ]
+    g = torch.Generator().manual_seed(team)
+    cases.append(make_case(torch.randint(0, 200, (700,), generator=g).tolist(), hq=8, hkv=2, seed=330 + team, fp8=fp8))
+    lib.b200attn_debug_set_team(team)
+    try:
+        for c in cases:
+            for _ in range(2):
+                out, lse = run_device(c, ops.VARIANT_SK3, 0)
+                check(c, out, lse)
+    finally:
+        lib.b200attn_debug_set_team(0)
+
+
+def test_sk3_plan_contents(lib):
+    """The plan the decode kernel follows: team ranges tile the stream, descriptors point at their starts, and the
+    owner / continuation bookkeeping of cut items is consistent (every continuation names an owner whose count of
+    continuing teams includes it)."""
+    lens = [4096, 1, 16, 17, 2049, 800, 4095, 33, 0, 5]
+    B, hq, hkv = len(lens), 16, 2
+    c = make_case(lens, hq=hq, hkv=hkv, seed=1)
+    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, hq, 128, 1))
+    for team in (12, 4, 1):
+        lib.b200attn_debug_set_team(team)
+        try:
+            ops.decode_plan(c.seq_lens.cuda(), c.block_table.cuda(), B, hq, hkv, 16, ws)
+        finally:
+            lib.b200attn_debug_set_team(0)
+        torch.cuda.synchronize()
+        plan = ops.debug_sk3_plan(ws, B, hq)
+        G, T, nt, hs = plan["groups"], plan["T"], plan["nt"], plan["hs_count"]
+        assert T == team and nt == G * (12 // T) and hs == hkv
+        tiles = [(s + 15) // 16 for s in lens]
+        assert plan["total"] == sum(tiles) * hs
+        ts = plan["tstart"]
+        assert ts[0] == 0 and ts[nt] == plan["total"] and all(ts[i] <= ts[i + 1] for i in range(nt))
+        # stream position -> (b, hs, tile)
+        pos = []
+        for b, n in enumerate(tiles):
+            for h in range(hs):
+                pos += [(b, h, t, n) for t in range(n)]
+        for i in range(nt):
+            if ts[i] < ts[i + 1]:
+                assert tuple(plan["tdesc"][i]) == pos[ts[i]]
+        conts = {}
+        for i in range(nt):
+            own, np_first, m_last, contig = plan["tinfo"][i]
+            if ts[i] < ts[i + 1] and pos[ts[i]][2] > 0:
+                assert own >= 0 and own < i
+                conts.setdefault(own, []).append(i)
+                assert np_first >= 2
+            else:
+                assert own == -1
+        for own, lst in conts.items():
+            assert plan["tinfo"][own][2] == len(lst), (own, lst, plan["tinfo"][own])
+            assert plan["tinfo"][lst[0]][1] == len(lst) + 1

@@ -12,7 +12,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 PEER_FLAG_BYTES = 8192
 AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH, AR_PUSH2 = 0, 1, 2, 3, 4, 5
 KV_BF16 = 0
@@ -23,6 +23,7 @@ VARIANT_CPASYNC = 2
 VARIANT_STREAM = 3
 VARIANT_STREAMK = 4
 VARIANT_SK2 = 5
+VARIANT_SK3 = 6
 DECODE_PLANNED = 1
 DECODE_EARLY_KV_READ = 2
 
@@ -84,6 +85,8 @@ SIGNATURES: dict[str, tuple] = {
     "b200attn_workspace_init": (C.c_int, [_vp, _sz, _vp]),
     "b200attn_decode_plan": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i64, _i32, _vp, _sz, _vp]),
     "b200attn_debug_set_trace": (None, [_vp]),
+    "b200attn_debug_set_team": (None, [C.c_int32]),
+    "b200attn_debug_plan_offset": (C.c_size_t, [C.c_int32, C.c_int32]),
     "b200attn_debug_sk_schedule": (None, [_i64, _i32, _i32, C.POINTER(_i64)]),
     "b200attn_paged_decode": (C.c_int, _DECODE_ARGS),
     "b200attn_paged_decode_partial": (C.c_int, _DECODE_ARGS),

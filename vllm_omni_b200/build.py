@@ -14,7 +14,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 CSRC = PKG_DIR / "csrc"
 LIB_PATH = PKG_DIR / "libb200attn.so"
-SOURCES = ["api.cu", "paged_decode.cu", "paged_decode_stream.cu", "paged_decode_streamk.cu", "paged_decode_sk2.cu", "cache_ops.cu", "paged_prefill.cu", "rope_cache.cu", "peer_allreduce.cu", "paged_prefill_umma.cu"]
+SOURCES = ["api.cu", "paged_decode.cu", "paged_decode_stream.cu", "paged_decode_streamk.cu", "paged_decode_sk2.cu", "paged_decode_sk3.cu", "cache_ops.cu", "paged_prefill.cu", "rope_cache.cu", "peer_allreduce.cu", "paged_prefill_umma.cu"]
 HEADERS = ["ptx.cuh", "umma.cuh", "decode_common.cuh", "sk_math.cuh", "kernels.h", "../../include/b200attn.h"]
 
 NVCC_FLAGS = [

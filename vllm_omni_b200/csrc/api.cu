@@ -247,9 +247,12 @@ int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64
 // it are left at zero by every kernel: [0, 256) stream-K v1 words, [256, ...) Sk2Ctrl of stream-K v2
 // (arrival counters, chunk-group claims, per-SM rates and weights). No variant writes anything else here,
 // so one workspace can serve different variants in turn.
-constexpr size_t kWsCtrlBytes = 16384;
+constexpr size_t kWsCtrlBytes = 65536;
+constexpr size_t kWsSk3CntOff = 16384;  // cooperative stream-K arrival counters [2 parities][teams <= 512 * 12]
 constexpr size_t kWsSk2CtrlOff = 256;
-static_assert(kWsSk2CtrlOff + sizeof(Sk2Ctrl) <= kWsCtrlBytes, "control area too small for Sk2Ctrl");
+static_assert(kWsSk2CtrlOff + sizeof(Sk2Ctrl) <= kWsSk3CntOff, "control area too small for Sk2Ctrl");
+static_assert(kWsSk3CntOff + 2ull * kSk2MaxGroups * kSk3Warps * sizeof(int32_t) <= kWsCtrlBytes,
+              "control area too small for the cooperative stream-K arrival counters");
 size_t fixed_workspace_bytes(int batch, int num_q_heads, int head_size, int splits) {
   const size_t rows = static_cast<size_t>(batch) * num_q_heads * splits;
   return kWsCtrlBytes + rows * head_size * sizeof(float) + rows * sizeof(float) + 256;
@@ -307,6 +310,36 @@ Sk2Layout sk2_layout(void* workspace, int sms) {
   l.part_lse = l.part_o + rows * kHeadDim;
   l.plan = reinterpret_cast<int32_t*>(l.part_lse + rows);
   return l;
+}
+
+// cooperative stream-K (paged_decode_sk3.cu) region, behind the stream-K v2 region:
+// [partial rows: 2 parities x 2 * teams x 8 x 128 f32 | their LSEs | plan]
+struct Sk3Layout {
+  float *part_o, *part_lse;
+  int32_t *plan, *cnt;
+};
+size_t sk3_region_off(int batch, int num_q_heads, int sms) {
+  return (sk2_workspace_bytes(batch, num_q_heads, sms) + 255) & ~static_cast<size_t>(255);
+}
+size_t sk3_slot_rows(int sms) { return 2ull * 2ull * sms * decode_sk3_warps() * kHeadsPerItem; }
+size_t sk3_workspace_bytes(int batch, int num_q_heads, int sms) {
+  return sk3_region_off(batch, num_q_heads, sms) + sk3_slot_rows(sms) * (kHeadDim + 1) * sizeof(float) +
+         (sk3_plan_ints(batch, sms) + 4) * sizeof(int32_t) + 256;
+}
+Sk3Layout sk3_layout(void* workspace, int batch, int num_q_heads, int sms) {
+  uint8_t* base = static_cast<uint8_t*>(workspace);
+  Sk3Layout l;
+  l.cnt = reinterpret_cast<int32_t*>(base + kWsSk3CntOff);
+  l.part_o = reinterpret_cast<float*>(base + sk3_region_off(batch, num_q_heads, sms));
+  l.part_lse = l.part_o + sk3_slot_rows(sms) * kHeadDim;
+  l.plan = reinterpret_cast<int32_t*>(l.part_lse + sk3_slot_rows(sms));
+  return l;
+}
+thread_local int g_sk3_team = 0;  // debug: forced team size (0 = the plan kernel's rule)
+int sk3_team_force() {
+  if (g_sk3_team > 0) return g_sk3_team;
+  const char* v = getenv("B200ATTN_SK3_TEAM");
+  return (v == nullptr || *v == '\0') ? 0 : atoi(v);
 }
 
 thread_local unsigned long long* g_trace = nullptr;
@@ -502,8 +535,10 @@ size_t b200attn_decode_workspace_bytes(int32_t max_batch, int32_t num_q_heads, i
   if (sms <= 0) sms = 148;
   const size_t sk = sk_workspace_bytes(max_batch, sms);
   const size_t sk2 = sk2_workspace_bytes(max_batch, num_q_heads, sms);
-  const size_t m = fixed > sk ? fixed : sk;
-  return m > sk2 ? m : sk2;
+  const size_t sk3 = sk3_workspace_bytes(max_batch, num_q_heads, sms);
+  size_t m = fixed > sk ? fixed : sk;
+  m = m > sk2 ? m : sk2;
+  return m > sk3 ? m : sk3;
 }
 
 static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t q_stride_tok,
@@ -533,13 +568,31 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
 
   if (num_splits < 0 || num_splits > kMaxSplits)
     return fail(B200ATTN_EINVAL, "num_splits %d out of [0, %d]", num_splits, kMaxSplits);
-  if (variant < B200ATTN_VARIANT_AUTO || variant > B200ATTN_VARIANT_SK2)
+  if (variant < B200ATTN_VARIANT_AUTO || variant > B200ATTN_VARIANT_SK3)
     return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
   if (flags & ~(B200ATTN_DECODE_PLANNED | B200ATTN_DECODE_EARLY_KV_READ))
     return fail(B200ATTN_EINVAL, "unknown decode flags 0x%x", flags);
+  // schedule: cooperative stream-K (teams of warps share an item, merges in shared memory, no reduce launch)
+  // unless the caller asks for a fixed split count or another kernel
+  bool use_sk3 = variant == B200ATTN_VARIANT_SK3 || (variant == B200ATTN_VARIANT_AUTO && num_splits == 0);
+  if (use_sk3) {
+    const int tpp = block_size / kTileTokens;
+    const bool fits = workspace != nullptr && tpp > 0 && tpp * kTileTokens == block_size && (tpp & (tpp - 1)) == 0 &&
+                      sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes && sms <= kSk2MaxGroups &&
+                      (reinterpret_cast<uintptr_t>(workspace) % 16) == 0;
+    if (!fits) {
+      if (variant == B200ATTN_VARIANT_SK3 || (flags & B200ATTN_DECODE_PLANNED))
+        return fail(B200ATTN_EWORKSPACE,
+                    "stream-K needs block_size = 16 * 2^k and a 16-byte aligned workspace of %zu B (got %zu)",
+                    sk3_workspace_bytes(batch, num_q_heads, sms), workspace_bytes);
+      use_sk3 = false;  // AUTO: fall back to the fixed-split schedule
+      if (variant == B200ATTN_VARIANT_AUTO) variant = B200ATTN_VARIANT_STREAM;
+    }
+  }
+  if (use_sk3) variant = B200ATTN_VARIANT_SK3;
   // schedule: stream-K v2 (equal tile chunks per warp, no split count, merge inside the kernel) unless the
   // caller asks for a fixed split count or another kernel
-  bool use_sk2 = variant == B200ATTN_VARIANT_SK2 || (variant == B200ATTN_VARIANT_AUTO && num_splits == 0);
+  bool use_sk2 = variant == B200ATTN_VARIANT_SK2;
   if (use_sk2) {
     const int tpp = block_size / kTileTokens;
     const bool fits = workspace != nullptr && tpp > 0 && (tpp & (tpp - 1)) == 0 &&
@@ -554,7 +607,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     }
   }
   if (use_sk2) variant = B200ATTN_VARIANT_SK2;
-  if ((flags & B200ATTN_DECODE_PLANNED) && !use_sk2)
+  if ((flags & B200ATTN_DECODE_PLANNED) && !use_sk2 && !use_sk3)
     return fail(B200ATTN_EINVAL, "B200ATTN_DECODE_PLANNED is only meaningful for the stream-K schedule");
   bool use_sk = variant == B200ATTN_VARIANT_STREAMK;
   if (use_sk) {
@@ -576,7 +629,12 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   float* part_lse = nullptr;
   int32_t* plan_cum = nullptr;
   Sk2Layout sk2{};
-  if (use_sk2) {
+  Sk3Layout sk3{};
+  if (use_sk3) {
+    num_splits = 1;
+    sk2 = sk2_layout(workspace, sms);  // the control words (claims, SM rates) are shared
+    sk3 = sk3_layout(workspace, batch, num_q_heads, sms);
+  } else if (use_sk2) {
     num_splits = 1;
     sk2 = sk2_layout(workspace, sms);
     part_o = sk2.part_o;
@@ -630,6 +688,10 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   p.trace = g_trace;
   p.sk2_plan = sk2.plan;
   p.sk2_ctrl = sk2.ctrl;
+  p.sk3_plan = sk3.plan;
+  p.sk3_part_o = sk3.part_o;
+  p.sk3_part_lse = sk3.part_lse;
+  p.sk3_cnt = sk3.cnt;
   p.flags = 0;
   const int64_t items = static_cast<int64_t>(batch) * num_kv_heads * num_splits * p.subgroups;
   if (items > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many work items");
@@ -645,7 +707,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
     const bool fp8 = kv_dtype == B200ATTN_KV_FP8_E4M3;
     if (fp8) {
-      if (variant != B200ATTN_VARIANT_STREAMK && variant != B200ATTN_VARIANT_SK2)
+      if (variant != B200ATTN_VARIANT_STREAMK && variant != B200ATTN_VARIANT_SK2 && variant != B200ATTN_VARIANT_SK3)
         return fail(B200ATTN_EUNSUPPORTED,
                     "fp8 KV decode is built for the stream-K schedule only (variant AUTO/SK2/STREAMK, num_splits 0, "
                     "block_size = 16 * 2^k, workspace of b200attn_decode_workspace_bytes)");
@@ -668,7 +730,8 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     for (int sh = 0; sh < 16; ++sh)
       if ((1 << sh) == p.tiles_per_page) p.tpp_shift = sh;
     p.tpp_mask = p.tiles_per_page - 1;
-    if ((variant == B200ATTN_VARIANT_STREAMK || variant == B200ATTN_VARIANT_SK2) && p.tpp_shift < 0) {
+    if ((variant == B200ATTN_VARIANT_STREAMK || variant == B200ATTN_VARIANT_SK2 || variant == B200ATTN_VARIANT_SK3) &&
+        p.tpp_shift < 0) {
       // block sizes that are not 16 * 2^k go through the fixed-split kernel
       return fail(B200ATTN_EUNSUPPORTED, "stream-K needs block_size = 16 * 2^k (got %d)", block_size);
     }
@@ -695,6 +758,27 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       e = launch_decode_cpasync(p, stream);
     } else if (variant == B200ATTN_VARIANT_STREAM) {
       e = launch_decode_stream(p, static_cast<int>(items < sms ? items : sms), stream);
+    } else if (variant == B200ATTN_VARIANT_SK3) {
+      const CUtensorMap *mk = nullptr, *mv = nullptr;
+      if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
+                               num_kv_heads, block_size, fp8, &mk))
+        return rc;
+      const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
+      if (int rc = get_kv_map5(v_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
+                               num_kv_heads, block_size, fp8, &mv))
+        return rc;
+      const bool pdl = env_flag("B200ATTN_PDL", true);
+      if (!(flags & B200ATTN_DECODE_PLANNED)) {
+        // no plan of this step in the workspace: make it now; the decode kernel then waits for it first
+        if (cudaError_t pe = launch_sk3_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms, sk3.plan, sk2.ctrl,
+                                             sk2_calib_max(), sk3_team_force(), stream))
+          return cuda_fail(pe, "decode plan launch");
+        p.flags |= kSk2FlagWaitFirst;
+      }
+      if ((flags & B200ATTN_DECODE_EARLY_KV_READ) && env_flag("B200ATTN_EARLY_KV_READ", true))
+        p.flags |= kSk2FlagEarlyKvRead;
+      if ((g_sk2_parity ^= 1) != 0) p.flags |= kSk2FlagParity;  // consecutive launches alternate their control words
+      e = launch_decode_sk3(tm_k, *mv, p, fp8, sms, pdl, stream);
     } else if (variant == B200ATTN_VARIANT_SK2) {
       const CUtensorMap *mk = nullptr, *mv = nullptr;
       if (int rc = get_kv_map5(k_cache, cache_stride_block, cache_stride_slot, cache_stride_head, num_blocks,
@@ -824,6 +908,12 @@ int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_h
   const int group = num_q_heads / num_kv_heads;
   const int subgroups = (group + kHeadsPerItem - 1) / kHeadsPerItem;
   const Sk2Layout l = sk2_layout(workspace, sms);
+  if (sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes) {
+    const Sk3Layout l3 = sk3_layout(workspace, batch, num_q_heads, sms);
+    if (cudaError_t e3 = launch_sk3_plan(seq_lens, batch, num_kv_heads * subgroups, sms, l3.plan, l.ctrl, sk2_calib_max(),
+                                         sk3_team_force(), static_cast<cudaStream_t>(stream)))
+      return cuda_fail(e3, "decode plan launch");
+  }
   cudaError_t e = launch_sk2_plan(seq_lens, batch, num_kv_heads * subgroups, sms, block_table, block_table_stride, tpp,
                                   shift, l.plan, l.ctrl, sk2_calib_max(), static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "decode plan launch");
@@ -846,6 +936,13 @@ void b200attn_debug_sk_schedule(int64_t total_tiles, int32_t num_warps, int32_t 
 }
 
 void b200attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<unsigned long long*>(device_buffer); }
+void b200attn_debug_set_team(int32_t warps) { g_sk3_team = warps; }
+size_t b200attn_debug_plan_offset(int32_t batch, int32_t num_q_heads) {
+  int sms = cached_num_sms();
+  if (sms <= 0) sms = 148;
+  uint8_t* base = nullptr;
+  return static_cast<size_t>(reinterpret_cast<uint8_t*>(sk3_layout(base, batch, num_q_heads, sms).plan) - base);
+}
 
 int b200attn_paged_prefill(const void* q, int64_t q_stride_tok, const void* k_cache, const void* v_cache,
                            int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,

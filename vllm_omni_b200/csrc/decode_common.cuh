@@ -34,6 +34,9 @@ constexpr int kSk2CalibMinTiles = 96;   // an SM's rate is only trusted if it st
 constexpr float kSk2CalibGain = 0.7f;   // share of the measured rate in a weight update
 constexpr int kSk2CalibUpdatesDefault = 8;  // weight updates before the weights are frozen (B200ATTN_SK2_CALIB)
 constexpr int kSk2FlagDebugInterleave = 4;  // debug: chunk c on CTA c % grid (timeline experiments; no merge, wrong output)
+constexpr int kSk3Warps = 12;            // cooperative stream-K (paged_decode_sk3.cu): warps per CTA
+constexpr int kSk3PlanHdrInts = 16;
+constexpr int kSk3PlanMagic = 0x534b3350;  // "SK3P"
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -85,6 +88,12 @@ struct DecodeParams {
   const int32_t* sk2_plan;  // layout in paged_decode_sk2.cu
   Sk2Ctrl* sk2_ctrl;
   int32_t flags;            // kSk2Flag*
+  // cooperative stream-K (paged_decode_sk3.cu): plan, partial slots [2 parities][2 * teams][8][128] (+ LSEs),
+  // arrival counters [2 parities][teams]
+  const int32_t* sk3_plan;
+  float* sk3_part_o;
+  float* sk3_part_lse;
+  int32_t* sk3_cnt;
 };
 
 // Stream-K schedule, computed identically by the decode and the reduce kernel from the tile total:

@@ -10,9 +10,9 @@ import torch
 
 from . import _lib
 from ._lib import (DECODE_EARLY_KV_READ, DECODE_PLANNED, KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC,  # noqa: F401
-                   VARIANT_SK2, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check)
+                   VARIANT_SK2, VARIANT_SK3, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check)
 
-WORKSPACE_MIN_BYTES = 16384  # control area (arrival / claim counters), see b200attn_workspace_init
+WORKSPACE_MIN_BYTES = 65536  # control area (arrival / claim counters), see b200attn_workspace_init
 
 _FP8_NAMES = ("fp8", "fp8_e4m3")
 
@@ -269,6 +269,27 @@ def decode_plan(seq_lens: torch.Tensor, block_table: torch.Tensor, batch: int, n
         block_table.stride(0), int(block_size), workspace.ptr, workspace.nbytes, _stream()))
 
 
+def debug_sk3_plan(workspace: DecodeWorkspace, batch: int, num_q_heads: int) -> dict:
+    """The plan `decode_plan` left in `workspace`, parsed (tests / timeline scripts; synchronises)."""
+    lib = _lib.load()
+    off = int(lib.b200attn_debug_plan_offset(int(batch), int(num_q_heads)))
+    words = workspace.buf[off:].view(torch.int32)
+    hdr = words[:16].cpu().tolist()
+    total, groups, T, nt, b, hs_count, _, magic, tpc = hdr[:9]
+    if magic != 0x534B3350:
+        raise RuntimeError("no cooperative stream-K plan in this workspace")
+    ntmax = groups * 12
+    o_desc = 16 + ((ntmax + 1 + 3) & ~3)
+    n_words = o_desc + 12 * ntmax + batch + 1
+    w = words[:n_words].cpu()
+    return {"total": total, "groups": groups, "T": T, "nt": nt, "batch": b, "hs_count": hs_count, "tpc": tpc,
+            "tstart": w[16:16 + ntmax + 1].tolist(),
+            "tdesc": w[o_desc:o_desc + 4 * ntmax].view(ntmax, 4).tolist(),
+            "tinfo": w[o_desc + 4 * ntmax:o_desc + 8 * ntmax].view(ntmax, 4).tolist(),
+            "wdesc": w[o_desc + 8 * ntmax:o_desc + 12 * ntmax].view(ntmax, 4).tolist(),
+            "cum": w[o_desc + 12 * ntmax:o_desc + 12 * ntmax + batch + 1].tolist()}
+
+
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                  block_table: torch.Tensor, seq_lens: torch.Tensor, max_seq_len: int,
                  softmax_scale: float, out: torch.Tensor | None = None,
@@ -292,7 +313,7 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         if planned:
             raise ValueError("planned=True needs the workspace decode_plan() was run on")
         workspace = DecodeWorkspace(q.device)
-    if num_splits != 1 or variant in (VARIANT_STREAMK, VARIANT_SK2):
+    if num_splits != 1 or variant in (VARIANT_STREAMK, VARIANT_SK2, VARIANT_SK3):
         s = num_splits if num_splits > 0 else decode_num_splits(
             batch, hq, k_cache.shape[2], max_seq_len)
         workspace.ensure(decode_workspace_bytes(batch, hq, d, s))
