@@ -300,6 +300,12 @@ int sk2_calib_max() {  // weight updates before the SM weights are frozen (0 = u
   const int x = atoi(v);
   return x < 0 ? 0 : x;
 }
+int sk3_calib_max() {
+  const char* v = getenv("B200ATTN_SK3_CALIB");
+  if (v == nullptr || *v == '\0') return kSk3CalibUpdatesDefault;
+  const int x = atoi(v);
+  return x < 0 ? 0 : x;
+}
 thread_local int g_sk2_parity = 0;
 Sk2Layout sk2_layout(void* workspace, int sms) {
   const size_t rows = sk2_part_rows(sms * decode_sk2_warps());
@@ -771,7 +777,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       if (!(flags & B200ATTN_DECODE_PLANNED)) {
         // no plan of this step in the workspace: make it now; the decode kernel then waits for it first
         if (cudaError_t pe = launch_sk3_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms, sk3.plan, sk2.ctrl,
-                                             sk2_calib_max(), sk3_team_force(), stream))
+                                             sk3_calib_max(), sk3_team_force(), stream))
           return cuda_fail(pe, "decode plan launch");
         p.flags |= kSk2FlagWaitFirst;
       }
@@ -910,7 +916,7 @@ int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_h
   const Sk2Layout l = sk2_layout(workspace, sms);
   if (sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes) {
     const Sk3Layout l3 = sk3_layout(workspace, batch, num_q_heads, sms);
-    if (cudaError_t e3 = launch_sk3_plan(seq_lens, batch, num_kv_heads * subgroups, sms, l3.plan, l.ctrl, sk2_calib_max(),
+    if (cudaError_t e3 = launch_sk3_plan(seq_lens, batch, num_kv_heads * subgroups, sms, l3.plan, l.ctrl, sk3_calib_max(),
                                          sk3_team_force(), static_cast<cudaStream_t>(stream)))
       return cuda_fail(e3, "decode plan launch");
   }

@@ -139,7 +139,9 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     const bool upd = !missing && ctrl->calib_updates < calib_max;
     const float rsum = sk3_block_sum(rate, s_red, tid), wsum = sk3_block_sum(w_raw, s_red, tid);
     const float w_old = wsum > 0.f ? w_raw / wsum : 1.f / groups;
-    float w = upd ? (1.f - kSk2CalibGain) * w_old + kSk2CalibGain * rate / rsum : w_old;
+    // the first updates follow the measurement closely, the later ones average the launch-to-launch noise out
+    const float gain = ctrl->calib_updates < 4 ? kSk2CalibGain : kSk3CalibGainLate;
+    float w = upd ? (1.f - gain) * w_old + gain * rate / rsum : w_old;
     if (!have) w = 0.f;
     const float norm = sk3_block_sum(w, s_red, tid);
     w /= norm;
@@ -806,8 +808,12 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     // what this SM achieved (the plan kernel turns it into the SM's share of the next steps' streams) ...
     if (smid < static_cast<uint32_t>(kSk2MaxGroups)) {
       const int32_t* tstart = plan + sk3_plan_tstart_off();
-      ctrl->stat_tiles[smid] = __ldg(tstart + (group + 1) * tpc) - __ldg(tstart + group * tpc);
-      ctrl->stat_cycles[smid] = static_cast<int>(min(static_cast<long long>(0x7fffffff), clock64() - sm.t0));
+      // summed over the launches since the last plan (every layer of a step): one launch is a noisy sample
+      const long long cyc = clock64() - sm.t0;
+      if (cyc > 0 && cyc < 0x10000000ll && ctrl->stat_cycles[smid] < 0x30000000) {
+        atomicAdd(&ctrl->stat_tiles[smid], __ldg(tstart + (group + 1) * tpc) - __ldg(tstart + group * tpc));
+        atomicAdd(&ctrl->stat_cycles[smid], static_cast<int>(cyc));
+      }
     }
     // ... and the last CTA of the launch re-arms the claim words of its parity
     __threadfence();
