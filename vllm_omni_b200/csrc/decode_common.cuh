@@ -38,6 +38,9 @@ constexpr float kSk3CalibGainLate = 0.4f;   // cooperative stream-K: weight-upda
 constexpr int kSk3CalibUpdatesDefault = 24; // ... and the number of updates before the weights are frozen (B200ATTN_SK3_CALIB)
 constexpr int kSk3Warps = 12;            // cooperative stream-K (paged_decode_sk3.cu): warps per CTA
 constexpr int kSk3PlanHdrInts = 16;
+constexpr int kSk3SegPerCta = 16;       // segments (team ranges + pool units) per CTA the plan and the slots have room for
+constexpr int kSk3MaxUnits = 8;         // pool units per team at most
+constexpr int kSk3PoolPctDefault = 14;  // share of a team range that is cut into pool units (B200ATTN_SK3_POOL)
 constexpr int kSk3PlanMagic = 0x534b3350;  // "SK3P"
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -52,6 +55,7 @@ struct Sk2Ctrl {
   float weight[kSk2MaxGroups];        // share of the tile stream per SM (0 everywhere: uniform)
   int32_t stat_tiles[kSk2MaxGroups];  // last launch: tiles the CTA on this SM streamed ...
   int32_t stat_cycles[kSk2MaxGroups]; // ... and the cycles it took
+  int32_t pool_next[2];               // cooperative stream-K: next pool unit to claim in the launch of parity 0 / 1
 };
 
 struct DecodeParams {
