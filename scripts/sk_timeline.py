@@ -71,6 +71,18 @@ for rep in range(launches):
     used = torch.zeros(int(smid.max()) + 1, dtype=torch.bool)
     used[smid] = True
     per_sm.append(end_by_sm)
+    # does an SM that got its first tiles late also end late? (per-SM mean of its warps' first landing vs its end)
+    fl_sum = torch.zeros(int(smid.max()) + 1).scatter_add_(0, smid, cols[1].float())
+    fl_cnt = torch.zeros(int(smid.max()) + 1).scatter_add_(0, smid, torch.ones(nw))
+    fl_by_sm = fl_sum / fl_cnt.clamp(min=1)
+    cc = torch.corrcoef(torch.stack([fl_by_sm[used], end_by_sm[used]]))[0, 1]
+    tiles_by_sm = torch.zeros(int(smid.max()) + 1).scatter_add_(0, smid, t[:, 5].float())
+    rate = tiles_by_sm[used] / (end_by_sm[used] - fl_by_sm[used]).clamp(min=1e-3)   # tiles / us after the first landing
+    print(json.dumps({"launch": rep, "corr_first_landed_vs_end_by_sm": round(float(cc), 3),
+                      "first_landed_by_sm_us": mmm(fl_by_sm[used]), "tiles_by_sm": mmm(tiles_by_sm[used]),
+                      "rate_after_first_landing_tiles_per_us": mmm(rate),
+                      "rate_rel_std": round(float(rate.std() / rate.mean()), 4),
+                      "end_std_us": round(float(end_by_sm[used].std()), 2)}), flush=True)
     print(json.dumps({"workload": wl_name, "variant": variant, "tp": tp, "launch": rep, "kv_bytes": inp.kv_bytes_per_layer,
                       "interleave": os.environ.get("B200ATTN_SK2_DEBUG_INTERLEAVE", "0"), "contiguous_blocks": contig,
                       "smid_max": int(smid.max()), "sms_used": int(used.sum()),

@@ -88,11 +88,11 @@ def test_workspace_bytes_formula(lib):
         return ctrl + sk_rows * 129 * 4 + (plan + 4) * 4 + 256
 
     # cooperative stream-K (default), behind the v2 region: partial rows (2 parities x 2 per segment, 16 segments per
-    # CTA) with their LSEs, then its plan (header 16 | team starts | segment desc + info 4 x segments each | cum)
+    # CTA) with their LSEs, then its plan (header 16 | team starts | segment desc + info 4 x segments each | 8 x warps start records | cum)
     def sk3(batch, hq):
         nw, nseg = 148 * 12, 148 * 16
         off = (sk2(batch, hq) + 255) // 256 * 256
-        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 8 * nseg + ((batch + 1 + 3) // 4 * 4)
+        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 8 * nseg + 8 * nw + ((batch + 1 + 3) // 4 * 4)
         return off + 2 * 2 * nseg * 8 * 129 * 4 + (plan + 4) * 4 + 256
 
     assert f(64, 32, 128, 8) == max(fixed, sk1(64), sk3(64, 32))

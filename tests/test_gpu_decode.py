@@ -509,7 +509,7 @@ def test_sk3_plan_contents(lib):
         seen_pool |= Ku > 0
         assert 0 <= Ku <= 8 and (Ku == 0 or pool > 0)
         tiles = [(s + 15) // 16 for s in lens]
-        assert plan["total"] == sum(tiles) * hs
+        assert plan["total"] == sum(tiles) * hs and plan["cum"][-1] == sum(tiles)
         ts = plan["tstart"]
         assert ts[0] == 0 and ts[nt] == plan["total"] and all(ts[i] <= ts[i + 1] for i in range(nt))
         sb = plan["seg_bounds"]

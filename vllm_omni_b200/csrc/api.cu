@@ -790,6 +790,12 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       }
       if ((flags & B200ATTN_DECODE_EARLY_KV_READ) && env_flag("B200ATTN_EARLY_KV_READ", true))
         p.flags |= kSk2FlagEarlyKvRead;
+      if (env_flag("B200ATTN_SK3_OWNER_FAST_ONLY", false)) p.flags |= kSk3FlagOwnerFastOnly;
+      {
+        const char* v = getenv("B200ATTN_SK3_L2PF");
+        const int x = (v == nullptr || *v == '\0') ? 4 : atoi(v);
+        p.l2_prefetch_tiles = x < 0 ? 0 : (x > 30 ? 30 : x);
+      }
       if ((g_sk2_parity ^= 1) != 0) p.flags |= kSk2FlagParity;  // consecutive launches alternate their control words
       e = launch_decode_sk3(tm_k, *mv, p, fp8, sms, pdl, stream);
     } else if (variant == B200ATTN_VARIANT_SK2) {

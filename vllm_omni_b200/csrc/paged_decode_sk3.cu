@@ -42,13 +42,15 @@ namespace b200 {
 // Segment index in stream order: seg = team * (1 + Ku) + j, j = 0 static, j = 1..Ku units.
 //
 // Plan layout (int32 words), G = CTAs of the grid, W = 12, NTmax = G * W teams, NSmax = kSk3SegPerCta * G segments:
-//   header[16] | tstart[NTmax + 1] | sdesc[NSmax][4] | sinfo[NSmax][4] | cum[batch + 1]
+//   header[16] | tstart[NTmax + 1] | sdesc[NSmax][4] | sinfo[NSmax][4] | wrec[G * W][8] | cum[batch + 1]
 //   header     {positions, G, T, NT = G * (W / T), batch, hs_count, Ku, magic, W / T, U, NS = NT * (1 + Ku)}
 //   tstart[c]  first stream position of team c (team c = CTA group c / (W/T), warps (c % (W/T)) * T ...)
 //   sdesc[s]   {sequence, head-group, tile, tiles of the sequence} at the start of segment s
 //   sinfo[s]   {owner segment of the item the segment's FIRST piece continues (-1: it starts an item),
 //               pieces of that item, segments that continue the segment's LAST item when the segment owns it
 //               and it is cut (0: not cut), 1 if those are exactly the next segments (no empty one between)}
+//   wrec[w]    per warp of the grid, what it needs to start on its team's static segment without a dependent
+//              load: {begin, end, sinfo.x, sinfo.y | sinfo.z << 15 | sinfo.w << 30} {sdesc of the segment}
 //   cum[b]     exclusive prefix of tiles per sequence
 // ------------------------------------------------------------------------------------------------
 __host__ __device__ __forceinline__ int64_t sk3_plan_tstart_off() { return kSk3PlanHdrInts; }
@@ -58,8 +60,11 @@ __host__ __device__ __forceinline__ int64_t sk3_plan_sdesc_off(int groups) {
 __host__ __device__ __forceinline__ int64_t sk3_plan_sinfo_off(int groups) {
   return sk3_plan_sdesc_off(groups) + 4ll * kSk3SegPerCta * groups;
 }
-__host__ __device__ __forceinline__ int64_t sk3_plan_cum_off(int groups) {
+__host__ __device__ __forceinline__ int64_t sk3_plan_wrec_off(int groups) {
   return sk3_plan_sdesc_off(groups) + 8ll * kSk3SegPerCta * groups;
+}
+__host__ __device__ __forceinline__ int64_t sk3_plan_cum_off(int groups) {
+  return sk3_plan_wrec_off(groups) + 8ll * kSk3Warps * groups;
 }
 
 size_t sk3_plan_ints(int batch, int groups) {
@@ -325,6 +330,17 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     sdesc[s] = d;
     sinfo[s] = info;
   }
+  __syncthreads();
+  // ---- phase 4: what every warp of the grid starts with
+  int4* wrec = reinterpret_cast<int4*>(plan + sk3_plan_wrec_off(groups));
+  for (int idx = tid; idx < groups * W; idx += 1024) {
+    const int c = (idx / W) * tpc + (idx % W) / T, s = c * (1 + Ku);
+    int t0, t1;
+    sk3_seg_range(sg, s, t0, t1);
+    const int4 info = sinfo[s];
+    wrec[2 * idx] = make_int4(t0, t1, info.x, info.y | (info.z << 15) | (info.w << 30));
+    wrec[2 * idx + 1] = sdesc[s];
+  }
 }
 
 cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, int32_t* plan, Sk2Ctrl* ctrl,
@@ -470,21 +486,38 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
   const bool fast = !whole && sm.word[a.tw0] == pieces - 1;
   float vs = 1.f;
   if (FP8) vs = __ldg(p.v_scale + kvh * p.scale_stride);
-  // fold the partial in `slot` (normalised row, log2-domain LSE) into a head's running merge
-  auto fold_slot = [&](Sk3Acc& s, int64_t slot, int h) {
-    const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane);
-    sk3_fold(s, o, 1.f, __ldcg(part_l + slot * kHeadsPerItem + h));
+  // The pieces of a cut item are always folded in the same order (the owner's, then the continuations by
+  // segment), each as its normalised row + log2-domain LSE, whoever does it and whether its own piece comes from
+  // registers or from its slot: the result does not depend on which team finished last.
+  struct Piece {
+    float4 o;
+    float l2;
   };
-  // ... and all partials of the item except this team's own piece when `skip_mine`
-  auto fold_others = [&](Sk3Acc& s, int h, bool skip_mine) {
-    if (!(skip_mine && owner)) fold_slot(s, nsmax + own, h);
-    if (owner && info.w) {
-      for (int j = own + 1; j <= own + info.z; ++j) fold_slot(s, j, h);
+  auto load_piece = [&](int64_t slot, int h) {
+    Piece q;
+    q.o = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane);
+    q.l2 = __ldcg(part_l + slot * kHeadsPerItem + h);
+    return q;
+  };
+  auto fold_item = [&](Sk3Acc& s, int h, bool have_mine, const Piece& mine) {
+    s.a = make_float4(0.f, 0.f, 0.f, 0.f);
+    s.l = 0.f;
+    s.m = -CUDART_INF_F;
+    {
+      const Piece q = (have_mine && owner) ? mine : load_piece(nsmax + own, h);
+      sk3_fold(s, q.o, 1.f, q.l2);
+    }
+    if (owner && info.w) {  // the continuations are exactly the next info.z segments
+      for (int j = own + 1; j <= own + info.z; ++j) {
+        const Piece q = load_piece(j, h);
+        sk3_fold(s, q.o, 1.f, q.l2);
+      }
       return;
     }
     for (int j = own + 1; j < sg.ns && sk3_seg_start(sg, j) < a.item_end; ++j) {
-      if ((skip_mine && j == seg) || !sk3_seg_nonempty(sg, j)) continue;
-      fold_slot(s, j, h);
+      if (!sk3_seg_nonempty(sg, j)) continue;
+      const Piece q = (have_mine && j == seg) ? mine : load_piece(j, h);
+      sk3_fold(s, q.o, 1.f, q.l2);
     }
   };
   auto write_row = [&](const Sk3Acc& s, int h) {
@@ -513,14 +546,22 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
                                                         h * kHeadDim + col);
       sk3_fold(s, v, sm.l[a.tw0 + k][h], mk);
     }
-    if (fast) fold_others(s, h, true);
-    if (whole || fast) {
+    if (whole) {
+      write_row(s, h);
+      continue;
+    }
+    Piece mine;  // this team's piece as it would sit in its slot
+    {
+      const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
+      mine.o = make_float4(s.a.x * inv, s.a.y * inv, s.a.z * inv, s.a.w * inv);
+      mine.l2 = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
+    }
+    if (fast) {
+      fold_item(s, h, true, mine);
       write_row(s, h);
     } else {
-      const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
-      *(reinterpret_cast<float4*>(part_o + (my_slot * kHeadsPerItem + h) * kHeadDim) + lane) =
-          make_float4(s.a.x * inv, s.a.y * inv, s.a.z * inv, s.a.w * inv);
-      if (lane == 0) part_l[my_slot * kHeadsPerItem + h] = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
+      *(reinterpret_cast<float4*>(part_o + (my_slot * kHeadsPerItem + h) * kHeadDim) + lane) = mine.o;
+      if (lane == 0) part_l[my_slot * kHeadsPerItem + h] = mine.l2;
     }
   }
   if (whole || fast) {
@@ -542,10 +583,10 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
   if (sm.word2[a.tw0] != pieces - 1) return;
   for (int h = a.wi; h < kHeadsPerItem; h += a.T) {
     Sk3Acc s;
-    s.a = make_float4(0.f, 0.f, 0.f, 0.f);
-    s.l = 0.f;
-    s.m = -CUDART_INF_F;
-    fold_others(s, h, false);
+    Piece none;
+    none.o = make_float4(0.f, 0.f, 0.f, 0.f);
+    none.l2 = 0.f;
+    fold_item(s, h, false, none);
     write_row(s, h);
   }
   if (a.wi == 0 && lane == 0) cnt[own] = 0;
@@ -557,8 +598,6 @@ template <int W, int D, int SB>
 __device__ __noinline__ void sk3_fetch_segment(const DecodeParams& p, Sk3Smem<W, D, SB>& sm, int tw0, int k) {
   const int groups = static_cast<int>(gridDim.x);
   const Sk3Segs sg = sk3_segs_of_plan(p.sk3_plan);
-  const int T = __ldg(p.sk3_plan + 2), tpc = __ldg(p.sk3_plan + 8);
-  const int team = sm.group * tpc + tw0 / T;
   int32_t* const pool_next = &p.sk2_ctrl->pool_next[(p.flags & kSk2FlagParity) ? 1 : 0];
   volatile int* qn = &sm.q_n[tw0];
   while (*qn <= k) {
@@ -571,11 +610,9 @@ __device__ __noinline__ void sk3_fetch_segment(const DecodeParams& p, Sk3Smem<W,
       e.seg = -1;
       e.begin = e.end = e.pad = 0;
       e.desc = e.info = make_int4(0, 0, 0, 0);
-      if (k == 0) {
-        e.seg = team * (1 + sg.Ku);
-      } else if (sm.q[tw0][(k - 1) & (kSk3QueueDepth - 1)].seg >= 0 || k == 1) {
+      if (sm.q[tw0][(k - 1) & (kSk3QueueDepth - 1)].seg >= 0) {  // (k >= 1: entry 0 is written by the kernel's prologue)
         const int claims = sg.nt * sg.Ku;
-        while (true) {
+        while (claims > 0) {
           const int c = atomicAdd(pool_next, 1);
           if (c >= claims) break;
           const int seg = (c % sg.nt) * (1 + sg.Ku) + 1 + c / sg.nt;  // round by round: every team's unit 1, then 2, ...
@@ -635,10 +672,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     sm.group = g;
     sm.tiles_done = 0;
   }
-  if (lane == 0) {
-    sm.q_n[warp] = 0;
-    sm.q_lock[warp] = 0;
-  }
+  if (lane == 0) sm.q_lock[warp] = 0;
   bool waited = false;
   auto wait_for_prior = [&]() {
     griddep_wait();
@@ -646,9 +680,13 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     if (threadIdx.x == 0) sm.t0 = clock64();
   };
   if (p.flags & kSk2FlagWaitFirst) wait_for_prior();  // the plan was written by the kernel right before this one
+  // one round of independent loads, for the group the CTA will almost always get (its own SM's)
   const int32_t* plan = p.sk3_plan;
   const int4 hdr = __ldg(reinterpret_cast<const int4*>(plan));
   const int4 hdr2 = __ldg(reinterpret_cast<const int4*>(plan) + 1);
+  const int g_spec = static_cast<int>(smid % static_cast<uint32_t>(G));
+  const int4* wrec = reinterpret_cast<const int4*>(plan + sk3_plan_wrec_off(G));
+  int4 wa = __ldg(wrec + 2 * (g_spec * W + warp)), wb = __ldg(wrec + 2 * (g_spec * W + warp) + 1);
   const int T = hdr.z;
   const int32_t* cum = plan + sk3_plan_cum_off(G);
   if (lane == 0) {
@@ -660,6 +698,22 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       tma_prefetch_desc(&tm_v);
     }
   }
+  // the team's first segment is its own static one (every warp of the team writes the same words)
+  auto write_first_entry = [&](int g) {
+    if (lane == 0) {
+      const int tw = warp - warp % T;
+      Sk3QEntry e;
+      e.seg = (g * (W / T) + warp / T) * (1 + hdr2.z);
+      e.begin = wa.x;
+      e.end = wa.y;
+      e.pad = 0;
+      e.desc = wb;
+      e.info = make_int4(wa.z, wa.w & 0x7fff, (wa.w >> 15) & 0x7fff, (wa.w >> 30) & 1);
+      sm.q[tw][0] = e;
+      sm.q_n[tw] = 1;
+    }
+  };
+  write_first_entry(g_spec);
   __syncthreads();
   const int group = sm.group;
   const int hs_count = p.num_kv_heads * p.subgroups;
@@ -668,6 +722,12 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     __trap();  // the plan in the workspace was made for another launch shape: fail loudly
   const int wi = warp % T, tw0 = warp - wi;
   const int gw = group * W + warp;
+  if (group != g_spec) {  // rare: this CTA runs another SM's group
+    wa = __ldg(wrec + 2 * gw);
+    wb = __ldg(wrec + 2 * gw + 1);
+    write_first_entry(group);
+    __syncthreads();
+  }
   if (p.trace != nullptr && lane == 0) {  // debug: entry stamp, SM id
     p.trace[gw * 8 + 0] = sk3_globaltimer();
     p.trace[gw * 8 + 4] = smid;
@@ -800,6 +860,23 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       if (--pf_left > 0) pf_fresh = sk3_advance(cum, p.batch, hs_count, T, pf);
     }
     if (q_deferred) {  // the first stages are in flight: now wait for the previous kernel and fetch q
+      if (early && p.l2_prefetch_tiles > 0) {
+        // ... but first ask for this warp's next tiles of the item as far as L2 (lane l holds the block id of the
+        // tile l steps behind the window base): the time an early CTA spends waiting for the stragglers of the
+        // previous kernel is HBM time nobody else uses
+        const int k = pf_kbase + lane - pf_k;  // steps ahead of the front
+        const int tile = pf_t0 + T * (pf_kbase + lane);
+        if (k >= 0 && k < p.l2_prefetch_tiles && k < pf_left && tile + 1 < pf.n) {
+          const int slot0 = (tile & p.tpp_mask) * kTileTokens;
+          if (FP8) {
+            tma_prefetch_l2_4d(&tm_k, 0, slot0, pf_kvh, ids);
+            tma_prefetch_l2_4d(&tm_v, 0, slot0, pf_kvh, ids);
+          } else {
+            tma_prefetch_l2_5d(&tm_k, 0, slot0, 0, pf_kvh, ids);
+            tma_prefetch_l2_5d(&tm_v, 0, slot0, 0, pf_kvh, ids);
+          }
+        }
+      }
       wait_for_prior();
       load_q_next();
       q_deferred = false;
@@ -826,8 +903,10 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       // register before the merge needs it)
       if (peek < 0 && wi == 0 && mp + 3 * T >= piece_end) {
         const int32_t* cnt = p.sk3_cnt + ((p.flags & kSk2FlagParity) ? kSk3SegPerCta * G : 0);
-        if (piece_begin > item_pos0)
-          peek = sk3_ld_relaxed(cnt + sm.q[tw0][qidx].info.x) & 0x7fffffff;  // the piece continues an item
+        if (piece_begin > item_pos0) {
+          if (!(p.flags & kSk3FlagOwnerFastOnly))
+            peek = sk3_ld_relaxed(cnt + sm.q[tw0][qidx].info.x) & 0x7fffffff;  // the piece continues an item
+        }
         else if (item_end > t_end)
           peek = sk3_ld_relaxed(cnt + sm.q[tw0][qidx].seg) & 0x7fffffff;     // it owns a cut item
       }
@@ -835,7 +914,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       int ds = cslot;
       if (mp < piece_end) {
         if (!have_item) {  // take the item the front prepared
-          cp_async_wait<0>();
+          cp_async_wait_all();  // this lane's own words (nobody else reads them)
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk)
 #pragma unroll

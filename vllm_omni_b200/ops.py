@@ -281,7 +281,8 @@ def debug_sk3_plan(workspace: DecodeWorkspace, batch: int, num_q_heads: int) -> 
         raise RuntimeError("no cooperative stream-K plan in this workspace")
     ntmax, nsmax = groups * 12, groups * 16
     o_desc = 16 + ((ntmax + 1 + 3) & ~3)
-    w = words[:o_desc + 8 * nsmax + batch + 1].cpu()
+    o_cum = o_desc + 8 * nsmax + 8 * ntmax   # behind the per-warp start records
+    w = words[:o_cum + batch + 1].cpu()
     tstart = w[16:16 + nt + 1].tolist()
     bounds = []
     for s_ in range(ns):
@@ -293,7 +294,7 @@ def debug_sk3_plan(workspace: DecodeWorkspace, batch: int, num_q_heads: int) -> 
             "Ku": Ku, "U": U, "ns": ns, "tstart": tstart, "seg_bounds": bounds,
             "sdesc": w[o_desc:o_desc + 4 * ns].view(ns, 4).tolist(),
             "sinfo": w[o_desc + 4 * nsmax:o_desc + 4 * nsmax + 4 * ns].view(ns, 4).tolist(),
-            "cum": w[o_desc + 8 * nsmax:o_desc + 8 * nsmax + batch + 1].tolist()}
+            "cum": w[o_cum:o_cum + batch + 1].tolist()}
 
 
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
