@@ -397,16 +397,10 @@ B200ATTN_API void b200attn_debug_set_trace(void* device_buffer);
  */
 B200ATTN_API void b200attn_debug_set_team(int32_t warps);
 
-/* Debug / test aid: share (percent, 0..90) of every team's range that the next cooperative stream-K plans of
- * this thread cut into pool units (claimed at run time by whichever team is free); -1 restores the default
- * (B200ATTN_SK3_POOL or 14). 0 = fully static schedule. */
-B200ATTN_API void b200attn_debug_set_pool(int32_t percent);
-
 /* Byte offset, inside a decode workspace, of the plan b200attn_decode_plan writes for (batch, num_q_heads)
  * on the current device (int32 words: header 16 {positions, CTAs G, team size T, teams, batch, head groups,
- * pool units per team Ku, magic, teams per CTA, unit size U, segments} | team starts [12 G + 1, padded to 4] |
- * segment descriptors [16 G][4] | segment info [16 G][4] | tiles prefix [batch + 1]); tests read the plan back
- * through it (vllm_omni_b200/ops.py debug_sk3_plan). */
+ * 0, magic, teams per CTA} | team starts [12 G + 1, padded to 4] | team descriptors [12 G][4] | team info
+ * [12 G][4] | warp descriptors [12 G][4] | tiles prefix [batch + 1]); tests read the plan back through it. */
 B200ATTN_API size_t b200attn_debug_plan_offset(int32_t batch, int32_t num_q_heads);
 
 /*

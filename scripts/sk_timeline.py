@@ -78,6 +78,7 @@ for rep in range(launches):
     cc = torch.corrcoef(torch.stack([fl_by_sm[used], end_by_sm[used]]))[0, 1]
     tiles_by_sm = torch.zeros(int(smid.max()) + 1).scatter_add_(0, smid, t[:, 5].float())
     rate = tiles_by_sm[used] / (end_by_sm[used] - fl_by_sm[used]).clamp(min=1e-3)   # tiles / us after the first landing
+    rate = rate if float(rate.sum()) > 0 else torch.ones_like(rate)                  # (kernels that do not count tiles)
     print(json.dumps({"launch": rep, "corr_first_landed_vs_end_by_sm": round(float(cc), 3),
                       "first_landed_by_sm_us": mmm(fl_by_sm[used]), "tiles_by_sm": mmm(tiles_by_sm[used]),
                       "rate_after_first_landing_tiles_per_us": mmm(rate),

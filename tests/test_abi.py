@@ -70,8 +70,8 @@ def test_workspace_bytes_formula(lib):
     f = lib.b200attn_decode_workspace_bytes
     assert f(0, 32, 128, 4) == 0
     # max over the schedules; without a GPU the stream-K parts assume 148 SMs x 12 warps.
-    # Every layout starts with a 128 KiB control area; then partial O rows and partial LSEs.
-    ctrl = 131072
+    # Every layout starts with a 64 KiB control area; then partial O rows and partial LSEs.
+    ctrl = 65536
     rows = 64 * 32 * 8
     fixed = ctrl + rows * 128 * 4 + rows * 4 + 256
     # stream-K v1: two partial slots per chunk (one chunk per warp, +1), then the tiles-prefix plan
@@ -87,13 +87,13 @@ def test_workspace_bytes_formula(lib):
         plan = 16 + ((nw + 1 + 3) // 4 * 4) + 36 * nw + ((batch + 1 + 3) // 4 * 4) + 2 * batch * hq
         return ctrl + sk_rows * 129 * 4 + (plan + 4) * 4 + 256
 
-    # cooperative stream-K (default), behind the v2 region: partial rows (2 parities x 2 per segment, 16 segments per
-    # CTA) with their LSEs, then its plan (header 16 | team starts | segment desc + info 4 x segments each | 8 x warps start records | cum)
+    # cooperative stream-K (default), behind the v2 region: partial rows (2 parities x 2 per team, teams <= warps)
+    # with their LSEs, then its plan (header 16 | team starts | team desc, team info, warp desc 4 x warps each | cum)
     def sk3(batch, hq):
-        nw, nseg = 148 * 12, 148 * 16
+        nw = 148 * 12
         off = (sk2(batch, hq) + 255) // 256 * 256
-        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 8 * nseg + 8 * nw + ((batch + 1 + 3) // 4 * 4)
-        return off + 2 * 2 * nseg * 8 * 129 * 4 + (plan + 4) * 4 + 256
+        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 12 * nw + ((batch + 1 + 3) // 4 * 4)
+        return off + 2 * 2 * nw * 8 * 129 * 4 + (plan + 4) * 4 + 256
 
     assert f(64, 32, 128, 8) == max(fixed, sk1(64), sk3(64, 32))
     assert f(1, 8, 128, 1) == sk3(1, 8)

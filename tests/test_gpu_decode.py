@@ -455,14 +455,13 @@ def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8, variant):
 
 
 # ------------------------------------------------------------------------------------------------
-# Cooperative stream-K (the default): teams of T warps share an item, the tail of every team range is a pool of
-# units claimed at run time. Every team size and pool share must give the oracle's result on shapes that put whole items, cut items (two pieces, many pieces), items shorter
+# Cooperative stream-K (the default): teams of T warps share an item. Every team size must give the
+# oracle's result on shapes that put whole items, cut items (two pieces, many pieces), items shorter
 # than a team, empty sequences and head sub-groups in one launch.
 # ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("team,pool", [(0, -1), (1, -1), (2, 14), (3, 40), (4, 14), (6, 25), (12, 14), (12, 0), (12, 60),
-                                       (4, 0), (1, 50)])
+@pytest.mark.parametrize("team", [0, 1, 2, 3, 4, 6, 12])
 @pytest.mark.parametrize("fp8", [False, True])
-def test_sk3_team_sizes(lib, team, pool, fp8):
+def test_sk3_team_sizes(lib, team, fp8):
     cases = [
         make_case([4096, 1, 16, 17, 2049, 800, 4095, 33, 0, 5], hq=16, hkv=2, seed=300 + team, fp8=fp8),
         make_case([20000], hq=8, hkv=1, seed=310 + team, fp8=fp8),
@@ -470,10 +469,7 @@ def test_sk3_team_sizes(lib, team, pool, fp8):
     ]
     g = torch.Generator().manual_seed(team)
     cases.append(make_case(torch.randint(0, 200, (700,), generator=g).tolist(), hq=8, hkv=2, seed=330 + team, fp8=fp8))
-    # enough positions (12.9k) for the pool to exist at the default share
-    cases.append(make_case([40000, 30000, 25000, 8000], hq=16, hkv=2, seed=340 + team, fp8=fp8))
     lib.b200attn_debug_set_team(team)
-    lib.b200attn_debug_set_pool(pool)
     try:
         for c in cases:
             for _ in range(2):
@@ -481,59 +477,47 @@ def test_sk3_team_sizes(lib, team, pool, fp8):
                 check(c, out, lse)
     finally:
         lib.b200attn_debug_set_team(0)
-        lib.b200attn_debug_set_pool(-1)
 
 
 def test_sk3_plan_contents(lib):
-    """The plan the decode kernel follows: segments (team ranges + pool units) tile the stream, descriptors point
-    at their starts, and the owner / continuation bookkeeping of cut items is consistent (every continuation names
-    the segment that holds the item's start, whose count of continuing segments includes it)."""
-    lens = [40960, 1, 16, 17, 20490, 8000, 40950, 33, 0, 5]
+    """The plan the decode kernel follows: team ranges tile the stream, descriptors point at their starts, and the
+    owner / continuation bookkeeping of cut items is consistent (every continuation names an owner whose count of
+    continuing teams includes it)."""
+    lens = [4096, 1, 16, 17, 2049, 800, 4095, 33, 0, 5]
     B, hq, hkv = len(lens), 16, 2
-    seq_lens = torch.tensor(lens, dtype=torch.int32, device="cuda")
-    block_table = torch.zeros(B, (max(lens) + 15) // 16, dtype=torch.int32, device="cuda")  # contents are not read here
+    c = make_case(lens, hq=hq, hkv=hkv, seed=1)
     ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(B, hq, 128, 1))
-    seen_pool = False
-    for team, pool in ((12, 0), (12, 14), (12, 50), (4, 14), (1, 30), (6, 90)):
+    for team in (12, 4, 1):
         lib.b200attn_debug_set_team(team)
-        lib.b200attn_debug_set_pool(pool)
         try:
-            ops.decode_plan(seq_lens, block_table, B, hq, hkv, 16, ws)
+            ops.decode_plan(c.seq_lens.cuda(), c.block_table.cuda(), B, hq, hkv, 16, ws)
         finally:
             lib.b200attn_debug_set_team(0)
-            lib.b200attn_debug_set_pool(-1)
         torch.cuda.synchronize()
         plan = ops.debug_sk3_plan(ws, B, hq)
-        G, T, nt, hs, Ku, ns = plan["groups"], plan["T"], plan["nt"], plan["hs_count"], plan["Ku"], plan["ns"]
-        assert T == team and nt == G * (12 // T) and hs == hkv and ns == nt * (1 + Ku) and ns <= 16 * G
-        seen_pool |= Ku > 0
-        assert 0 <= Ku <= 8 and (Ku == 0 or pool > 0)
+        G, T, nt, hs = plan["groups"], plan["T"], plan["nt"], plan["hs_count"]
+        assert T == team and nt == G * (12 // T) and hs == hkv
         tiles = [(s + 15) // 16 for s in lens]
-        assert plan["total"] == sum(tiles) * hs and plan["cum"][-1] == sum(tiles)
+        assert plan["total"] == sum(tiles) * hs
         ts = plan["tstart"]
         assert ts[0] == 0 and ts[nt] == plan["total"] and all(ts[i] <= ts[i + 1] for i in range(nt))
-        sb = plan["seg_bounds"]
-        assert sb[0][0] == 0 and sb[-1][1] == plan["total"]
-        assert all(sb[i][1] == sb[i + 1][0] for i in range(ns - 1)) and all(b0 <= b1 for b0, b1 in sb)
-        # stream position -> (b, hs, tile, n)
+        # stream position -> (b, hs, tile)
         pos = []
         for b, n in enumerate(tiles):
             for h in range(hs):
                 pos += [(b, h, t, n) for t in range(n)]
+        for i in range(nt):
+            if ts[i] < ts[i + 1]:
+                assert tuple(plan["tdesc"][i]) == pos[ts[i]]
         conts = {}
-        for i in range(ns):
-            own, np_first, m_last, contig = plan["sinfo"][i]
-            b0, b1 = sb[i]
-            if b0 < b1:
-                assert tuple(plan["sdesc"][i]) == pos[b0]
-            if b0 < b1 and pos[b0][2] > 0:
-                assert 0 <= own < i and sb[own][0] <= b0 - pos[b0][2] < sb[own][1]
+        for i in range(nt):
+            own, np_first, m_last, contig = plan["tinfo"][i]
+            if ts[i] < ts[i + 1] and pos[ts[i]][2] > 0:
+                assert own >= 0 and own < i
                 conts.setdefault(own, []).append(i)
                 assert np_first >= 2
             else:
                 assert own == -1
         for own, lst in conts.items():
-            assert plan["sinfo"][own][2] == len(lst), (own, lst, plan["sinfo"][own])
-            assert all(plan["sinfo"][i][1] == len(lst) + 1 for i in lst)
-            assert plan["sinfo"][own][3] == (1 if lst == list(range(own + 1, own + 1 + len(lst))) else 0)
-    assert seen_pool
+            assert plan["tinfo"][own][2] == len(lst), (own, lst, plan["tinfo"][own])
+            assert plan["tinfo"][lst[0]][1] == len(lst) + 1

@@ -247,11 +247,11 @@ int check_cache_args(const void* k_cache, const void* v_cache, int64_t sb, int64
 // it are left at zero by every kernel: [0, 256) stream-K v1 words, [256, ...) Sk2Ctrl of stream-K v2
 // (arrival counters, chunk-group claims, per-SM rates and weights). No variant writes anything else here,
 // so one workspace can serve different variants in turn.
-constexpr size_t kWsCtrlBytes = 131072;
-constexpr size_t kWsSk3CntOff = 16384;  // cooperative stream-K arrival counters [2 parities][segments <= 512 * 16]
+constexpr size_t kWsCtrlBytes = 65536;
+constexpr size_t kWsSk3CntOff = 16384;  // cooperative stream-K arrival counters [2 parities][teams <= 512 * 12]
 constexpr size_t kWsSk2CtrlOff = 256;
 static_assert(kWsSk2CtrlOff + sizeof(Sk2Ctrl) <= kWsSk3CntOff, "control area too small for Sk2Ctrl");
-static_assert(kWsSk3CntOff + 2ull * kSk2MaxGroups * kSk3SegPerCta * sizeof(int32_t) <= kWsCtrlBytes,
+static_assert(kWsSk3CntOff + 2ull * kSk2MaxGroups * kSk3Warps * sizeof(int32_t) <= kWsCtrlBytes,
               "control area too small for the cooperative stream-K arrival counters");
 size_t fixed_workspace_bytes(int batch, int num_q_heads, int head_size, int splits) {
   const size_t rows = static_cast<size_t>(batch) * num_q_heads * splits;
@@ -319,7 +319,7 @@ Sk2Layout sk2_layout(void* workspace, int sms) {
 }
 
 // cooperative stream-K (paged_decode_sk3.cu) region, behind the stream-K v2 region:
-// [partial rows: 2 parities x 2 * segments x 8 x 128 f32 | their LSEs | plan]
+// [partial rows: 2 parities x 2 * teams x 8 x 128 f32 | their LSEs | plan]
 struct Sk3Layout {
   float *part_o, *part_lse;
   int32_t *plan, *cnt;
@@ -327,7 +327,7 @@ struct Sk3Layout {
 size_t sk3_region_off(int batch, int num_q_heads, int sms) {
   return (sk2_workspace_bytes(batch, num_q_heads, sms) + 255) & ~static_cast<size_t>(255);
 }
-size_t sk3_slot_rows(int sms) { return 2ull * 2ull * sms * kSk3SegPerCta * kHeadsPerItem; }
+size_t sk3_slot_rows(int sms) { return 2ull * 2ull * sms * decode_sk3_warps() * kHeadsPerItem; }
 size_t sk3_workspace_bytes(int batch, int num_q_heads, int sms) {
   return sk3_region_off(batch, num_q_heads, sms) + sk3_slot_rows(sms) * (kHeadDim + 1) * sizeof(float) +
          (sk3_plan_ints(batch, sms) + 4) * sizeof(int32_t) + 256;
@@ -340,13 +340,6 @@ Sk3Layout sk3_layout(void* workspace, int batch, int num_q_heads, int sms) {
   l.part_lse = l.part_o + sk3_slot_rows(sms) * kHeadDim;
   l.plan = reinterpret_cast<int32_t*>(l.part_lse + sk3_slot_rows(sms));
   return l;
-}
-thread_local int g_sk3_pool = -1;  // debug: forced pool share in percent (-1 = environment / default)
-int sk3_pool_pct() {
-  if (g_sk3_pool >= 0) return g_sk3_pool;
-  const char* v = getenv("B200ATTN_SK3_POOL");
-  const int x = (v == nullptr || *v == '\0') ? kSk3PoolPctDefault : atoi(v);
-  return x < 0 ? 0 : (x > 90 ? 90 : x);
 }
 thread_local int g_sk3_team = 0;  // debug: forced team size (0 = the plan kernel's rule)
 int sk3_team_force() {
@@ -784,18 +777,12 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       if (!(flags & B200ATTN_DECODE_PLANNED)) {
         // no plan of this step in the workspace: make it now; the decode kernel then waits for it first
         if (cudaError_t pe = launch_sk3_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms, sk3.plan, sk2.ctrl,
-                                             sk3_calib_max(), sk3_team_force(), sk3_pool_pct(), stream))
+                                             sk3_calib_max(), sk3_team_force(), stream))
           return cuda_fail(pe, "decode plan launch");
         p.flags |= kSk2FlagWaitFirst;
       }
       if ((flags & B200ATTN_DECODE_EARLY_KV_READ) && env_flag("B200ATTN_EARLY_KV_READ", true))
         p.flags |= kSk2FlagEarlyKvRead;
-      if (env_flag("B200ATTN_SK3_OWNER_FAST_ONLY", false)) p.flags |= kSk3FlagOwnerFastOnly;
-      {
-        const char* v = getenv("B200ATTN_SK3_L2PF");
-        const int x = (v == nullptr || *v == '\0') ? 4 : atoi(v);
-        p.l2_prefetch_tiles = x < 0 ? 0 : (x > 30 ? 30 : x);
-      }
       if ((g_sk2_parity ^= 1) != 0) p.flags |= kSk2FlagParity;  // consecutive launches alternate their control words
       e = launch_decode_sk3(tm_k, *mv, p, fp8, sms, pdl, stream);
     } else if (variant == B200ATTN_VARIANT_SK2) {
@@ -930,7 +917,7 @@ int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_h
   if (sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes) {
     const Sk3Layout l3 = sk3_layout(workspace, batch, num_q_heads, sms);
     if (cudaError_t e3 = launch_sk3_plan(seq_lens, batch, num_kv_heads * subgroups, sms, l3.plan, l.ctrl, sk3_calib_max(),
-                                         sk3_team_force(), sk3_pool_pct(), static_cast<cudaStream_t>(stream)))
+                                         sk3_team_force(), static_cast<cudaStream_t>(stream)))
       return cuda_fail(e3, "decode plan launch");
   }
   cudaError_t e = launch_sk2_plan(seq_lens, batch, num_kv_heads * subgroups, sms, block_table, block_table_stride, tpp,
@@ -956,7 +943,6 @@ void b200attn_debug_sk_schedule(int64_t total_tiles, int32_t num_warps, int32_t 
 
 void b200attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<unsigned long long*>(device_buffer); }
 void b200attn_debug_set_team(int32_t warps) { g_sk3_team = warps; }
-void b200attn_debug_set_pool(int32_t percent) { g_sk3_pool = percent; }
 size_t b200attn_debug_plan_offset(int32_t batch, int32_t num_q_heads) {
   int sms = cached_num_sms();
   if (sms <= 0) sms = 148;

@@ -29,7 +29,6 @@ constexpr int kSk2PlanMagic = 0x534b3250;  // "SK2P"
 constexpr int kSk2FlagWaitFirst = 1;    // griddepcontrol.wait before the plan is read (plan made by the previous kernel)
 constexpr int kSk2FlagEarlyKvRead = 2;  // KV tiles other than a sequence's last may be loaded before the wait
 constexpr int kSk2FlagParity = 8;        // launch parity: consecutive launches on a stream alternate their claim words
-constexpr int kSk3FlagOwnerFastOnly = 16;  // debug: only the owner of a cut item may take the no-atomic path
 constexpr int kSk2MaxGroups = 512;      // CTAs of the persistent grid (= SMs) the control area has room for
 constexpr int kSk2CalibMinTiles = 96;   // an SM's rate is only trusted if it streamed at least this many tiles
 constexpr float kSk2CalibGain = 0.7f;   // share of the measured rate in a weight update
@@ -39,9 +38,6 @@ constexpr float kSk3CalibGainLate = 0.4f;   // cooperative stream-K: weight-upda
 constexpr int kSk3CalibUpdatesDefault = 24; // ... and the number of updates before the weights are frozen (B200ATTN_SK3_CALIB)
 constexpr int kSk3Warps = 12;            // cooperative stream-K (paged_decode_sk3.cu): warps per CTA
 constexpr int kSk3PlanHdrInts = 16;
-constexpr int kSk3SegPerCta = 16;       // segments (team ranges + pool units) per CTA the plan and the slots have room for
-constexpr int kSk3MaxUnits = 8;         // pool units per team at most
-constexpr int kSk3PoolPctDefault = 0;   // share of a team range that is cut into pool units (B200ATTN_SK3_POOL); off by default, see profiles/README.md
 constexpr int kSk3PlanMagic = 0x534b3350;  // "SK3P"
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -56,7 +52,6 @@ struct Sk2Ctrl {
   float weight[kSk2MaxGroups];        // share of the tile stream per SM (0 everywhere: uniform)
   int32_t stat_tiles[kSk2MaxGroups];  // last launch: tiles the CTA on this SM streamed ...
   int32_t stat_cycles[kSk2MaxGroups]; // ... and the cycles it took
-  int32_t pool_next[2];               // cooperative stream-K: next pool unit to claim in the launch of parity 0 / 1
 };
 
 struct DecodeParams {
@@ -101,7 +96,6 @@ struct DecodeParams {
   float* sk3_part_o;
   float* sk3_part_lse;
   int32_t* sk3_cnt;
-  int32_t l2_prefetch_tiles;  // tiles per warp brought to L2 behind the ring while the kernel waits for its predecessor
 };
 
 // Stream-K schedule, computed identically by the decode and the reduce kernel from the tile total:

@@ -36,13 +36,12 @@ size_t sk2_plan_ints(int batch, int nw, int hs_count);
 cudaError_t launch_sk2_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream);
 // cooperative stream-K (paged_decode_sk3.cu): teams of warps share an item, merges in shared memory, no reduce launch
 cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, int32_t* plan, Sk2Ctrl* ctrl,
-                            int calib_max, int team_force, int pool_pct, cudaStream_t stream);
+                            int calib_max, int team_force, cudaStream_t stream);
 cudaError_t launch_decode_sk3(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, bool fp8,
                               int grid, bool pdl, cudaStream_t stream);
 size_t decode_sk3_smem_bytes(bool fp8);
 size_t sk3_plan_ints(int batch, int groups);
 int decode_sk3_warps();
-int decode_sk3_seg_per_cta();
 size_t decode_tma_smem_bytes();
 size_t decode_cpasync_smem_bytes();
 

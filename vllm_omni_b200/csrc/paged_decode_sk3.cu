@@ -33,75 +33,27 @@
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------------
-// Segments. A team's range [s, e) is one STATIC segment followed by Ku UNIT segments of U positions at its
-// end (the "pool": 1/7 of the stream or so). A team works through its own static segment, then claims unit
-// segments — anybody's — from a global counter until none is left: SMs do not stream at equal rates and the
-// residue after calibration is per-launch noise (profiles/README.md), so the last part of the stream goes to
-// whoever is free. Units are claimed round by round (every team's first unit, then every team's second, ...):
-// the pieces of one cut item are claimed a round apart, so its last piece usually finds the others complete.
-// Segment index in stream order: seg = team * (1 + Ku) + j, j = 0 static, j = 1..Ku units.
-//
-// Plan layout (int32 words), G = CTAs of the grid, W = 12, NTmax = G * W teams, NSmax = kSk3SegPerCta * G segments:
-//   header[16] | tstart[NTmax + 1] | sdesc[NSmax][4] | sinfo[NSmax][4] | wrec[G * W][8] | cum[batch + 1]
-//   header     {positions, G, T, NT = G * (W / T), batch, hs_count, Ku, magic, W / T, U, NS = NT * (1 + Ku)}
+// Plan layout (int32 words), G = CTAs of the grid, W = 12, NTmax = G * W teams at most:
+//   header[16] | tstart[NTmax + 1] | tdesc[NTmax][4] | tinfo[NTmax][4] | wdesc[G * W][4] | cum[batch + 1]
+//   header     {positions, G, T, NT = G * (W / T), batch, hs_count, tpp_shift, magic, W / T}
 //   tstart[c]  first stream position of team c (team c = CTA group c / (W/T), warps (c % (W/T)) * T ...)
-//   sdesc[s]   {sequence, head-group, tile, tiles of the sequence} at the start of segment s
-//   sinfo[s]   {owner segment of the item the segment's FIRST piece continues (-1: it starts an item),
-//               pieces of that item, segments that continue the segment's LAST item when the segment owns it
-//               and it is cut (0: not cut), 1 if those are exactly the next segments (no empty one between)}
-//   wrec[w]    per warp of the grid, what it needs to start on its team's static segment without a dependent
-//              load: {begin, end, sinfo.x, sinfo.y | sinfo.z << 15 | sinfo.w << 30} {sdesc of the segment}
+//   tdesc[c]   {sequence, head-group, tile, tiles of the sequence} at tstart[c]
+//   tinfo[c]   {owner team of the item the team's FIRST piece continues (-1: the range starts an item),
+//               pieces of that item, teams that continue the team's LAST item when the team owns it and
+//               it is cut (0: not cut), 1 if those are exactly the next teams (no empty team between)}
+//   wdesc[w]   tdesc of the first position of warp w of the grid (sequence = batch: the warp has none)
 //   cum[b]     exclusive prefix of tiles per sequence
 // ------------------------------------------------------------------------------------------------
 __host__ __device__ __forceinline__ int64_t sk3_plan_tstart_off() { return kSk3PlanHdrInts; }
-__host__ __device__ __forceinline__ int64_t sk3_plan_sdesc_off(int groups) {
-  return kSk3PlanHdrInts + ((groups * kSk3Warps + 1 + 3) & ~3);
-}
-__host__ __device__ __forceinline__ int64_t sk3_plan_sinfo_off(int groups) {
-  return sk3_plan_sdesc_off(groups) + 4ll * kSk3SegPerCta * groups;
-}
-__host__ __device__ __forceinline__ int64_t sk3_plan_wrec_off(int groups) {
-  return sk3_plan_sdesc_off(groups) + 8ll * kSk3SegPerCta * groups;
-}
-__host__ __device__ __forceinline__ int64_t sk3_plan_cum_off(int groups) {
-  return sk3_plan_wrec_off(groups) + 8ll * kSk3Warps * groups;
-}
+__host__ __device__ __forceinline__ int64_t sk3_plan_tdesc_off(int ntmax) { return kSk3PlanHdrInts + ((ntmax + 1 + 3) & ~3); }
+__host__ __device__ __forceinline__ int64_t sk3_plan_tinfo_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 4ll * ntmax; }
+__host__ __device__ __forceinline__ int64_t sk3_plan_wdesc_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 8ll * ntmax; }
+__host__ __device__ __forceinline__ int64_t sk3_plan_cum_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 12ll * ntmax; }
 
 size_t sk3_plan_ints(int batch, int groups) {
-  return static_cast<size_t>(sk3_plan_cum_off(groups)) + ((static_cast<size_t>(batch) + 1 + 3) & ~size_t(3));
+  return static_cast<size_t>(sk3_plan_cum_off(groups * kSk3Warps)) + ((static_cast<size_t>(batch) + 1 + 3) & ~size_t(3));
 }
 int decode_sk3_warps() { return kSk3Warps; }
-int decode_sk3_seg_per_cta() { return kSk3SegPerCta; }
-
-// segment j of a team range [s, e): the units are cut from the end
-__host__ __device__ __forceinline__ void sk3_seg_bounds(int s, int e, int Ku, int U, int j, int& b0, int& b1) {
-  const int lo = e - (Ku - j + 1) * U, hi = e - (Ku - j) * U;
-  b0 = j == 0 ? s : (lo > s ? lo : s);
-  b1 = hi > s ? hi : s;
-}
-
-struct Sk3Segs {  // what is needed to place a segment
-  const int32_t* tstart;
-  int nt, Ku, U, ns, total;
-};
-__device__ __forceinline__ Sk3Segs sk3_segs_of_plan(const int32_t* plan) {  // header words, see the layout above
-  return Sk3Segs{plan + sk3_plan_tstart_off(), __ldg(plan + 3), __ldg(plan + 6), __ldg(plan + 9), __ldg(plan + 10), __ldg(plan)};
-}
-__device__ __forceinline__ void sk3_seg_range(const Sk3Segs& g, int seg, int& b0, int& b1) {
-  const int c = seg / (1 + g.Ku), j = seg - c * (1 + g.Ku);
-  sk3_seg_bounds(g.tstart[c], g.tstart[c + 1], g.Ku, g.U, j, b0, b1);
-}
-__device__ __forceinline__ int sk3_seg_start(const Sk3Segs& g, int seg) {
-  if (seg >= g.ns) return g.total;
-  int b0, b1;
-  sk3_seg_range(g, seg, b0, b1);
-  return b0;
-}
-__device__ __forceinline__ bool sk3_seg_nonempty(const Sk3Segs& g, int seg) {
-  int b0, b1;
-  sk3_seg_range(g, seg, b0, b1);
-  return b1 > b0;
-}
 
 // team that holds stream position t: the last c in [0, nt) with tstart[c] <= t
 __device__ __forceinline__ int sk3_team_of(const int32_t* tstart, int nt, int t) {
@@ -111,17 +63,6 @@ __device__ __forceinline__ int sk3_team_of(const int32_t* tstart, int nt, int t)
     if (tstart[mid] <= t) lo = mid; else hi = mid;
   }
   return lo;
-}
-// segment that holds stream position t (the last one that starts at or before t)
-__device__ __forceinline__ int sk3_seg_of(const Sk3Segs& g, int t) {
-  const int c = sk3_team_of(g.tstart, g.nt, t);
-  int j = g.Ku;
-  for (; j > 0; --j) {
-    int b0, b1;
-    sk3_seg_bounds(g.tstart[c], g.tstart[c + 1], g.Ku, g.U, j, b0, b1);
-    if (b0 <= t) break;
-  }
-  return c * (1 + g.Ku) + j;
 }
 
 // stream position -> {sequence, head-group, tile, tiles of the sequence}; cum[b] <= pos / hs_count < cum[b + 1]
@@ -163,12 +104,12 @@ __host__ __device__ __forceinline__ int sk3_team_size(int avg) {
 }
 
 // One CTA, once per step. Phase 0: SM weights from the rates the decode kernel recorded (frozen after
-// `calib_max` updates, then a launch is a deterministic function of its inputs up to who claims which unit,
-// which does not change what is computed). Phase 1: tiles prefix. Phase 2: CTA ranges by weight, team ranges
-// inside. Phase 3: segment descriptors and which segments share a cut item.
+// `calib_max` updates, then a launch is a deterministic function of its inputs). Phase 1: tiles prefix.
+// Phase 2: CTA ranges by weight, team ranges inside, team descriptors. Phase 3: warp descriptors.
+// Phase 4: which teams share a cut item.
 __global__ void __launch_bounds__(1024)
 sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, int groups, int32_t* __restrict__ plan,
-                Sk2Ctrl* __restrict__ ctrl, int calib_max, int team_force, int pool_pct) {
+                Sk2Ctrl* __restrict__ ctrl, int calib_max, int team_force) {
   __shared__ int s_warp[32];
   __shared__ float s_red[32];
   __shared__ int s_carry, s_nonempty;
@@ -177,10 +118,12 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
   __shared__ int s_cum[kSk3PlanSmemBatch + 1];
   __shared__ int s_tstart[kSk2MaxGroups * kSk3Warps + 1];
   constexpr int W = kSk3Warps;
+  const int ntmax = groups * W;
   int32_t* tstart = plan + sk3_plan_tstart_off();
-  int4* sdesc = reinterpret_cast<int4*>(plan + sk3_plan_sdesc_off(groups));
-  int4* sinfo = reinterpret_cast<int4*>(plan + sk3_plan_sinfo_off(groups));
-  int32_t* cum = plan + sk3_plan_cum_off(groups);
+  int4* tdesc = reinterpret_cast<int4*>(plan + sk3_plan_tdesc_off(ntmax));
+  int4* tinfo = reinterpret_cast<int4*>(plan + sk3_plan_tinfo_off(ntmax));
+  int4* wdesc = reinterpret_cast<int4*>(plan + sk3_plan_wdesc_off(ntmax));
+  int32_t* cum = plan + sk3_plan_cum_off(ntmax);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
     s_carry = 0;
@@ -247,20 +190,6 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
   const int avg = tiles / max(1, s_nonempty);
   const int T = (team_force >= 1 && team_force <= W && W % team_force == 0) ? team_force : sk3_team_size(avg);
   const int tpc = W / T, nt = groups * tpc;
-  // the pool: the last pool_pct % of a team range, in units of two rows of tiles (one row when the range is short)
-  int U = 2 * T, Ku = 0;
-  {
-    const int rows_tail = static_cast<int>(static_cast<int64_t>(total) * pool_pct / 100 / nt / T);
-    if (rows_tail >= 4) {
-      Ku = (rows_tail + 1) / 2;
-    } else {
-      U = T;
-      Ku = rows_tail;
-    }
-    const int cap = kSk3SegPerCta * groups / nt - 1;
-    Ku = max(0, min(Ku, min(kSk3MaxUnits, cap)));
-  }
-  const int ns = nt * (1 + Ku);
   if (tid == 0) {
     cum[batch] = tiles;
     if (cum_in_smem) s_cum[batch] = tiles;
@@ -270,11 +199,9 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     plan[3] = nt;
     plan[4] = batch;
     plan[5] = hs_count;
-    plan[6] = Ku;
+    plan[6] = 0;
     plan[7] = kSk3PlanMagic;
     plan[8] = tpc;
-    plan[9] = U;
-    plan[10] = ns;
     // CTA ranges: cumulative weights; every CTA gets at least one position while there are any, so the non-empty
     // CTAs are a prefix of the grid
     double acc = 0.0;
@@ -295,83 +222,65 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     const int t0 = c == nt ? total : gs + k * q + min(k, r);
     tstart[c] = t0;
     s_tstart[c] = t0;
+    if (c < nt) tdesc[c] = t0 < total ? sk3_desc_of(cum_r, batch, hs_count, t0) : make_int4(batch, 0, 0, 1);
   }
   __syncthreads();
-  // ---- phase 3: segments
-  const Sk3Segs sg{s_tstart, nt, Ku, U, ns, total};
-  for (int s = tid; s < ns; s += 1024) {
-    int t0, t1;
-    sk3_seg_range(sg, s, t0, t1);
+  // ---- phase 3: first position of every warp
+  for (int idx = tid; idx < groups * W; idx += 1024) {
+    const int g = idx / W, w = idx % W;
+    const int c = g * tpc + w / T;
+    const int pos = s_tstart[c] + w % T;
+    wdesc[idx] = pos < s_tstart[c + 1] ? sk3_desc_of(cum_r, batch, hs_count, pos) : make_int4(batch, 0, 0, 1);
+  }
+  // ---- phase 4: cut items
+  for (int c = tid; c < nt; c += 1024) {
+    const int t0 = s_tstart[c], t1 = s_tstart[c + 1];
     int4 info = make_int4(-1, 0, 0, 1);
-    int4 d = make_int4(batch, 0, 0, 1);
     if (t1 > t0) {
-      d = sk3_desc_of(cum_r, batch, hs_count, t0);
-      if (d.z > 0) {  // the segment starts inside an item
+      const int4 d = sk3_desc_of(cum_r, batch, hs_count, t0);
+      if (d.z > 0) {  // the range starts inside an item
         const int i0 = t0 - d.z, i1 = i0 + d.w;
-        const int own = sk3_seg_of(sg, i0);
+        const int own = sk3_team_of(s_tstart, nt, i0);
         int np = 1;
-        for (int j = own + 1; j < ns && sk3_seg_start(sg, j) < i1; ++j) np += sk3_seg_nonempty(sg, j) ? 1 : 0;
+        for (int j = own + 1; j < nt && s_tstart[j] < i1; ++j) np += s_tstart[j + 1] > s_tstart[j] ? 1 : 0;
         info.x = own;
         info.y = np;
       }
       const int4 e = sk3_desc_of(cum_r, batch, hs_count, t1 - 1);
       const int i0 = t1 - 1 - e.z, i1 = i0 + e.w;
-      if (i1 > t1 && i0 >= t0) {  // the last item starts here and goes on in other segments
-        int m = 0, last = s;
-        for (int j = s + 1; j < ns && sk3_seg_start(sg, j) < i1; ++j)
-          if (sk3_seg_nonempty(sg, j)) {
+      if (i1 > t1 && i0 >= t0) {  // the last item starts here and goes on in other teams
+        int m = 0, last = c;
+        for (int j = c + 1; j < nt && s_tstart[j] < i1; ++j)
+          if (s_tstart[j + 1] > s_tstart[j]) {
             ++m;
             last = j;
           }
         info.z = m;
-        info.w = (last == s + m) ? 1 : 0;
+        info.w = (last == c + m) ? 1 : 0;
       }
     }
-    sdesc[s] = d;
-    sinfo[s] = info;
-  }
-  __syncthreads();
-  // ---- phase 4: what every warp of the grid starts with
-  int4* wrec = reinterpret_cast<int4*>(plan + sk3_plan_wrec_off(groups));
-  for (int idx = tid; idx < groups * W; idx += 1024) {
-    const int c = (idx / W) * tpc + (idx % W) / T, s = c * (1 + Ku);
-    int t0, t1;
-    sk3_seg_range(sg, s, t0, t1);
-    const int4 info = sinfo[s];
-    wrec[2 * idx] = make_int4(t0, t1, info.x, info.y | (info.z << 15) | (info.w << 30));
-    wrec[2 * idx + 1] = sdesc[s];
+    tinfo[c] = info;
   }
 }
 
 cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, int32_t* plan, Sk2Ctrl* ctrl,
-                            int calib_max, int team_force, int pool_pct, cudaStream_t stream) {
-  sk3_plan_kernel<<<1, 1024, 0, stream>>>(seq_lens, batch, hs_count, groups, plan, ctrl, calib_max, team_force, pool_pct);
+                            int calib_max, int team_force, cudaStream_t stream) {
+  sk3_plan_kernel<<<1, 1024, 0, stream>>>(seq_lens, batch, hs_count, groups, plan, ctrl, calib_max, team_force);
   return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------------
 // decode kernel
 // ------------------------------------------------------------------------------------------------
-struct Sk3QEntry {  // one segment a team works on, published in shared memory by the warp that fetched it
-  int seg, begin, end, pad;
-  int4 desc, info;
-};
-constexpr int kSk3QueueDepth = 4;  // a front is at most two segments ahead of its math, warps of a team one apart
-
 template <int W, int D, int SB>
 struct Sk3Smem {
   alignas(1024) uint8_t ring[W][D][SB];  // SB = bytes of one stage (K tile + V tile)
   alignas(8) uint64_t bar[W][D];         // "stage landed" mbarriers, one per ring slot
-  uint32_t qstage[W][16][32];            // per warp: q fragments of the item the front prepared (cp.async, no registers)
-  alignas(16) Sk3QEntry q[W][kSk3QueueDepth];  // per team (index: its first warp): the segments it took, in order
-  int q_n[W];                            // ... how many so far
-  int q_lock[W];
   float m[W][kHeadsPerItem];             // merge: reference max (log2 domain) of every warp's state ...
   float l[W][kHeadsPerItem];             // ... and its row sum
   int stash[W];                          // ring slot that holds the warp's accumulators during a merge
   int word[W];                           // per team: the arrival count one thread saw (owner's look) ...
   int word2[W];                          // ... and the one its atomic returned
-  int tiles_done;                        // tiles this CTA streamed (static + claimed)
   long long t0;                          // clock64 at CTA start (the SM's rate is recorded at the end)
   int group;                             // chunk group this CTA claimed
 };
@@ -446,93 +355,41 @@ __device__ __forceinline__ void sk3_fold(Sk3Acc& s, const float4 o, float lo, fl
 }
 
 // Everything a team does at the end of a piece after the warps stashed their states: fold the T states per
-// head, then write the row / leave a partial / fold the other pieces' partials (see the file header).
-// Partial slots: [parity][2 * NSmax][8 heads][128] — slot `seg` for a segment's first piece when it continues an
-// item, slot NSmax + seg for its last piece when it owns a cut item; arrival counters [parity][NSmax] by owner.
+// head, then write the row / leave a partial / fold the neighbours' partials (see the file header).
+//   slot_of(team, owner_side): partial slot in the workspace; cnt: arrival counters (this launch's parity)
 struct Sk3MergeArgs {
   int b, hs;          // the item
   int first, last;    // the piece starts / ends the item
-  int qidx;           // the team's queue entry of the segment (index, info)
-  int tw0, T, wi;
+  int team, tw0, T, wi;
+  int own, np_first;  // tinfo.x, .y (continuation side)
+  int m_last, contig; // tinfo.z, .w (owner side)
   int item_end;       // stream position behind the item
-  int peek;           // arrival count of the item seen shortly before the piece ended (warp 0 of the team)
+  int nt, ntmax;
+  int peek;           // owner side: arrival count seen when the piece began (warp 0 of the team)
 };
 
 template <int W, int D, int SB, bool FP8>
 __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>& sm, const Sk3MergeArgs a, int warp, int lane) {
   const int parity = (p.flags & kSk2FlagParity) ? 1 : 0;
   const int bar_id = 1 + a.tw0 / a.T, nthr = a.T * 32;
-  const int nsmax = kSk3SegPerCta * static_cast<int>(gridDim.x);
-  const Sk3Segs sg = sk3_segs_of_plan(p.sk3_plan);
-  const int seg = sm.q[a.tw0][a.qidx].seg;
-  const int4 info = sm.q[a.tw0][a.qidx].info;  // {owner of the first piece's item, its pieces, continuations, contiguous}
-  float* const part_o = p.sk3_part_o + static_cast<int64_t>(parity) * 2 * nsmax * kHeadsPerItem * kHeadDim;
-  float* const part_l = p.sk3_part_lse + static_cast<int64_t>(parity) * 2 * nsmax * kHeadsPerItem;
-  int32_t* const cnt = p.sk3_cnt + parity * nsmax;
+  float* const part_o = p.sk3_part_o + static_cast<int64_t>(parity) * 2 * a.ntmax * kHeadsPerItem * kHeadDim;
+  float* const part_l = p.sk3_part_lse + static_cast<int64_t>(parity) * 2 * a.ntmax * kHeadsPerItem;
+  int32_t* const cnt = p.sk3_cnt + parity * a.ntmax;
+  const int32_t* const tstart = p.sk3_plan + sk3_plan_tstart_off();
   const bool whole = a.first && a.last;
-  const bool owner = a.first && !a.last;  // cut at the end: the other pieces live in later segments
-  const int pieces = owner ? info.z + 1 : info.y;
-  const int own = owner ? seg : info.x;  // the segment that holds the item's start: counter index, first slot
-  const int64_t my_slot = owner ? nsmax + seg : seg;
+  const bool owner = a.first && !a.last;  // cut at the end: the other pieces live in later teams
+  const int pieces = owner ? a.m_last + 1 : a.np_first;
   const int kvh = a.hs / p.subgroups, sub = a.hs % p.subgroups;
-  if (!whole && a.wi == 0 && lane == 0) {
-    // one thread decides for the team; its fence orders the other pieces' partials before everybody's loads
+  if (owner && a.wi == 0 && lane == 0) {
+    // one thread decides for the team; its fence orders the neighbours' partials before everybody's loads
     if (a.peek == pieces - 1) __threadfence();
     sm.word[a.tw0] = a.peek;
   }
   __syncwarp();
   named_bar_sync(bar_id, nthr);  // every state of the team is stashed
-  // fast: every other piece of the item had arrived when this one looked, so this team is the one that finishes it
-  const bool fast = !whole && sm.word[a.tw0] == pieces - 1;
+  const bool fast = owner && sm.word[a.tw0] == pieces - 1;
   float vs = 1.f;
   if (FP8) vs = __ldg(p.v_scale + kvh * p.scale_stride);
-  // The pieces of a cut item are always folded in the same order (the owner's, then the continuations by
-  // segment), each as its normalised row + log2-domain LSE, whoever does it and whether its own piece comes from
-  // registers or from its slot: the result does not depend on which team finished last.
-  struct Piece {
-    float4 o;
-    float l2;
-  };
-  auto load_piece = [&](int64_t slot, int h) {
-    Piece q;
-    q.o = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane);
-    q.l2 = __ldcg(part_l + slot * kHeadsPerItem + h);
-    return q;
-  };
-  auto fold_item = [&](Sk3Acc& s, int h, bool have_mine, const Piece& mine) {
-    s.a = make_float4(0.f, 0.f, 0.f, 0.f);
-    s.l = 0.f;
-    s.m = -CUDART_INF_F;
-    {
-      const Piece q = (have_mine && owner) ? mine : load_piece(nsmax + own, h);
-      sk3_fold(s, q.o, 1.f, q.l2);
-    }
-    if (owner && info.w) {  // the continuations are exactly the next info.z segments
-      for (int j = own + 1; j <= own + info.z; ++j) {
-        const Piece q = load_piece(j, h);
-        sk3_fold(s, q.o, 1.f, q.l2);
-      }
-      return;
-    }
-    for (int j = own + 1; j < sg.ns && sk3_seg_start(sg, j) < a.item_end; ++j) {
-      if (!sk3_seg_nonempty(sg, j)) continue;
-      const Piece q = (have_mine && j == seg) ? mine : load_piece(j, h);
-      sk3_fold(s, q.o, 1.f, q.l2);
-    }
-  };
-  auto write_row = [&](const Sk3Acc& s, int h) {
-    const int head_in_group = sub * kHeadsPerItem + h;
-    if (head_in_group >= p.group) return;
-    const int hq = kvh * p.group + head_in_group;
-    const float inv = s.l > 0.f ? vs / s.l : 0.f;
-    uint2 pk;
-    pk.x = pack_bf16x2(s.a.x * inv, s.a.y * inv);
-    pk.y = pack_bf16x2(s.a.z * inv, s.a.w * inv);
-    *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(a.b) * p.out_stride_tok + static_cast<int64_t>(hq) * kHeadDim +
-                              lane * 4) = pk;
-    if (p.lse != nullptr && lane == 0)
-      p.lse[static_cast<int64_t>(a.b) * p.num_q_heads + hq] = s.l > 0.f ? (s.m + log2f(s.l)) * kLn2 : -CUDART_INF_F;
-  };
   for (int h = a.wi; h < kHeadsPerItem; h += a.T) {
     Sk3Acc s;
     s.a = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -546,28 +403,55 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
                                                         h * kHeadDim + col);
       sk3_fold(s, v, sm.l[a.tw0 + k][h], mk);
     }
-    if (whole) {
-      write_row(s, h);
-      continue;
+    const int head_in_group = sub * kHeadsPerItem + h;
+    const bool head_ok = head_in_group < p.group;
+    const int hq = kvh * p.group + head_in_group;
+    if (fast) {  // the neighbours' partials are complete: (normalised row, log2-domain LSE) each
+      // the pieces of a cut item are folded in one order and one form (normalised row + LSE, the owner's first)
+      // whoever does it, so the result does not depend on which team happened to finish last
+      const float inv0 = s.l > 0.f ? 1.f / s.l : 0.f;
+      const float4 o0 = make_float4(s.a.x * inv0, s.a.y * inv0, s.a.z * inv0, s.a.w * inv0);
+      const float l0 = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
+      s.a = make_float4(0.f, 0.f, 0.f, 0.f);
+      s.l = 0.f;
+      s.m = -CUDART_INF_F;
+      sk3_fold(s, o0, 1.f, l0);
+      for (int j = a.team + 1, left = a.m_last; left > 0; ++j) {
+        if (!a.contig && !(__ldg(tstart + j + 1) > __ldg(tstart + j))) continue;
+        --left;
+        const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (static_cast<int64_t>(j) * kHeadsPerItem + h) * kHeadDim) + lane);
+        const float lj = __ldcg(part_l + static_cast<int64_t>(j) * kHeadsPerItem + h);
+        sk3_fold(s, o, 1.f, lj);
+      }
     }
-    Piece mine;  // this team's piece as it would sit in its slot
-    {
-      const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
-      mine.o = make_float4(s.a.x * inv, s.a.y * inv, s.a.z * inv, s.a.w * inv);
-      mine.l2 = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
-    }
-    if (fast) {
-      fold_item(s, h, true, mine);
-      write_row(s, h);
+    const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
+    if (whole || fast) {
+      if (head_ok) {
+        uint2 pk;
+        pk.x = pack_bf16x2(s.a.x * inv * vs, s.a.y * inv * vs);
+        pk.y = pack_bf16x2(s.a.z * inv * vs, s.a.w * inv * vs);
+        *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(a.b) * p.out_stride_tok + static_cast<int64_t>(hq) * kHeadDim +
+                                  lane * 4) = pk;
+        if (p.lse != nullptr && lane == 0)
+          p.lse[static_cast<int64_t>(a.b) * p.num_q_heads + hq] = s.l > 0.f ? (s.m + log2f(s.l)) * kLn2 : -CUDART_INF_F;
+      }
     } else {
-      *(reinterpret_cast<float4*>(part_o + (my_slot * kHeadsPerItem + h) * kHeadDim) + lane) = mine.o;
-      if (lane == 0) part_l[my_slot * kHeadsPerItem + h] = mine.l2;
+      const int64_t slot = owner ? a.ntmax + a.team : a.team;
+      *(reinterpret_cast<float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane) =
+          make_float4(s.a.x * inv, s.a.y * inv, s.a.z * inv, s.a.w * inv);
+      if (lane == 0) part_l[slot * kHeadsPerItem + h] = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
     }
   }
-  if (whole || fast) {
-    if (fast && a.wi == 0 && lane == 0) cnt[own] = 0;  // ready for the launch after the next
+  if (whole) {
     fence_proxy_async_smem();
     named_bar_sync(bar_id, nthr);  // the stash slots may be refilled
+    return;
+  }
+  const int own = owner ? a.team : a.own;
+  if (fast) {
+    if (a.wi == 0 && lane == 0) cnt[own] = 0;  // ready for the launch after the next
+    fence_proxy_async_smem();
+    named_bar_sync(bar_id, nthr);
     return;
   }
   // a partial was written: announce it; the last arriver of the item folds all of them
@@ -583,58 +467,33 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
   if (sm.word2[a.tw0] != pieces - 1) return;
   for (int h = a.wi; h < kHeadsPerItem; h += a.T) {
     Sk3Acc s;
-    Piece none;
-    none.o = make_float4(0.f, 0.f, 0.f, 0.f);
-    none.l2 = 0.f;
-    fold_item(s, h, false, none);
-    write_row(s, h);
+    s.a = make_float4(0.f, 0.f, 0.f, 0.f);
+    s.l = 0.f;
+    s.m = -CUDART_INF_F;
+    {
+      const int64_t slot = a.ntmax + own;
+      const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane);
+      sk3_fold(s, o, 1.f, __ldcg(part_l + slot * kHeadsPerItem + h));
+    }
+    for (int j = own + 1; j < a.nt && __ldg(tstart + j) < a.item_end; ++j) {
+      if (!(__ldg(tstart + j + 1) > __ldg(tstart + j))) continue;
+      const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (static_cast<int64_t>(j) * kHeadsPerItem + h) * kHeadDim) + lane);
+      sk3_fold(s, o, 1.f, __ldcg(part_l + static_cast<int64_t>(j) * kHeadsPerItem + h));
+    }
+    const int head_in_group = sub * kHeadsPerItem + h;
+    if (head_in_group < p.group) {
+      const int hq = kvh * p.group + head_in_group;
+      const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
+      uint2 pk;
+      pk.x = pack_bf16x2(s.a.x * inv * vs, s.a.y * inv * vs);
+      pk.y = pack_bf16x2(s.a.z * inv * vs, s.a.w * inv * vs);
+      *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(a.b) * p.out_stride_tok + static_cast<int64_t>(hq) * kHeadDim +
+                                lane * 4) = pk;
+      if (p.lse != nullptr && lane == 0)
+        p.lse[static_cast<int64_t>(a.b) * p.num_q_heads + hq] = s.l > 0.f ? (s.m + log2f(s.l)) * kLn2 : -CUDART_INF_F;
+    }
   }
   if (a.wi == 0 && lane == 0) cnt[own] = 0;
-}
-
-// The k-th segment of a team (k = 0: its own static segment; k >= 1: claimed from the pool, -1 when the pool is
-// empty): fetched once per team by whichever warp needs it first, published in shared memory.
-template <int W, int D, int SB>
-__device__ __noinline__ void sk3_fetch_segment(const DecodeParams& p, Sk3Smem<W, D, SB>& sm, int tw0, int k) {
-  const int groups = static_cast<int>(gridDim.x);
-  const Sk3Segs sg = sk3_segs_of_plan(p.sk3_plan);
-  int32_t* const pool_next = &p.sk2_ctrl->pool_next[(p.flags & kSk2FlagParity) ? 1 : 0];
-  volatile int* qn = &sm.q_n[tw0];
-  while (*qn <= k) {
-    if (atomicCAS(&sm.q_lock[tw0], 0, 1) != 0) {
-      __nanosleep(64);
-      continue;
-    }
-    if (*qn == k) {
-      Sk3QEntry e;
-      e.seg = -1;
-      e.begin = e.end = e.pad = 0;
-      e.desc = e.info = make_int4(0, 0, 0, 0);
-      if (sm.q[tw0][(k - 1) & (kSk3QueueDepth - 1)].seg >= 0) {  // (k >= 1: entry 0 is written by the kernel's prologue)
-        const int claims = sg.nt * sg.Ku;
-        while (claims > 0) {
-          const int c = atomicAdd(pool_next, 1);
-          if (c >= claims) break;
-          const int seg = (c % sg.nt) * (1 + sg.Ku) + 1 + c / sg.nt;  // round by round: every team's unit 1, then 2, ...
-          if (sk3_seg_nonempty(sg, seg)) {
-            e.seg = seg;
-            break;
-          }
-        }
-      }
-      if (e.seg >= 0) {
-        sk3_seg_range(sg, e.seg, e.begin, e.end);
-        e.desc = __ldg(reinterpret_cast<const int4*>(p.sk3_plan + sk3_plan_sdesc_off(groups)) + e.seg);
-        e.info = __ldg(reinterpret_cast<const int4*>(p.sk3_plan + sk3_plan_sinfo_off(groups)) + e.seg);
-      }
-      sm.q[tw0][k & (kSk3QueueDepth - 1)] = e;
-      __threadfence_block();
-      *qn = k + 1;
-    }
-    __threadfence_block();
-    atomicExch(&sm.q_lock[tw0], 0);
-  }
-  __threadfence_block();
 }
 
 template <int W, int D, bool FP8>
@@ -650,7 +509,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   // ---- which chunk group this CTA runs: the one of the SM it sits on (the plan sized group g for SM g), claimed
-  // with one atomic so that every group is run exactly once whatever the block scheduler did; control words of two
+  // with one atomic so that every group is run exactly once whatever the block scheduler did; claim words of two
   // consecutive launches (which may overlap under programmatic dependent launch) are kept apart by the launch
   // parity; the last CTA to finish re-arms the words of its launch.
   Sk2Ctrl* const ctrl = p.sk2_ctrl;
@@ -658,8 +517,9 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   const int G = static_cast<int>(gridDim.x);
   uint32_t smid;
   asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  const int g_spec = static_cast<int>(smid % static_cast<uint32_t>(G));
   if (threadIdx.x == 0) {
-    int g = static_cast<int>(smid % static_cast<uint32_t>(G));
+    int g = g_spec;
     if (atomicCAS(&ctrl->claimed[parity][g], 0, 1) != 0) {
       for (int k = 1; k <= G; ++k) {
         const int gg = (g + k) % G;
@@ -670,9 +530,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       }
     }
     sm.group = g;
-    sm.tiles_done = 0;
   }
-  if (lane == 0) sm.q_lock[warp] = 0;
   bool waited = false;
   auto wait_for_prior = [&]() {
     griddep_wait();
@@ -680,15 +538,19 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     if (threadIdx.x == 0) sm.t0 = clock64();
   };
   if (p.flags & kSk2FlagWaitFirst) wait_for_prior();  // the plan was written by the kernel right before this one
-  // one round of independent loads, for the group the CTA will almost always get (its own SM's)
+  // ---- the warp's work: one round of independent loads, issued for the group the CTA will almost always get
   const int32_t* plan = p.sk3_plan;
+  const int ntmax = G * W;
   const int4 hdr = __ldg(reinterpret_cast<const int4*>(plan));
   const int4 hdr2 = __ldg(reinterpret_cast<const int4*>(plan) + 1);
-  const int g_spec = static_cast<int>(smid % static_cast<uint32_t>(G));
-  const int4* wrec = reinterpret_cast<const int4*>(plan + sk3_plan_wrec_off(G));
-  int4 wa = __ldg(wrec + 2 * (g_spec * W + warp)), wb = __ldg(wrec + 2 * (g_spec * W + warp) + 1);
-  const int T = hdr.z;
-  const int32_t* cum = plan + sk3_plan_cum_off(G);
+  const int T = hdr.z, nt = hdr.w, tpc = __ldg(plan + 8);
+  const int wi = warp % T, tw0 = warp - wi;
+  int team = g_spec * tpc + warp / T;
+  int4 wd = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_wdesc_off(ntmax)) + g_spec * W + warp);
+  int4 td = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tdesc_off(ntmax)) + team);
+  int4 ti = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tinfo_off(ntmax)) + team);
+  int t_begin = __ldg(plan + sk3_plan_tstart_off() + team), t_end = __ldg(plan + sk3_plan_tstart_off() + team + 1);
+  const int32_t* cum = plan + sk3_plan_cum_off(ntmax);
   if (lane == 0) {
 #pragma unroll
     for (int s = 0; s < D; ++s) mbar_init(&sm.bar[warp][s], 1);
@@ -698,43 +560,30 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       tma_prefetch_desc(&tm_v);
     }
   }
-  // the team's first segment is its own static one (every warp of the team writes the same words)
-  auto write_first_entry = [&](int g) {
-    if (lane == 0) {
-      const int tw = warp - warp % T;
-      Sk3QEntry e;
-      e.seg = (g * (W / T) + warp / T) * (1 + hdr2.z);
-      e.begin = wa.x;
-      e.end = wa.y;
-      e.pad = 0;
-      e.desc = wb;
-      e.info = make_int4(wa.z, wa.w & 0x7fff, (wa.w >> 15) & 0x7fff, (wa.w >> 30) & 1);
-      sm.q[tw][0] = e;
-      sm.q_n[tw] = 1;
-    }
-  };
-  write_first_entry(g_spec);
   __syncthreads();
   const int group = sm.group;
-  const int hs_count = p.num_kv_heads * p.subgroups;
-  if (hdr.y != G || T < 1 || T > W || (W % T) != 0 || hdr2.x != p.batch || hdr2.y != hs_count || hdr2.w != kSk3PlanMagic ||
-      __ldg(plan + 10) > kSk3SegPerCta * G)
-    __trap();  // the plan in the workspace was made for another launch shape: fail loudly
-  const int wi = warp % T, tw0 = warp - wi;
-  const int gw = group * W + warp;
   if (group != g_spec) {  // rare: this CTA runs another SM's group
-    wa = __ldg(wrec + 2 * gw);
-    wb = __ldg(wrec + 2 * gw + 1);
-    write_first_entry(group);
-    __syncthreads();
+    team = group * tpc + warp / T;
+    wd = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_wdesc_off(ntmax)) + group * W + warp);
+    td = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tdesc_off(ntmax)) + team);
+    ti = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tinfo_off(ntmax)) + team);
+    t_begin = __ldg(plan + sk3_plan_tstart_off() + team);
+    t_end = __ldg(plan + sk3_plan_tstart_off() + team + 1);
   }
+  const int gw = group * W + warp;
   if (p.trace != nullptr && lane == 0) {  // debug: entry stamp, SM id
     p.trace[gw * 8 + 0] = sk3_globaltimer();
     p.trace[gw * 8 + 4] = smid;
   }
   // the next kernel of the chain may start its own prologue (it cannot get an SM before this CTA exits)
   griddep_launch_dependents();
+
+  const int hs_count = p.num_kv_heads * p.subgroups;
+  if (hdr.y != G || T < 1 || T > W || (W % T) != 0 || hdr2.x != p.batch || hdr2.y != hs_count || hdr2.w != kSk3PlanMagic)
+    __trap();  // the plan in the workspace was made for another launch shape: fail loudly
   const bool early = (p.flags & kSk2FlagEarlyKvRead) != 0;
+  const int my_first = t_begin + wi;
+  const int cnt_tiles = my_first < t_end ? (t_end - my_first + T - 1) / T : 0;
 
   const SkLane sl = sk_make_lane(lane);
   const uint32_t ring0 = smem_u32(sm.ring[warp][0]);
@@ -742,76 +591,54 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   const uint64_t pol = l2_policy_evict_first();  // KV pages are streamed once per step
 
   // prefetch-front state
-  Sk3Walk pf{0, 0, 0, 1};
-  int pf_left = 0;          // positions of this warp left in the front's segment
-  int f_next = 0;           // segments the front fetched so far
-  bool f_done = false;      // the front saw the end of the pool
-  int pf_t0 = 0, pf_k = 0, pf_kbase = 0, pf_kvh = 0;  // block ids: tile pf_t0 + T * (pf_kbase + lane) of the item
+  Sk3Walk pf{wd.x, wd.y, wd.z, wd.w};
+  int pf_left = cnt_tiles;
+  int pf_t0 = pf.tile, pf_k = 0, pf_kbase = 0, pf_kvh = 0;  // block ids: tile pf_t0 + T * (pf_kbase + lane) of the item
   int ids = 0;
   int pf_items_ahead = 0;   // item starts prepared by the front and not yet taken by the math (0 or 1)
   bool pf_fresh = true;     // the front stands on a tile whose item it has not prepared yet
   bool q_deferred = false;  // the prepared item's q has not been loaded (griddepcontrol.wait pending)
   int it_b = 0, it_hs = 0;  // the item the front prepared last (the front itself may have moved on)
   int pslot = 0, pending = 0;
-  // math state
-  int m_next = 0;           // segments the math fetched so far
+  // math state: the team's pieces in order; this warp's positions inside them
+  int mb = td.x, mhs = td.y, mn = td.w;
+  int item_pos0 = t_begin - td.z;  // stream position of tile 0 of the current item
+  int piece_begin = t_begin;
+  int mp = my_first;               // this warp's next position
   int cslot = 0;
   uint32_t cphase = 0;  // parity of the current pass over the ring
-  bool first_landed = false;
-  int my_tiles = 0;
-  uint32_t qf[8][2];
+  bool have_item = false, got = false, first_landed = false;
+  int peek = -1;
+  uint32_t qf[8][2], qf_n[8][2];
 #pragma unroll
-  for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = 0u;
+  for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = qf_n[kk][0] = qf_n[kk][1] = 0u;
   float scale = p.scale_log2, scale_n = p.scale_log2;
   int slen = 0, slen_n = 0;
   WarpState st;
   state_reset(st);
 
-  // q (and the K scale) of the item the front prepared last: the words of this lane's B fragments go from global
-  // to the warp's staging row with cp.async — the math takes them when it gets to the item.
-  // bf16: qf[kk][i] = Q[head g][16 kk + 2 t + 8 i, +1]; fp8 (f16 MMAs, permuted k): Q[head g][16 kk + 4 t + 2 i, +1]
-  auto load_q_next = [&]() {
-    const int g = lane >> 2, t = lane & 3;
-    const int kvh = it_hs / p.subgroups, sub = it_hs % p.subgroups;
-    const int head_in_group = sub * kHeadsPerItem + g;
-    const uint32_t* row = reinterpret_cast<const uint32_t*>(p.q + static_cast<int64_t>(it_b) * p.q_stride_tok +
-                                                            static_cast<int64_t>(kvh * p.group + head_in_group) * kHeadDim);
-    const uint32_t dst = smem_u32(&sm.qstage[warp][0][lane]);
-    if (head_in_group < p.group) {
-#pragma unroll
-      for (int kk = 0; kk < 8; ++kk)
-#pragma unroll
-        for (int i = 0; i < 2; ++i)
-          cp_async_4(dst + (kk * 2 + i) * 128, row + kk * 8 + (FP8 ? 2 * t + i : t + 4 * i));
+  auto load_q_next = [&]() {  // q (and the K scale) of the item the front prepared last
+    WorkItem w;
+    w.b = it_b;
+    w.kvh = it_hs / p.subgroups;
+    w.sub = it_hs % p.subgroups;
+    if (FP8) {
+      sk_load_q_f16(p, w.b, w.kvh, w.sub, lane, qf_n);
+      scale_n = p.scale_log2 * __ldg(p.k_scale + w.kvh * p.scale_stride);
     } else {
-#pragma unroll
-      for (int w = 0; w < 16; ++w) sm.qstage[warp][w][lane] = 0u;
+      load_q_frags(p, w, lane, qf_n);
     }
-    if (FP8) scale_n = p.scale_log2 * __ldg(p.k_scale + kvh * p.scale_stride);
   };
-  auto segment = [&](int k) -> const Sk3QEntry& {  // the team's k-th segment (warp-uniform)
-    if (lane == 0) sk3_fetch_segment<W, D, SB>(p, sm, tw0, k);
-    __syncwarp();
-    return sm.q[tw0][k & (kSk3QueueDepth - 1)];
-  };
-  // keep the ring full: issue this warp's next tiles, moving on to the team's next segments
-  auto fill_ring = [&]() {
-    while (pending < D) {
-      if (pf_left == 0) {
-        if (f_done || f_next >= m_next + 2) break;  // at most two segments ahead of the math
-        const Sk3QEntry& e = segment(f_next);
-        ++f_next;
-        if (e.seg < 0) {
-          f_done = true;
-          break;
-        }
-        const int first = e.begin + wi;
-        pf_left = first < e.end ? (e.end - first + T - 1) / T : 0;
-        if (pf_left == 0) continue;
-        pf = Sk3Walk{e.desc.x, e.desc.y, e.desc.z, e.desc.w};
-        if (wi > 0) sk3_advance(cum, p.batch, hs_count, wi, pf);
-        pf_fresh = true;
-      }
+
+  while (piece_begin < t_end) {
+    const int item_end = item_pos0 + mn;
+    const int piece_end = min(item_end, t_end);
+    // the owner of a cut item looks at the arrival counter a few tiles before it ends its piece (the answer is in
+    // a register before the merge needs it)
+    if (peek < 0 && wi == 0 && ti.z > 0 && piece_begin == item_pos0 && item_end > t_end && mp + 3 * T >= piece_end)
+      peek = sk3_ld_relaxed(p.sk3_cnt + parity * ntmax + team) & 0x7fffffff;
+    // ================= keep the ring full =================
+    while (pending < D && pf_left > 0) {
       if (pf_fresh) {
         // first tile (of this warp) in an item: qf_n holds one prepared item, so the front never runs two item
         // starts ahead of the math
@@ -860,158 +687,111 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       if (--pf_left > 0) pf_fresh = sk3_advance(cum, p.batch, hs_count, T, pf);
     }
     if (q_deferred) {  // the first stages are in flight: now wait for the previous kernel and fetch q
-      if (early && p.l2_prefetch_tiles > 0) {
-        // ... but first ask for this warp's next tiles of the item as far as L2 (lane l holds the block id of the
-        // tile l steps behind the window base): the time an early CTA spends waiting for the stragglers of the
-        // previous kernel is HBM time nobody else uses
-        const int k = pf_kbase + lane - pf_k;  // steps ahead of the front
-        const int tile = pf_t0 + T * (pf_kbase + lane);
-        if (k >= 0 && k < p.l2_prefetch_tiles && k < pf_left && tile + 1 < pf.n) {
-          const int slot0 = (tile & p.tpp_mask) * kTileTokens;
-          if (FP8) {
-            tma_prefetch_l2_4d(&tm_k, 0, slot0, pf_kvh, ids);
-            tma_prefetch_l2_4d(&tm_v, 0, slot0, pf_kvh, ids);
-          } else {
-            tma_prefetch_l2_5d(&tm_k, 0, slot0, 0, pf_kvh, ids);
-            tma_prefetch_l2_5d(&tm_v, 0, slot0, 0, pf_kvh, ids);
-          }
-        }
-      }
       wait_for_prior();
       load_q_next();
       q_deferred = false;
     }
-  };
-
-  while (true) {
-    const Sk3QEntry& cur = segment(m_next);
-    ++m_next;
-    if (cur.seg < 0) break;
-    const int qidx = (m_next - 1) & (kSk3QueueDepth - 1);
-    const int t_end = cur.end;
-    // the segment's pieces in order; this warp's positions inside them
-    int mb = cur.desc.x, mhs = cur.desc.y, mn = cur.desc.w;
-    int item_pos0 = cur.begin - cur.desc.z;  // stream position of tile 0 of the current item
-    int piece_begin = cur.begin;
-    int mp = cur.begin + wi;                 // this warp's next position
-    bool have_item = false, got = false;
-    int peek = -1;
-    while (piece_begin < t_end) {
-      const int item_end = item_pos0 + mn;
-      const int piece_end = min(item_end, t_end);
-      // a piece of a cut item looks at the item's arrival counter a few tiles before it ends (the answer is in a
-      // register before the merge needs it)
-      if (peek < 0 && wi == 0 && mp + 3 * T >= piece_end) {
-        const int32_t* cnt = p.sk3_cnt + ((p.flags & kSk2FlagParity) ? kSk3SegPerCta * G : 0);
-        if (piece_begin > item_pos0) {
-          if (!(p.flags & kSk3FlagOwnerFastOnly))
-            peek = sk3_ld_relaxed(cnt + sm.q[tw0][qidx].info.x) & 0x7fffffff;  // the piece continues an item
-        }
-        else if (item_end > t_end)
-          peek = sk3_ld_relaxed(cnt + sm.q[tw0][qidx].seg) & 0x7fffffff;     // it owns a cut item
-      }
-      fill_ring();
-      int ds = cslot;
-      if (mp < piece_end) {
-        if (!have_item) {  // take the item the front prepared
-          cp_async_wait_all();  // this lane's own words (nobody else reads them)
+    int ds = cslot;
+    if (mp < piece_end) {
+      if (!have_item) {  // take the item the front prepared
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk)
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-              const uint32_t raw = sm.qstage[warp][kk * 2 + i][lane];  // two bf16
-              qf[kk][i] = FP8 ? pack_f16x2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u)) : raw;
-            }
-          scale = scale_n;
-          slen = slen_n;
-          pf_items_ahead = 0;
-          have_item = true;
-          continue;  // the front may now prepare the item after this one
+        for (int kk = 0; kk < 8; ++kk) {
+          qf[kk][0] = qf_n[kk][0];
+          qf[kk][1] = qf_n[kk][1];
         }
-        // ================= math on the oldest stage =================
-        mbar_wait(&sm.bar[warp][cslot], cphase);
-        if (p.trace != nullptr && !first_landed && lane == 0) p.trace[gw * 8 + 1] = sk3_globaltimer();
-        first_landed = true;
-        {
-          const int tile = mp - item_pos0;
-          const int valid = (tile + 1 == mn) ? slen - tile * kTileTokens : kTileTokens;
-          if (FP8)
-            sk_consume_fp8<true>(ring0 + cslot * SB, sm.ring[warp][cslot], valid, qf, sl, scale, st, lane);
-          else
-            sk_consume<true>(ring0 + cslot * SB, sm.ring[warp][cslot], valid, qf, sl, scale, st, lane);
-          if (valid < kTileTokens) fence_proxy_async_smem();  // zeroed V rows vs. the next TMA write
-        }
-        __syncwarp();  // every lane has read the slot before lane 0 refills it
-        --pending;
-        ++my_tiles;
-        got = true;
-        mp += T;
-        if (++cslot == D) {
-          cslot = 0;
-          cphase ^= 1u;
-        }
-        if (mp < piece_end) continue;
+        scale = scale_n;
+        slen = slen_n;
+        pf_items_ahead = 0;
+        have_item = true;
+        continue;  // the front may now prepare the item after this one
       }
-      // ================= the piece is done for this warp: fold the team's states =================
+      // ================= math on the oldest stage =================
+      mbar_wait(&sm.bar[warp][cslot], cphase);
+      if (p.trace != nullptr && !first_landed && lane == 0) p.trace[gw * 8 + 1] = sk3_globaltimer();
+      first_landed = true;
       {
-        const int g = lane >> 2, t = lane & 3;
-        if (got) {
-#pragma unroll
-          for (int off = 4; off <= 16; off <<= 1) {
-            st.l[0] += __shfl_xor_sync(0xffffffffu, st.l[0], off);
-            st.l[1] += __shfl_xor_sync(0xffffffffu, st.l[1], off);
-          }
-          float* stash = reinterpret_cast<float*>(sm.ring[warp][ds]);  // the slot just drained is free
-          const int da = FP8 ? 2 * g : g, db = FP8 ? 2 * g + 1 : g + 8;  // fragment row -> d, see sk_consume_fp8
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            stash[sk3_stash_idx(2 * t, 16 * j + da)] = st.acc[j][0];
-            stash[sk3_stash_idx(2 * t + 1, 16 * j + da)] = st.acc[j][1];
-            stash[sk3_stash_idx(2 * t, 16 * j + db)] = st.acc[j][2];
-            stash[sk3_stash_idx(2 * t + 1, 16 * j + db)] = st.acc[j][3];
-          }
-          if (g == 0) {
-            sm.m[warp][2 * t] = st.m[0];
-            sm.m[warp][2 * t + 1] = st.m[1];
-            sm.l[warp][2 * t] = st.l[0];
-            sm.l[warp][2 * t + 1] = st.l[1];
-          }
-          if (lane == 0) sm.stash[warp] = ds;
-        } else if (lane < kHeadsPerItem) {
-          sm.m[warp][lane] = -CUDART_INF_F;
-          sm.l[warp][lane] = 0.f;
-        }
-        if (!waited) wait_for_prior();  // the merge writes global memory
-        Sk3MergeArgs a;
-        a.b = mb;
-        a.hs = mhs;
-        a.first = piece_begin == item_pos0;
-        a.last = piece_end == item_end;
-        a.qidx = qidx;
-        a.tw0 = tw0;
-        a.T = T;
-        a.wi = wi;
-        a.item_end = item_end;
-        a.peek = peek;
-        sk3_merge<W, D, SB, FP8>(p, sm, a, warp, lane);
-        state_reset(st);
-        got = false;
-        have_item = false;
-        peek = -1;
+        const int tile = mp - item_pos0;
+        const int valid = (tile + 1 == mn) ? slen - tile * kTileTokens : kTileTokens;
+        if (FP8)
+          sk_consume_fp8<true>(ring0 + cslot * SB, sm.ring[warp][cslot], valid, qf, sl, scale, st, lane);
+        else
+          sk_consume<true>(ring0 + cslot * SB, sm.ring[warp][cslot], valid, qf, sl, scale, st, lane);
+        if (valid < kTileTokens) fence_proxy_async_smem();  // zeroed V rows vs. the next TMA write
       }
-      piece_begin = piece_end;
-      if (piece_end == item_end && piece_begin < t_end) {  // next item of the segment
-        item_pos0 = item_end;
-        if (++mhs == hs_count) {
-          mhs = 0;
-          int c0 = __ldg(cum + mb + 1), c1 = c0;
-          do {
-            ++mb;
-            c0 = c1;
-            c1 = mb < p.batch ? __ldg(cum + mb + 1) : c0 + 1;
-          } while (mb < p.batch && c1 == c0);
-          mn = c1 - c0;
+      __syncwarp();  // every lane has read the slot before lane 0 refills it
+      --pending;
+      got = true;
+      mp += T;
+      if (++cslot == D) {
+        cslot = 0;
+        cphase ^= 1u;
+      }
+      if (mp < piece_end) continue;
+    }
+    // ================= the piece is done for this warp: fold the team's states =================
+    {
+      const int g = lane >> 2, t = lane & 3;
+      if (got) {
+#pragma unroll
+        for (int off = 4; off <= 16; off <<= 1) {
+          st.l[0] += __shfl_xor_sync(0xffffffffu, st.l[0], off);
+          st.l[1] += __shfl_xor_sync(0xffffffffu, st.l[1], off);
         }
+        float* stash = reinterpret_cast<float*>(sm.ring[warp][ds]);  // the slot just drained is free
+        const int da = FP8 ? 2 * g : g, db = FP8 ? 2 * g + 1 : g + 8;  // fragment row -> d, see sk_consume_fp8
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          stash[sk3_stash_idx(2 * t, 16 * j + da)] = st.acc[j][0];
+          stash[sk3_stash_idx(2 * t + 1, 16 * j + da)] = st.acc[j][1];
+          stash[sk3_stash_idx(2 * t, 16 * j + db)] = st.acc[j][2];
+          stash[sk3_stash_idx(2 * t + 1, 16 * j + db)] = st.acc[j][3];
+        }
+        if (g == 0) {
+          sm.m[warp][2 * t] = st.m[0];
+          sm.m[warp][2 * t + 1] = st.m[1];
+          sm.l[warp][2 * t] = st.l[0];
+          sm.l[warp][2 * t + 1] = st.l[1];
+        }
+        if (lane == 0) sm.stash[warp] = ds;
+      } else if (lane < kHeadsPerItem) {
+        sm.m[warp][lane] = -CUDART_INF_F;
+        sm.l[warp][lane] = 0.f;
+      }
+      if (!waited) wait_for_prior();  // the merge writes global memory
+      Sk3MergeArgs a;
+      a.b = mb;
+      a.hs = mhs;
+      a.first = piece_begin == item_pos0;
+      a.last = piece_end == item_end;
+      a.team = team;
+      a.tw0 = tw0;
+      a.T = T;
+      a.wi = wi;
+      a.own = ti.x;
+      a.np_first = ti.y;
+      a.m_last = ti.z;
+      a.contig = ti.w;
+      a.item_end = item_end;
+      a.nt = nt;
+      a.ntmax = ntmax;
+      a.peek = peek;
+      sk3_merge<W, D, SB, FP8>(p, sm, a, warp, lane);
+      state_reset(st);
+      got = false;
+      have_item = false;
+    }
+    piece_begin = piece_end;
+    if (piece_end == item_end && piece_begin < t_end) {  // next item of the team's range
+      item_pos0 = item_end;
+      if (++mhs == hs_count) {
+        mhs = 0;
+        int c0 = __ldg(cum + mb + 1), c1 = c0;
+        do {
+          ++mb;
+          c0 = c1;
+          c1 = mb < p.batch ? __ldg(cum + mb + 1) : c0 + 1;
+        } while (mb < p.batch && c1 == c0);
+        mn = c1 - c0;
       }
     }
   }
@@ -1023,7 +803,6 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     if (!first_landed) p.trace[gw * 8 + 1] = t_end_ns;
     p.trace[gw * 8 + 2] = t_end_ns;
     p.trace[gw * 8 + 3] = t_end_ns;
-    p.trace[gw * 8 + 5] = static_cast<unsigned long long>(my_tiles);
   }
   // rows of empty sequences: zero, LSE = -inf (no tile of theirs is in the stream)
   for (int b = static_cast<int>(blockIdx.x) * W + warp; b < p.batch; b += G * W) {
@@ -1033,23 +812,22 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     if (p.lse != nullptr)
       for (int h = lane; h < p.num_q_heads; h += 32) p.lse[static_cast<int64_t>(b) * p.num_q_heads + h] = -CUDART_INF_F;
   }
-  if (lane == 0 && my_tiles > 0) atomicAdd(&sm.tiles_done, my_tiles);
   __syncthreads();
   if (threadIdx.x == 0) {
-    // what this SM achieved (the plan kernel turns it into the SM's share of the next steps' streams), summed over
-    // the launches since the last plan (every layer of a step): one launch is a noisy sample ...
+    // what this SM achieved (the plan kernel turns it into the SM's share of the next steps' streams) ...
     if (smid < static_cast<uint32_t>(kSk2MaxGroups)) {
+      const int32_t* tstart = plan + sk3_plan_tstart_off();
+      // summed over the launches since the last plan (every layer of a step): one launch is a noisy sample
       const long long cyc = clock64() - sm.t0;
       if (cyc > 0 && cyc < 0x10000000ll && ctrl->stat_cycles[smid] < 0x30000000) {
-        atomicAdd(&ctrl->stat_tiles[smid], sm.tiles_done);
+        atomicAdd(&ctrl->stat_tiles[smid], __ldg(tstart + (group + 1) * tpc) - __ldg(tstart + group * tpc));
         atomicAdd(&ctrl->stat_cycles[smid], static_cast<int>(cyc));
       }
     }
-    // ... and the last CTA of the launch re-arms the control words of its parity
+    // ... and the last CTA of the launch re-arms the claim words of its parity
     __threadfence();
     if (atomicAdd(&ctrl->finished[parity], 1) == G - 1) {
       for (int g = 0; g < G; ++g) ctrl->claimed[parity][g] = 0;
-      ctrl->pool_next[parity] = 0;
       ctrl->finished[parity] = 0;
       __threadfence();
     }

@@ -41,18 +41,6 @@ __device__ __forceinline__ void tma_load_4d_s(uint32_t dst, const CUtensorMap* t
       : "memory");
 }
 
-// the same boxes, only as far as L2 (no shared memory, no completion)
-__device__ __forceinline__ void tma_prefetch_l2_5d(const CUtensorMap* tm, int c0, int c1, int c2, int c3, int c4) {
-  asm volatile("cp.async.bulk.prefetch.tensor.5d.L2.global.tile [%0, {%1, %2, %3, %4, %5}];" ::"l"(reinterpret_cast<uint64_t>(tm)),
-               "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-               : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* tm, int c0, int c1, int c2, int c3) {
-  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(reinterpret_cast<uint64_t>(tm)),
-               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-               : "memory");
-}
-
 // Online-softmax reference max is refreshed lazily: the running reference m may lag the true
 // row max by up to kTau (log2 units), so P <= 2^kTau (exact in fp32 / bf16 range) and the
 // accumulator rescale — and the cross-lane max reduction that feeds it — only run when some

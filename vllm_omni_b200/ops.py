@@ -12,7 +12,7 @@ from . import _lib
 from ._lib import (DECODE_EARLY_KV_READ, DECODE_PLANNED, KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC,  # noqa: F401
                    VARIANT_SK2, VARIANT_SK3, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check)
 
-WORKSPACE_MIN_BYTES = 131072  # control area (arrival / claim counters), see b200attn_workspace_init
+WORKSPACE_MIN_BYTES = 65536  # control area (arrival / claim counters), see b200attn_workspace_init
 
 _FP8_NAMES = ("fp8", "fp8_e4m3")
 
@@ -270,31 +270,24 @@ def decode_plan(seq_lens: torch.Tensor, block_table: torch.Tensor, batch: int, n
 
 
 def debug_sk3_plan(workspace: DecodeWorkspace, batch: int, num_q_heads: int) -> dict:
-    """The plan `decode_plan` left in `workspace`, parsed (tests / timeline scripts; synchronises). Segment s of
-    team c: s = c * (1 + Ku) + j, j = 0 the team's static part, j = 1..Ku the pool units cut from its end."""
+    """The plan `decode_plan` left in `workspace`, parsed (tests / timeline scripts; synchronises)."""
     lib = _lib.load()
     off = int(lib.b200attn_debug_plan_offset(int(batch), int(num_q_heads)))
     words = workspace.buf[off:].view(torch.int32)
     hdr = words[:16].cpu().tolist()
-    total, groups, T, nt, b, hs_count, Ku, magic, tpc, U, ns = hdr[:11]
+    total, groups, T, nt, b, hs_count, _, magic, tpc = hdr[:9]
     if magic != 0x534B3350:
         raise RuntimeError("no cooperative stream-K plan in this workspace")
-    ntmax, nsmax = groups * 12, groups * 16
+    ntmax = groups * 12
     o_desc = 16 + ((ntmax + 1 + 3) & ~3)
-    o_cum = o_desc + 8 * nsmax + 8 * ntmax   # behind the per-warp start records
-    w = words[:o_cum + batch + 1].cpu()
-    tstart = w[16:16 + nt + 1].tolist()
-    bounds = []
-    for s_ in range(ns):
-        c, j = divmod(s_, 1 + Ku)
-        s0, e0 = tstart[c], tstart[c + 1]
-        lo, hi = e0 - (Ku - j + 1) * U, e0 - (Ku - j) * U
-        bounds.append((s0 if j == 0 else max(lo, s0), max(hi, s0)))
+    n_words = o_desc + 12 * ntmax + batch + 1
+    w = words[:n_words].cpu()
     return {"total": total, "groups": groups, "T": T, "nt": nt, "batch": b, "hs_count": hs_count, "tpc": tpc,
-            "Ku": Ku, "U": U, "ns": ns, "tstart": tstart, "seg_bounds": bounds,
-            "sdesc": w[o_desc:o_desc + 4 * ns].view(ns, 4).tolist(),
-            "sinfo": w[o_desc + 4 * nsmax:o_desc + 4 * nsmax + 4 * ns].view(ns, 4).tolist(),
-            "cum": w[o_cum:o_cum + batch + 1].tolist()}
+            "tstart": w[16:16 + ntmax + 1].tolist(),
+            "tdesc": w[o_desc:o_desc + 4 * ntmax].view(ntmax, 4).tolist(),
+            "tinfo": w[o_desc + 4 * ntmax:o_desc + 8 * ntmax].view(ntmax, 4).tolist(),
+            "wdesc": w[o_desc + 8 * ntmax:o_desc + 12 * ntmax].view(ntmax, 4).tolist(),
+            "cum": w[o_desc + 12 * ntmax:o_desc + 12 * ntmax + batch + 1].tolist()}
 
 
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
