@@ -22,6 +22,9 @@ ap.add_argument("--kv-cache-dtype", default="auto")
 ap.add_argument("--graphs", action="store_true", help="CUDA-graph decode (no torch.compile) instead of eager")
 ap.add_argument("--max-tokens", type=int, default=12)
 ap.add_argument("--layers", type=int, default=4)
+ap.add_argument("--omni", action="store_true",
+                help="run inside vllm-omni: the reference's OmniEngineArgs (its plugin loader finds this repo's entry "
+                     "point), GPUARWorker / GPUARModelRunner, and its own Qwen2 decoder (qwen2_old.py) as the model")
 ap.add_argument("--out", default="")
 args = ap.parse_args()
 
@@ -39,10 +42,109 @@ CONFIG = {
 }
 
 
+OMNI_CONFIG = {  # the reference's own decoder for its Qwen2.5-Omni thinker (qwen2_old.py: bias in qkv, no q/k norm)
+    "architectures": ["B200ThinkerStandIn"], "model_type": "qwen2", "vocab_size": 2048, "hidden_size": 2048,
+    "intermediate_size": 2048, "num_hidden_layers": args.layers, "num_attention_heads": 16,
+    "num_key_value_heads": 2, "max_position_embeddings": 4096, "rms_norm_eps": 1e-6,
+    "rope_theta": 1000000.0, "tie_word_embeddings": False, "torch_dtype": "bfloat16", "hidden_act": "silu",
+    "bos_token_id": 1, "eos_token_id": 2, "sliding_window": None, "use_sliding_window": False,
+}
+
+
+def run_omni():
+    """The same prompts through the reference's own engine arguments, worker and AR model runner."""
+    import torch
+    from tests import ref_import
+    stubbed = ref_import.setup()
+    import vllm_omni  # noqa: F401  (applies the reference's patches to vLLM)
+    from vllm import SamplingParams
+    from vllm.v1.engine.llm_engine import LLMEngine
+    from vllm_omni.engine.arg_utils import OmniEngineArgs
+    from vllm_omni.engine.stage_init_utils import extract_stage_metadata  # noqa: F401  (where a backend is forced)
+
+    # the reference's decoder with a forward() that takes the AR runner's keyword arguments (tests/omni_standin.py)
+    from vllm_omni.model_executor.models.registry import OmniModelRegistry
+    from vllm import ModelRegistry
+    for reg in (OmniModelRegistry, ModelRegistry):   # (the reference mirrors its own models into vLLM's registry too)
+        reg.register_model("B200ThinkerStandIn", "tests.omni_standin:ThinkerStandIn")
+    d = tempfile.mkdtemp(prefix="tiny_qwen2_old_")
+    Path(d, "config.json").write_text(json.dumps(OMNI_CONFIG))
+    # stage engine_args as a stage YAML would give them (qwen3_omni_moe.yaml:14-27), with the backend knob
+    stage_args = dict(model=d, load_format="dummy", skip_tokenizer_init=True, dtype="bfloat16", max_model_len=2048,
+                      gpu_memory_utilization=0.15, kv_cache_dtype=args.kv_cache_dtype, seed=0, max_num_seqs=16,
+                      enable_prefix_caching=False, model_stage="thinker", model_arch="B200ThinkerStandIn",
+                      worker_type="ar", engine_output_type="text",
+                      worker_cls="vllm_omni.worker.gpu_ar_worker.GPUARWorker")
+    if args.backend == "CUSTOM":
+        from vllm_omni_b200 import plugin
+        stage_args = plugin.force_for_stage(stage_args)     # next to stage_init_utils.py:282-293's ROCm precedent
+    else:
+        stage_args["attention_backend"] = args.backend
+    if args.graphs:
+        stage_args["compilation_config"] = {"mode": 0, "cudagraph_mode": "FULL_DECODE_ONLY",
+                                            "cudagraph_capture_sizes": [1, 2, 4, 8]}
+    else:
+        stage_args["enforce_eager"] = True
+    # vLLM version skew, outside the attention path: the reference pins vLLM 0.19.0 (docker/Dockerfile.cuda:1), this
+    # image has 0.22, whose GPUModelRunner._bookkeeping_sync no longer takes spec_decode_metadata
+    import inspect
+    from vllm.v1.worker.gpu_model_runner import GPUModelRunner
+    from vllm_omni.worker.gpu_ar_model_runner import GPUARModelRunner
+    n_params = len(inspect.signature(GPUModelRunner._bookkeeping_sync).parameters)
+    skew = []
+    if n_params == 6:
+        base_sync = GPUModelRunner._bookkeeping_sync
+        GPUARModelRunner._bookkeeping_sync = lambda self, *a: base_sync(self, *a[:5])
+        skew.append("_bookkeeping_sync(spec_decode_metadata dropped)")
+    engine_args = OmniEngineArgs(**stage_args)   # __post_init__ runs vllm_omni.plugins.load_omni_general_plugins()
+    engine = LLMEngine.from_engine_args(engine_args)
+    worker = engine.engine_core.engine_core.model_executor.driver_worker.worker
+    mr = worker.model_runner
+    gen = torch.Generator(device="cuda").manual_seed(1234)
+    with torch.no_grad():
+        for name, prm in sorted(mr.model.named_parameters()):
+            if prm.ndim == 1 and "norm" in name:
+                prm.fill_(1.0)
+            elif prm.ndim == 1:
+                prm.zero_()                                   # qkv bias
+            else:
+                prm.copy_((torch.randn(prm.shape, generator=gen, device="cuda") * 0.03).to(prm.dtype))
+    g = torch.Generator().manual_seed(0)
+    lens = [5, 37, 130, 1, 700, 64, 33]
+    sp = SamplingParams(temperature=0.0, max_tokens=args.max_tokens, logprobs=1, detokenize=False, ignore_eos=True)
+    for i, n in enumerate(lens):
+        engine.add_request(str(i), {"prompt_token_ids": torch.randint(3, OMNI_CONFIG["vocab_size"], (n,), generator=g).tolist()}, sp)
+    done = {}
+    while engine.has_unfinished_requests():
+        for o in engine.step():
+            if o.finished:
+                done[int(o.request_id)] = o
+    res = []
+    for i in range(len(lens)):
+        c = done[i].outputs[0]
+        res.append({"tokens": list(c.token_ids), "logprobs": [next(iter(lp.values())).logprob for lp in c.logprobs]})
+    layers = mr.compilation_config.static_forward_context
+    attn = next(iter(layers.values()))
+    builders = [type(b).__name__ for grp in getattr(mr, "attn_groups", []) for g_ in grp for b in getattr(g_, "metadata_builders", [])]
+    from vllm_omni import plugins as omni_plugins
+    line = json.dumps({"backend": args.backend, "impl": type(attn.impl).__name__, "kv_cache_dtype": args.kv_cache_dtype,
+                       "graphs": args.graphs, "omni": True, "worker": type(worker).__name__,
+                       "model_runner": type(mr).__name__, "model": type(mr.model).__module__ + "." + type(mr.model).__name__,
+                       "model_config": type(engine.vllm_config.model_config).__name__,
+                       "metadata_builders": sorted(set(builders)), "omni_plugins_loaded": bool(omni_plugins.omni_plugins_loaded),
+                       "stubbed_imports": sorted(stubbed), "vllm_version_skew_adapters": skew,
+                       "results": res})
+    if args.out:
+        Path(args.out).write_text(line + "\n")
+    print(line, flush=True)
+
+
 def main():
     import torch
     from vllm import LLM, SamplingParams
 
+    if args.omni:
+        return run_omni()
     if args.backend == "CUSTOM":
         from vllm_omni_b200 import plugin
         plugin.register()

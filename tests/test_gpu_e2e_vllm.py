@@ -34,6 +34,25 @@ def stock_reference(tmp_path, *args):
     pytest.skip("no stock vLLM attention backend runs this configuration on this box")
 
 
+def logprob_floor(tmp_path, ref, *args):
+    """How far two STOCK backends sit from each other on the same weights and prompts (max |logprob difference|
+    over the tokens they agree on): the noise floor of a bf16 model under another summation order. None if only
+    one stock backend runs here."""
+    for be in STOCK:
+        if be == ref["backend"]:
+            continue
+        other, _ = run_engine(tmp_path, f"floor_{be}", "--backend", be, *args)
+        if other is not None:
+            worst = 0.0
+            for ra, rb in zip(ref["results"], other["results"]):
+                for i, (ta, tb) in enumerate(zip(ra["tokens"], rb["tokens"])):
+                    if ta != tb:
+                        break
+                    worst = max(worst, abs(ra["logprobs"][i] - rb["logprobs"][i]))
+            return worst
+    return None
+
+
 def compare(a, b, tol, min_equal):
     n = same = 0
     worst = 0.0
@@ -63,11 +82,17 @@ def test_custom_backend_matches_stock_backend_eager_and_graphs(lib, vllm_ok, tmp
     assert got["impl"] == "B200AttentionImpl"
     ref = stock_reference(tmp_path)
     assert ref["impl"] != "B200AttentionImpl"
-    compare(got, ref, tol=0.05, min_equal=0.9)
+    # tolerance: 0.05 on the chosen tokens' logprobs, or 1.5 x the distance between two stock backends when that is
+    # larger (a random-init bf16 model amplifies summation-order noise; measured 0.04-0.06 between FLASH_ATTN and
+    # FLASHINFER) — the kernel-level bound is the 2e-3 oracle test, this one is about the plumbing
+    floor = logprob_floor(tmp_path, ref)
+    tol = max(0.05, 1.5 * floor) if floor is not None else 0.08
+    print(f"stock-vs-stock logprob distance {floor}, tolerance {tol:.3f}")
+    print("eager:", compare(got, ref, tol=tol, min_equal=0.9))
     # decode replayed from CUDA graphs (FULL_DECODE_ONLY): no host sync / allocation in forward()
     got_g, err = run_engine(tmp_path, "custom_graphs", "--backend", "CUSTOM", "--graphs")
     assert got_g is not None, err
-    compare(got_g, ref, tol=0.05, min_equal=0.9)
+    print("graphs:", compare(got_g, ref, tol=tol, min_equal=0.9))
 
 
 @pytest.mark.timeout(2400)
