@@ -9,10 +9,12 @@ checked for agreement. Library kernels are comparators only; nothing here is on 
   python scripts/compare_vllm_backends.py [workload] [layers]   -> one JSON line per implementation
 """
 import json
+import os
 import sys
 from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+os.environ.setdefault("B200ATTN_PLAN_SK2", "1")   # the step's plan launch also makes the second-generation plan (comparison arm)
 import torch
 
 from vllm_omni_b200 import ops, workloads

@@ -63,8 +63,11 @@ def launches():
         for k, v in ours.items():
             med = sorted(v)[len(v) // 2]
             step[k] = [x for x in v if x < 8 * med] if "cache_write" in k else v
+        per_step = {k: v for k, v in step.items() if "_plan_kernel" in k}
+        step = {k: v for k, v in step.items() if "_plan_kernel" not in k}
         tot = sum(sum(v) / len(v) for v in step.values())
-        lines += ["", "Per-layer step (one launch of each of our kernels, setup-sized cache writes excluded):", ""]
+        lines += ["", "Once per step: " + ", ".join(f"`{k}` {sum(v)/len(v):.2f} us" for k, v in per_step.items()), "",
+                  "Per-layer step (one launch of each of our kernels, setup-sized cache writes excluded):", ""]
         for k, v in step.items():
             a = sum(v) / len(v)
             lines.append(f"- `{k}`: {a:.2f} us = {100*a/tot:.1f} % of the layer")
@@ -75,6 +78,15 @@ def launches():
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
+def kernel_sources_sha() -> str:
+    """Same digest as bench.py: a capture is only quoted as `roofline.traffic` while the kernel sources match."""
+    import hashlib
+    h = hashlib.sha256()
+    for name in ("paged_decode_sk3.cu", "sk_math.cuh", "decode_common.cuh", "ptx.cuh"):
+        h.update((ROOT / "vllm_omni_b200" / "csrc" / name).read_bytes())
+    return h.hexdigest()[:16]
+
+
 def record_traffic(workload, kernel, hdr, units, r):
     """profiles/traffic.json: measured DRAM bytes per launch of the dominant kernel (bench.py's roofline.traffic)."""
     tot = 0.0
@@ -83,7 +95,8 @@ def record_traffic(workload, kernel, hdr, units, r):
         tot += float(r[i]) * UNIT[units[i]]
     path = OUT / "traffic.json"
     d = json.loads(path.read_text()) if path.exists() else {}
-    d[workload] = {"kernel": kernel, "dram_bytes_per_launch": tot, "source": f"{tag}_prof_{workload}.ncu-rep"}
+    d[workload] = {"kernel": kernel, "dram_bytes_per_launch": tot, "source": f"{tag}_prof_{workload}.ncu-rep",
+                   "capture": f"{tag}_prof_{workload}.ncu-rep", "kernel_sources_sha": kernel_sources_sha()}
     path.write_text(json.dumps(d, indent=1, sort_keys=True) + "\n")
 
 
@@ -102,7 +115,7 @@ def ncu_reports():
                  "read with `ncu -i ... --page raw --csv`.", ""]
         for r in rows[2:]:
             name = short(r[hdr.index("Kernel Name")])
-            if "paged_decode_streamk_kernel" in name:
+            if "paged_decode_sk3_kernel" in name or "paged_decode_streamk_kernel" in name:
                 record_traffic(Path(f).stem.split("_prof_")[-1], name, hdr, units, r)
             lines += [f"## `{name}`", "", "| metric | value | unit |", "|---|---|---|"]
             for m in METRICS:
@@ -146,7 +159,7 @@ def sass():
 
 
 def copies():
-    for pat in ("sk_trace_*.log", "bench_*.json", "prefill_*.json", "compare_*.json", "scale_*.json"):
+    for pat in ("sk_trace_*.log", "bench_*.json", "prefill_*.json", "compare_*.json", "scale_*.json", "sweep_*.json"):
         for f in sorted(glob.glob(str(SRC / pat))):
             txt = open(f).read().strip()
             if txt:

@@ -70,12 +70,57 @@ def prefill(out_dir: Path):
         print(f"{name}: wrote out_fa2")
 
 
+FP8_CASES = {
+    # name: (seq_lens, hq, hkv, seed, k_scale, v_scale) — scalar scales: what the stock fp8 decode can express
+    "decode_fp8_32q4kv": ([130, 17, 1, 64, 300], 32, 4, 31, 0.5, 0.25),
+    "decode_fp8_16q2kv": ([48, 1, 15, 16, 150], 16, 2, 32, 1.0, 2.0),
+}
+
+
+def fp8(out_dir: Path):
+    """fp8-e4m3 KV cache with per-tensor scales: vLLM's fp8 `reshape_and_cache_flash` writes the cache bytes, FlashInfer's
+    TRT-LLM-gen decode (what vLLM's FLASHINFER backend runs for an fp8 cache, flashinfer.py:1694-1822) reads them.
+    Stored: the cache bytes (uint8) and the decode output, with the query dtype the stock kernel was given."""
+    from vllm import _custom_ops as vops
+    import flashinfer
+    for name, (lens, hq, hkv, seed, ks, vs) in FP8_CASES.items():
+        c = make_case(lens, hq=hq, hkv=hkv, seed=seed)
+        d, bs, nb = 128, c.block_size, c.num_blocks
+        kv = torch.zeros(2, nb, bs, hkv, d, dtype=torch.uint8, device="cuda")
+        kst = torch.full((1,), ks, dtype=torch.float32, device="cuda")
+        vst = torch.full((1,), vs, dtype=torch.float32, device="cuda")
+        vops.reshape_and_cache_flash(c.hist_k.cuda(), c.hist_v.cuda(), kv[0], kv[1], c.slots.cuda(), "fp8", kst, vst)
+        torch.cuda.synchronize()
+        rec = dict(q=bits(c.q), cache_vllm_fp8=kv.cpu().numpy(), block_table=c.block_table.numpy(),
+                   seq_lens=c.seq_lens.numpy(), scale=np.float32(c.scale), hq=hq, hkv=hkv, seed=seed,
+                   k_scale=np.float32(ks), v_scale=np.float32(vs))
+        q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
+        ws = torch.zeros(128 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+        k = kv[0].permute(0, 2, 1, 3).contiguous().view(torch.float8_e4m3fn)   # HND
+        v = kv[1].permute(0, 2, 1, 3).contiguous().view(torch.float8_e4m3fn)
+        for qname, qq, qs in (("bf16", q, 1.0), ("fp8", q.to(torch.float8_e4m3fn), 1.0)):
+            try:
+                out = torch.empty_like(q)
+                flashinfer.decode.trtllm_batch_decode_with_kv_cache(qq, (k, v), ws, bt, sl, c.max_seq_len,
+                                                                    bmm1_scale=c.scale * ks * qs, bmm2_scale=vs, out=out,
+                                                                    kv_layout="HND")
+                torch.cuda.synchronize()
+                rec[f"out_trtllm_q{qname}"] = bits(out)
+            except Exception as e:  # noqa: BLE001
+                print(f"{name}: trtllm-gen with {qname} q unavailable: {type(e).__name__}: {str(e)[:160]}")
+        np.savez_compressed(out_dir / f"vllm_{name}.npz", **rec)
+        print(f"{name}: wrote {sorted(k for k in rec if k.startswith('out_'))}")
+
+
 def main(out_dir: Path):
     out_dir.mkdir(parents=True, exist_ok=True)
     assert torch.cuda.is_available()
     if "--prefill-only" in sys.argv:
         return prefill(out_dir)
+    if "--fp8-only" in sys.argv:
+        return fp8(out_dir)
     prefill(out_dir)
+    fp8(out_dir)
     from vllm import _custom_ops as vops
     for name, (lens, hq, hkv, seed) in CASES.items():
         c = make_case(lens, hq=hq, hkv=hkv, seed=seed)

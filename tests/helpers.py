@@ -96,6 +96,17 @@ def excess_rel_err(x: torch.Tensor, ref: torch.Tensor) -> float:
     return float(err.max()) / float(ref.abs().max().clamp_min(1e-20))
 
 
+def row_excess_rel_err(x: torch.Tensor, ref: torch.Tensor) -> float:
+    """The same excess error, but every output row ([..., d]: one (sequence, head)) is divided by ITS OWN max|ref|,
+    so a row of small magnitude cannot hide behind a large one (max over rows)."""
+    x = x.detach().to(torch.float32).cpu()
+    ref = ref.detach().to(torch.float32).cpu()
+    err = ((x - ref).abs() - bf16_half_ulp(ref)).clamp_min(0)
+    scale = ref.abs().amax(dim=-1, keepdim=True)
+    ok = scale > 0
+    return float((err / scale.clamp_min(1e-30))[ok.expand_as(err)].max()) if bool(ok.any()) else 0.0
+
+
 def rel_l2(x: torch.Tensor, ref: torch.Tensor) -> float:
     x = x.detach().to(torch.float32).cpu()
     ref = ref.detach().to(torch.float32).cpu()

@@ -85,3 +85,47 @@ def test_prefill_oracle_within_tolerance_of_vllm_flash_attn(name):
     stock = bf16(z["out_fa2"])
     e, l2 = excess_rel_err(stock, ref), kernel_rel_l2(stock, ref)
     assert e <= 2e-3 and l2 <= 2e-3, (name, e, l2)
+
+
+# ------------------------------------------------------------------------------------------------
+# fp8-e4m3 KV cache, per-tensor scales (what the stock fp8 decode can express): the cache bytes written by vLLM's fp8
+# `reshape_and_cache_flash`, and FlashInfer's TRT-LLM-gen decode (bf16 query) reading them.
+# ------------------------------------------------------------------------------------------------
+FP8_FILES = ["vllm_decode_fp8_32q4kv.npz", "vllm_decode_fp8_16q2kv.npz"]
+
+
+def load_fp8(name):
+    p = GOLDEN / name
+    assert p.exists(), f"{p} missing: run tests/golden/gen_vllm_gpu_golden.py --fp8-only on a GPU box with vLLM"
+    z = np.load(p)
+    c = make_case(z["seq_lens"].tolist(), hq=int(z["hq"]), hkv=int(z["hkv"]), seed=int(z["seed"]))
+    ks = torch.full((1,), float(z["k_scale"]), dtype=torch.float32)
+    vs = torch.full((1,), float(z["v_scale"]), dtype=torch.float32)
+    return z, c, ks, vs
+
+
+@pytest.mark.parametrize("name", FP8_FILES)
+def test_fp8_slot_writes_equal_vllm_reshape_and_cache_flash(name):
+    """e4m3_satfinite(x / scale) of both oracle restatements, byte for byte against vLLM's CUDA kernel."""
+    z, c, ks, vs = load_fp8(name)
+    want = torch.from_numpy(z["cache_vllm_fp8"].copy())       # [2, nb, bs, Hkv, d] uint8
+    nb, bs, hkv, d = want.shape[1:]
+    for impl in (oracle.ref_reshape_and_cache, c_oracle.reshape_and_cache):
+        kv = torch.zeros(2, nb, bs, hkv, d, dtype=torch.uint8)
+        impl(c.hist_k, c.hist_v, kv[0], kv[1], c.slots, True, ks, vs)
+        assert torch.equal(kv, want), impl.__module__
+
+
+@pytest.mark.parametrize("name", FP8_FILES)
+def test_fp8_decode_oracle_within_tolerance_of_trtllm_gen(name):
+    """The oracle fed the dequantised fp8 cache against the stock fp8 decode (bf16 query, scalar k/v scales folded
+    into bmm1 / bmm2 exactly as vLLM's FLASHINFER backend passes them): the FP8 tolerance of this repo's tests —
+    2e-3 against the dequantised cache — is one the stock kernel meets too."""
+    z, c, ks, vs = load_fp8(name)
+    assert "out_trtllm_qbf16" in z.files
+    kv = torch.from_numpy(z["cache_vllm_fp8"].copy())
+    stock = bf16(z["out_trtllm_qbf16"])
+    for ref in (oracle.ref_paged_decode(c.q, kv[0], kv[1], c.block_table, c.seq_lens, float(z["scale"]), True, ks, vs)[0],
+                c_oracle.paged_decode(c.q, kv[0], kv[1], c.block_table, c.seq_lens, float(z["scale"]), True, ks, vs)[0]):
+        e, l2 = excess_rel_err(stock, ref), kernel_rel_l2(stock, ref)
+        assert e <= 2e-3 and l2 <= 2e-3, (name, e, l2)

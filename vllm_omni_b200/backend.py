@@ -55,7 +55,9 @@ class B200AttentionBackend(AttentionBackend):
 
     @staticmethod
     def get_supported_kernel_block_sizes() -> list[int | MultipleOf]:
-        return [MultipleOf(16)]
+        # 16-token tiles, 16 * 2^k tokens per page: what the stream-K schedules (the only ones with an fp8 path)
+        # index with shifts. Anything else would be refused at the first decode, so it is refused here, at start-up.
+        return [16, 32, 64, 128]
 
     @staticmethod
     def get_kv_cache_shape(num_blocks: int, block_size: int, num_kv_heads: int, head_size: int,

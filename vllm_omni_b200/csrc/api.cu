@@ -920,6 +920,8 @@ int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_h
                                          sk3_team_force(), static_cast<cudaStream_t>(stream)))
       return cuda_fail(e3, "decode plan launch");
   }
+  if (sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes && !env_flag("B200ATTN_PLAN_SK2", false))
+    return 0;  // the second-generation plan (40 us) is only made where that kernel is still compared
   cudaError_t e = launch_sk2_plan(seq_lens, batch, num_kv_heads * subgroups, sms, block_table, block_table_stride, tpp,
                                   shift, l.plan, l.ctrl, sk2_calib_max(), static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "decode plan launch");

@@ -244,7 +244,7 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
         int np = 1;
         for (int j = own + 1; j < nt && s_tstart[j] < i1; ++j) np += s_tstart[j + 1] > s_tstart[j] ? 1 : 0;
         info.x = own;
-        info.y = np;
+        info.y = np | (sk3_team_of(s_tstart, nt, i1 - 1) - own == np - 1 ? (1 << 30) : 0);
       }
       const int4 e = sk3_desc_of(cum_r, batch, hs_count, t1 - 1);
       const int i0 = t1 - 1 - e.z, i1 = i0 + e.w;
@@ -276,6 +276,7 @@ template <int W, int D, int SB>
 struct Sk3Smem {
   alignas(1024) uint8_t ring[W][D][SB];  // SB = bytes of one stage (K tile + V tile)
   alignas(8) uint64_t bar[W][D];         // "stage landed" mbarriers, one per ring slot
+  uint32_t qstage[W][16][32];            // per warp: q fragments of the item the front prepared (cp.async, no registers)
   float m[W][kHeadsPerItem];             // merge: reference max (log2 domain) of every warp's state ...
   float l[W][kHeadsPerItem];             // ... and its row sum
   int stash[W];                          // ring slot that holds the warp's accumulators during a merge
@@ -355,18 +356,26 @@ __device__ __forceinline__ void sk3_fold(Sk3Acc& s, const float4 o, float lo, fl
 }
 
 // Everything a team does at the end of a piece after the warps stashed their states: fold the T states per
-// head, then write the row / leave a partial / fold the neighbours' partials (see the file header).
-//   slot_of(team, owner_side): partial slot in the workspace; cnt: arrival counters (this launch's parity)
+// head, then write the row / leave a partial / fold the other pieces' partials (see the file header).
+// Partial slots [parity][2 * NTmax][8 heads][128]: slot `team` for a team's first piece when it continues an item,
+// slot NTmax + team for its last piece when it owns a cut item; arrival counters [parity][NTmax] by owner.
 struct Sk3MergeArgs {
   int b, hs;          // the item
   int first, last;    // the piece starts / ends the item
   int team, tw0, T, wi;
-  int own, np_first;  // tinfo.x, .y (continuation side)
-  int m_last, contig; // tinfo.z, .w (owner side)
+  int own, np_first;  // tinfo.x, .y: continuation side (owner team, pieces | all-teams-in-between-non-empty << 30)
+  int m_last, contig; // tinfo.z, .w: owner side
   int item_end;       // stream position behind the item
   int nt, ntmax;
-  int peek;           // owner side: arrival count seen when the piece began (warp 0 of the team)
+  int peek;           // arrival count of the item this warp saw shortly before the piece ended (-1: did not look)
 };
+
+struct Sk3Piece {  // one piece of a cut item as it sits in its slot: normalised row (4 columns per lane) + log2-domain LSE
+  float4 o;
+  float l2;
+};
+constexpr int kSk3FoldBatch = 2;  // partial loads in flight per lane while a cut item is folded
+constexpr int kSk3FoldEarly = 2;  // pieces of an item whose partials are asked for ahead of the team barrier (incl. the own one)
 
 template <int W, int D, int SB, bool FP8>
 __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>& sm, const Sk3MergeArgs a, int warp, int lane) {
@@ -378,18 +387,87 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
   const int32_t* const tstart = p.sk3_plan + sk3_plan_tstart_off();
   const bool whole = a.first && a.last;
   const bool owner = a.first && !a.last;  // cut at the end: the other pieces live in later teams
-  const int pieces = owner ? a.m_last + 1 : a.np_first;
+  const int pieces = owner ? a.m_last + 1 : (a.np_first & 0x3fffffff);
+  // the pieces are the owner's, then the next pieces - 1 teams, when no empty team sits between them (always, but
+  // for steps with fewer positions than warps)
+  const bool contig = owner ? a.contig != 0 : (a.np_first >> 30) != 0;
+  const int own = owner ? a.team : a.own;       // the team that holds the item's start: counter index, first slot
+  const int my_idx = owner ? 0 : a.team - own;  // (contig) this piece's place in the item
+  const int64_t my_slot = owner ? a.ntmax + a.team : a.team;
   const int kvh = a.hs / p.subgroups, sub = a.hs % p.subgroups;
-  if (owner && a.wi == 0 && lane == 0) {
-    // one thread decides for the team; its fence orders the neighbours' partials before everybody's loads
-    if (a.peek == pieces - 1) __threadfence();
-    sm.word[a.tw0] = a.peek;
+  auto slot_of = [&](int idx) -> int64_t { return idx == 0 ? a.ntmax + own : own + idx; };  // (contig)
+  auto load_piece = [&](int64_t slot, int h) {
+    Sk3Piece q;
+    q.o = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane);
+    q.l2 = __ldcg(part_l + slot * kHeadsPerItem + h);
+    return q;
+  };
+  // A piece that saw every other piece of its item arrived will finish the item: it asks for the first of their
+  // partials (for this warp's first head) before the team barrier, so the loads fly while the team assembles.
+  const bool saw_all = !whole && a.peek == pieces - 1;
+  const bool pre = saw_all && contig && a.wi < kHeadsPerItem;
+  Sk3Piece early[kSk3FoldEarly];
+  if (saw_all) __threadfence();  // orders the other pieces' partials before this thread's loads
+  if (pre) {
+#pragma unroll
+    for (int i = 0; i < kSk3FoldEarly; ++i)
+      if (i < pieces && i != my_idx) early[i] = load_piece(slot_of(i), a.wi);
   }
+  if (!whole && a.wi == 0 && lane == 0) sm.word[a.tw0] = a.peek;  // one thread decides for the team
   __syncwarp();
   named_bar_sync(bar_id, nthr);  // every state of the team is stashed
-  const bool fast = owner && sm.word[a.tw0] == pieces - 1;
+  // fast: every other piece had arrived when this team looked, so this team is the one that finishes the item
+  const bool fast = !whole && sm.word[a.tw0] == pieces - 1;
+  if (fast && !saw_all) __threadfence();
   float vs = 1.f;
   if (FP8) vs = __ldg(p.v_scale + kvh * p.scale_stride);
+  // The pieces of a cut item are always folded in the same order (the owner's, then the continuations by team) and
+  // form (normalised row + LSE), whoever does it and whether its own piece comes from registers or from its slot:
+  // the result does not depend on which team finished last.
+  auto fold_item = [&](Sk3Acc& s, int h, bool have_mine, const Sk3Piece& mine, bool have_early) {
+    s.a = make_float4(0.f, 0.f, 0.f, 0.f);
+    s.l = 0.f;
+    s.m = -CUDART_INF_F;
+    if (contig) {
+      for (int base = 0; base < pieces; base += kSk3FoldBatch) {
+        Sk3Piece q[kSk3FoldBatch];
+#pragma unroll
+        for (int i = 0; i < kSk3FoldBatch; ++i) {
+          const int idx = base + i;
+          if (idx >= pieces) continue;
+          if (have_mine && idx == my_idx) q[i] = mine;
+          else if (have_early && idx < kSk3FoldEarly) q[i] = early[i < kSk3FoldEarly ? i : 0];
+          else q[i] = load_piece(slot_of(idx), h);
+        }
+#pragma unroll
+        for (int i = 0; i < kSk3FoldBatch; ++i)
+          if (base + i < pieces) sk3_fold(s, q[i].o, 1.f, q[i].l2);
+      }
+      return;
+    }
+    {
+      const Sk3Piece q = (have_mine && owner) ? mine : load_piece(a.ntmax + own, h);
+      sk3_fold(s, q.o, 1.f, q.l2);
+    }
+    for (int j = own + 1; j < a.nt && __ldg(tstart + j) < a.item_end; ++j) {
+      if (!(__ldg(tstart + j + 1) > __ldg(tstart + j))) continue;
+      const Sk3Piece q = (have_mine && j == a.team) ? mine : load_piece(j, h);
+      sk3_fold(s, q.o, 1.f, q.l2);
+    }
+  };
+  auto write_row = [&](const Sk3Acc& s, int h) {
+    const int head_in_group = sub * kHeadsPerItem + h;
+    if (head_in_group >= p.group) return;
+    const int hq = kvh * p.group + head_in_group;
+    const float inv = s.l > 0.f ? vs / s.l : 0.f;
+    uint2 pk;
+    pk.x = pack_bf16x2(s.a.x * inv, s.a.y * inv);
+    pk.y = pack_bf16x2(s.a.z * inv, s.a.w * inv);
+    *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(a.b) * p.out_stride_tok + static_cast<int64_t>(hq) * kHeadDim +
+                              lane * 4) = pk;
+    if (p.lse != nullptr && lane == 0)
+      p.lse[static_cast<int64_t>(a.b) * p.num_q_heads + hq] = s.l > 0.f ? (s.m + log2f(s.l)) * kLn2 : -CUDART_INF_F;
+  };
   for (int h = a.wi; h < kHeadsPerItem; h += a.T) {
     Sk3Acc s;
     s.a = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -403,62 +481,36 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
                                                         h * kHeadDim + col);
       sk3_fold(s, v, sm.l[a.tw0 + k][h], mk);
     }
-    const int head_in_group = sub * kHeadsPerItem + h;
-    const bool head_ok = head_in_group < p.group;
-    const int hq = kvh * p.group + head_in_group;
-    if (fast) {  // the neighbours' partials are complete: (normalised row, log2-domain LSE) each
-      // the pieces of a cut item are folded in one order and one form (normalised row + LSE, the owner's first)
-      // whoever does it, so the result does not depend on which team happened to finish last
-      const float inv0 = s.l > 0.f ? 1.f / s.l : 0.f;
-      const float4 o0 = make_float4(s.a.x * inv0, s.a.y * inv0, s.a.z * inv0, s.a.w * inv0);
-      const float l0 = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
-      s.a = make_float4(0.f, 0.f, 0.f, 0.f);
-      s.l = 0.f;
-      s.m = -CUDART_INF_F;
-      sk3_fold(s, o0, 1.f, l0);
-      for (int j = a.team + 1, left = a.m_last; left > 0; ++j) {
-        if (!a.contig && !(__ldg(tstart + j + 1) > __ldg(tstart + j))) continue;
-        --left;
-        const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (static_cast<int64_t>(j) * kHeadsPerItem + h) * kHeadDim) + lane);
-        const float lj = __ldcg(part_l + static_cast<int64_t>(j) * kHeadsPerItem + h);
-        sk3_fold(s, o, 1.f, lj);
-      }
+    if (whole) {
+      write_row(s, h);
+      continue;
     }
-    const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
-    if (whole || fast) {
-      if (head_ok) {
-        uint2 pk;
-        pk.x = pack_bf16x2(s.a.x * inv * vs, s.a.y * inv * vs);
-        pk.y = pack_bf16x2(s.a.z * inv * vs, s.a.w * inv * vs);
-        *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(a.b) * p.out_stride_tok + static_cast<int64_t>(hq) * kHeadDim +
-                                  lane * 4) = pk;
-        if (p.lse != nullptr && lane == 0)
-          p.lse[static_cast<int64_t>(a.b) * p.num_q_heads + hq] = s.l > 0.f ? (s.m + log2f(s.l)) * kLn2 : -CUDART_INF_F;
-      }
+    Sk3Piece mine;  // this team's piece as it would sit in its slot
+    {
+      const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
+      mine.o = make_float4(s.a.x * inv, s.a.y * inv, s.a.z * inv, s.a.w * inv);
+      mine.l2 = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
+    }
+    if (fast) {
+      fold_item(s, h, true, mine, pre && h == a.wi);
+      write_row(s, h);
     } else {
-      const int64_t slot = owner ? a.ntmax + a.team : a.team;
-      *(reinterpret_cast<float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane) =
-          make_float4(s.a.x * inv, s.a.y * inv, s.a.z * inv, s.a.w * inv);
-      if (lane == 0) part_l[slot * kHeadsPerItem + h] = s.l > 0.f ? s.m + log2f(s.l) : -CUDART_INF_F;
+      *(reinterpret_cast<float4*>(part_o + (my_slot * kHeadsPerItem + h) * kHeadDim) + lane) = mine.o;
+      if (lane == 0) part_l[my_slot * kHeadsPerItem + h] = mine.l2;
     }
   }
-  if (whole) {
+  if (whole || fast) {
+    if (fast && a.wi == 0 && lane == 0) cnt[own] = 0;  // ready for the launch after the next
     fence_proxy_async_smem();
     named_bar_sync(bar_id, nthr);  // the stash slots may be refilled
     return;
   }
-  const int own = owner ? a.team : a.own;
-  if (fast) {
-    if (a.wi == 0 && lane == 0) cnt[own] = 0;  // ready for the launch after the next
-    fence_proxy_async_smem();
-    named_bar_sync(bar_id, nthr);
-    return;
-  }
-  // a partial was written: announce it; the last arriver of the item folds all of them
+  // a partial was written: one thread announces it (the barrier makes the team's stores visible to it, its fence to
+  // the device); the last arriver of the item folds all of them
   fence_proxy_async_smem();
-  __threadfence();
   named_bar_sync(bar_id, nthr);
   if (a.wi == 0 && lane == 0) {
+    __threadfence();
     const int old = atomicAdd(cnt + own, 1);
     if (old == pieces - 1) __threadfence();
     sm.word2[a.tw0] = old;
@@ -467,31 +519,11 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
   if (sm.word2[a.tw0] != pieces - 1) return;
   for (int h = a.wi; h < kHeadsPerItem; h += a.T) {
     Sk3Acc s;
-    s.a = make_float4(0.f, 0.f, 0.f, 0.f);
-    s.l = 0.f;
-    s.m = -CUDART_INF_F;
-    {
-      const int64_t slot = a.ntmax + own;
-      const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (slot * kHeadsPerItem + h) * kHeadDim) + lane);
-      sk3_fold(s, o, 1.f, __ldcg(part_l + slot * kHeadsPerItem + h));
-    }
-    for (int j = own + 1; j < a.nt && __ldg(tstart + j) < a.item_end; ++j) {
-      if (!(__ldg(tstart + j + 1) > __ldg(tstart + j))) continue;
-      const float4 o = __ldcg(reinterpret_cast<const float4*>(part_o + (static_cast<int64_t>(j) * kHeadsPerItem + h) * kHeadDim) + lane);
-      sk3_fold(s, o, 1.f, __ldcg(part_l + static_cast<int64_t>(j) * kHeadsPerItem + h));
-    }
-    const int head_in_group = sub * kHeadsPerItem + h;
-    if (head_in_group < p.group) {
-      const int hq = kvh * p.group + head_in_group;
-      const float inv = s.l > 0.f ? 1.f / s.l : 0.f;
-      uint2 pk;
-      pk.x = pack_bf16x2(s.a.x * inv * vs, s.a.y * inv * vs);
-      pk.y = pack_bf16x2(s.a.z * inv * vs, s.a.w * inv * vs);
-      *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(a.b) * p.out_stride_tok + static_cast<int64_t>(hq) * kHeadDim +
-                                lane * 4) = pk;
-      if (p.lse != nullptr && lane == 0)
-        p.lse[static_cast<int64_t>(a.b) * p.num_q_heads + hq] = s.l > 0.f ? (s.m + log2f(s.l)) * kLn2 : -CUDART_INF_F;
-    }
+    Sk3Piece none;
+    none.o = make_float4(0.f, 0.f, 0.f, 0.f);
+    none.l2 = 0.f;
+    fold_item(s, h, false, none, false);
+    write_row(s, h);
   }
   if (a.wi == 0 && lane == 0) cnt[own] = 0;
 }
@@ -609,38 +641,53 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   uint32_t cphase = 0;  // parity of the current pass over the ring
   bool have_item = false, got = false, first_landed = false;
   int peek = -1;
-  uint32_t qf[8][2], qf_n[8][2];
+  uint32_t qf[8][2];
 #pragma unroll
-  for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = qf_n[kk][0] = qf_n[kk][1] = 0u;
+  for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = 0u;
   float scale = p.scale_log2, scale_n = p.scale_log2;
   int slen = 0, slen_n = 0;
   WarpState st;
   state_reset(st);
 
-  auto load_q_next = [&]() {  // q (and the K scale) of the item the front prepared last
-    WorkItem w;
-    w.b = it_b;
-    w.kvh = it_hs / p.subgroups;
-    w.sub = it_hs % p.subgroups;
-    if (FP8) {
-      sk_load_q_f16(p, w.b, w.kvh, w.sub, lane, qf_n);
-      scale_n = p.scale_log2 * __ldg(p.k_scale + w.kvh * p.scale_stride);
+  // q (and the K scale) of the item the front prepared last: the words of this lane's B fragments go from global
+  // to the warp's staging row with cp.async (no registers held while the math is still on the previous item) — the
+  // math takes them when it gets to the item.
+  // bf16: qf[kk][i] = Q[head g][16 kk + 2 t + 8 i, +1]; fp8 (f16 MMAs, permuted k): Q[head g][16 kk + 4 t + 2 i, +1]
+  auto load_q_next = [&]() {
+    const int g = lane >> 2, t = lane & 3;
+    const int kvh = it_hs / p.subgroups, sub = it_hs % p.subgroups;
+    const int head_in_group = sub * kHeadsPerItem + g;
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(p.q + static_cast<int64_t>(it_b) * p.q_stride_tok +
+                                                            static_cast<int64_t>(kvh * p.group + head_in_group) * kHeadDim);
+    const uint32_t dst = smem_u32(&sm.qstage[warp][0][lane]);
+    if (head_in_group < p.group) {
+#pragma unroll
+      for (int kk = 0; kk < 8; ++kk)
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          cp_async_4(dst + (kk * 2 + i) * 128, row + kk * 8 + (FP8 ? 2 * t + i : t + 4 * i));
     } else {
-      load_q_frags(p, w, lane, qf_n);
+#pragma unroll
+      for (int w = 0; w < 16; ++w) sm.qstage[warp][w][lane] = 0u;
     }
+    if (FP8) scale_n = p.scale_log2 * __ldg(p.k_scale + kvh * p.scale_stride);
   };
 
   while (piece_begin < t_end) {
     const int item_end = item_pos0 + mn;
     const int piece_end = min(item_end, t_end);
-    // the owner of a cut item looks at the arrival counter a few tiles before it ends its piece (the answer is in
-    // a register before the merge needs it)
-    if (peek < 0 && wi == 0 && ti.z > 0 && piece_begin == item_pos0 && item_end > t_end && mp + 3 * T >= piece_end)
-      peek = sk3_ld_relaxed(p.sk3_cnt + parity * ntmax + team) & 0x7fffffff;
+    // a piece of a cut item looks at the item's arrival counter a few tiles before it ends (the answer is in a
+    // register before the merge needs it)
+    if (peek < 0 && mp + 3 * T >= piece_end) {
+      if (piece_begin > item_pos0)
+        peek = sk3_ld_relaxed(p.sk3_cnt + parity * ntmax + ti.x) & 0x7fffffff;   // the piece continues an item
+      else if (item_end > t_end)
+        peek = sk3_ld_relaxed(p.sk3_cnt + parity * ntmax + team) & 0x7fffffff;   // it owns a cut item
+    }
     // ================= keep the ring full =================
     while (pending < D && pf_left > 0) {
       if (pf_fresh) {
-        // first tile (of this warp) in an item: qf_n holds one prepared item, so the front never runs two item
+        // first tile (of this warp) in an item: the staging row holds one prepared item, so the front never runs two item
         // starts ahead of the math
         if (pf_items_ahead == 1) break;
         it_b = pf.b;
@@ -694,11 +741,14 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     int ds = cslot;
     if (mp < piece_end) {
       if (!have_item) {  // take the item the front prepared
+        cp_async_wait_all();  // this lane's own words (nobody else reads them)
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          qf[kk][0] = qf_n[kk][0];
-          qf[kk][1] = qf_n[kk][1];
-        }
+        for (int kk = 0; kk < 8; ++kk)
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const uint32_t raw = sm.qstage[warp][kk * 2 + i][lane];  // two bf16
+            qf[kk][i] = FP8 ? pack_f16x2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u)) : raw;
+          }
         scale = scale_n;
         slen = slen_n;
         pf_items_ahead = 0;
@@ -778,7 +828,12 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       sk3_merge<W, D, SB, FP8>(p, sm, a, warp, lane);
       state_reset(st);
       got = false;
-      have_item = false;
+      have_item = false;  // (nothing of the item is kept across the merge: the next piece takes its own q)
+#pragma unroll
+      for (int kk = 0; kk < 8; ++kk) qf[kk][0] = qf[kk][1] = 0u;
+      scale = p.scale_log2;
+      slen = 0;
+      peek = -1;
     }
     piece_begin = piece_end;
     if (piece_end == item_end && piece_begin < t_end) {  // next item of the team's range
