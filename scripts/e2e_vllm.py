@@ -25,6 +25,9 @@ ap.add_argument("--layers", type=int, default=4)
 ap.add_argument("--omni", action="store_true",
                 help="run inside vllm-omni: the reference's OmniEngineArgs (its plugin loader finds this repo's entry "
                      "point), GPUARWorker / GPUARModelRunner, and its own Qwen2 decoder (qwen2_old.py) as the model")
+ap.add_argument("--kv-scales", default="", help="with --omni: 'per-head' = the decoder is built with a compressed-tensors "
+                "KV-cache scheme (strategy attn_head) routed through the reference's ComponentQuantizationConfig, and "
+                "its per-KV-head k/v scales are set to very different values per head")
 ap.add_argument("--out", default="")
 args = ap.parse_args()
 
@@ -68,7 +71,15 @@ def run_omni():
     for reg in (OmniModelRegistry, ModelRegistry):   # (the reference mirrors its own models into vLLM's registry too)
         reg.register_model("B200ThinkerStandIn", "tests.omni_standin:ThinkerStandIn")
     d = tempfile.mkdtemp(prefix="tiny_qwen2_old_")
-    Path(d, "config.json").write_text(json.dumps(OMNI_CONFIG))
+    cfg = dict(OMNI_CONFIG)
+    per_head = args.kv_scales == "per-head"
+    if per_head:
+        # what an llm-compressor checkpoint with an fp8 KV cache and one scale per attention head declares
+        cfg["quantization_config"] = {
+            "quant_method": "compressed-tensors", "format": "dense", "config_groups": {}, "ignore": [],
+            "kv_cache_scheme": {"num_bits": 8, "type": "float", "strategy": "attn_head", "symmetric": True,
+                                "dynamic": False}}
+    Path(d, "config.json").write_text(json.dumps(cfg))
     # stage engine_args as a stage YAML would give them (qwen3_omni_moe.yaml:14-27), with the backend knob
     stage_args = dict(model=d, load_format="dummy", skip_tokenizer_init=True, dtype="bfloat16", max_model_len=2048,
                       gpu_memory_utilization=0.15, kv_cache_dtype=args.kv_cache_dtype, seed=0, max_num_seqs=16,
@@ -97,7 +108,22 @@ def run_omni():
         GPUARModelRunner._bookkeeping_sync = lambda self, *a: base_sync(self, *a[:5])
         skew.append("_bookkeeping_sync(spec_decode_metadata dropped)")
     engine_args = OmniEngineArgs(**stage_args)   # __post_init__ runs vllm_omni.plugins.load_omni_general_plugins()
-    engine = LLMEngine.from_engine_args(engine_args)
+    routed = None
+    if per_head:
+        # vllm_omni/quantization: per-component routing by longest layer-name prefix (component_config.py:63-82);
+        # the decoder lives under "model.", so its attention layers resolve to the checkpoint's config and
+        # everything else (lm_head) to "no quantisation"
+        from vllm.usage.usage_lib import UsageContext
+        from vllm_omni.quantization.component_config import ComponentQuantizationConfig
+        vllm_config = engine_args.create_engine_config(UsageContext.LLM_CLASS)
+        inner = vllm_config.quant_config
+        assert inner is not None and getattr(inner, "kv_cache_scheme", None), "checkpoint KV-cache scheme was not parsed"
+        vllm_config.quant_config = ComponentQuantizationConfig({"model": inner}, default_config=None)
+        routed = {"attn": type(vllm_config.quant_config.resolve("model.layers.0.self_attn.attn")).__name__,
+                  "lm_head": type(vllm_config.quant_config.resolve("lm_head")).__name__}
+        engine = LLMEngine.from_vllm_config(vllm_config, UsageContext.LLM_CLASS)
+    else:
+        engine = LLMEngine.from_engine_args(engine_args)
     worker = engine.engine_core.engine_core.model_executor.driver_worker.worker
     mr = worker.model_runner
     gen = torch.Generator(device="cuda").manual_seed(1234)
@@ -109,6 +135,18 @@ def run_omni():
                 prm.zero_()                                   # qkv bias
             else:
                 prm.copy_((torch.randn(prm.shape, generator=gen, device="cuda") * 0.03).to(prm.dtype))
+    scales = None
+    if per_head:
+        # the scales a checkpoint would carry, one per KV head and very different between the heads: reading the
+        # wrong head's scale is a 16x error in that head's scores / values
+        ks = torch.tensor([0.25, 4.0], device="cuda")
+        vs = torch.tensor([4.0, 0.25], device="cuda")
+        for layer in mr.compilation_config.static_forward_context.values():
+            assert layer._k_scale.numel() == 2 and layer._v_scale.numel() == 2, "per-head scales did not reach the layer"
+            with torch.no_grad():
+                layer._k_scale.copy_(ks)
+                layer._v_scale.copy_(vs)
+        scales = {"k": ks.tolist(), "v": vs.tolist()}
     g = torch.Generator().manual_seed(0)
     lens = [5, 37, 130, 1, 700, 64, 33]
     sp = SamplingParams(temperature=0.0, max_tokens=args.max_tokens, logprobs=1, detokenize=False, ignore_eos=True)
@@ -133,6 +171,8 @@ def run_omni():
                        "model_config": type(engine.vllm_config.model_config).__name__,
                        "metadata_builders": sorted(set(builders)), "omni_plugins_loaded": bool(omni_plugins.omni_plugins_loaded),
                        "stubbed_imports": sorted(stubbed), "vllm_version_skew_adapters": skew,
+                       "quant_routing": routed, "kv_scales": scales,
+                       "impl_scale_numel": getattr(attn.impl, "last_scale_numel", None),
                        "results": res})
     if args.out:
         Path(args.out).write_text(line + "\n")

@@ -52,3 +52,24 @@ def test_backend_under_the_reference_worker_and_model_runner(lib, omni_ok, tmp_p
     print(f"vllm-omni runner, graphs={graphs}: {same}/{n} greedy tokens equal, max logprob difference {worst:.4f}; "
           f"stand-ins for missing imports: {got['stubbed_imports']}; vLLM version-skew adapters: "
           f"{got['vllm_version_skew_adapters']}")
+
+
+@pytest.mark.timeout(2400)
+def test_per_head_fp8_scales_through_the_reference_quant_routing(lib, omni_ok, tmp_path):
+    """a checkpoint-style compressed-tensors KV-cache scheme (fp8, strategy attn_head) is routed by
+    the reference's `ComponentQuantizationConfig` (vllm_omni/quantization/component_config.py:63-82: longest layer-name
+    prefix; "model." -> the checkpoint's config, everything else -> none) to vLLM's KV-cache method, which gives every
+    attention layer `[Hkv]` k/v scales; `B200AttentionImpl` must receive them as such (`scale_numel == Hkv`) and use
+    the right head's scale: the two heads' scales differ by 16x (k 0.25 / 4.0, v 4.0 / 0.25), so indexing them wrongly
+    destroys the output, while indexing them rightly leaves the usual fp8-vs-bf16 distance."""
+    got, err = run_engine(tmp_path, "omni_perhead", "--omni", "--backend", "CUSTOM", "--kv-cache-dtype", "fp8",
+                          "--kv-scales", "per-head")
+    assert got is not None, err
+    assert got["impl"] == "B200AttentionImpl" and got["model_runner"] == "GPUARModelRunner"
+    assert got["quant_routing"] == {"attn": "CompressedTensorsConfig", "lm_head": "NoneType"}
+    assert got["impl_scale_numel"] == 2 and got["kv_scales"] == {"k": [0.25, 4.0], "v": [4.0, 0.25]}
+    ref, err = run_engine(tmp_path, "omni_bf16", "--omni", "--backend", "CUSTOM")
+    assert ref is not None, err
+    same, n, worst = compare(got, ref, tol=0.4, min_equal=0.6)
+    print(f"per-head fp8 cache vs bf16 cache under the reference's runner: {same}/{n} greedy tokens, "
+          f"max logprob difference {worst:.3f}")

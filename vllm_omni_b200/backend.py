@@ -276,6 +276,7 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         out = output.view(-1, self.num_heads, self.head_size)
         k_scale = getattr(layer, "_k_scale", None)
         v_scale = getattr(layer, "_v_scale", None)
+        self.last_scale_numel = None if k_scale is None else int(k_scale.numel())   # 1 = per tensor, Hkv = per head
         nd, ndt = md.num_decodes, md.num_decode_tokens
         if nd > 0 and self.replica_split is not None:
             rs = self.replica_split
