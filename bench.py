@@ -798,7 +798,7 @@ def run_e2e(args, arm: Arm):
     B, hq, hkv, d, L = arm.B, arm.hq, arm.hkv, arm.d, arm.L
     impl = be.B200AttentionImpl(hq, d, inp.softmax_scale, hkv, None, None, wl.kv_cache_dtype)
     if arm.rs is not None:
-        impl.enable_replica_split(arm.rs)
+        impl.enable_replica_split(arm.rs, B)   # staging buffers sized once, outside the captured region
     qsl = torch.arange(B + 1, dtype=torch.int32, device="cuda")
     md = be.B200AttentionMetadata(
         num_actual_tokens=B, max_query_len=1, query_start_loc=qsl, max_seq_len=inp.max_seq_len,

@@ -140,3 +140,38 @@ def test_peer_exchange_matches_replica_split_indexing(lib, R, batch):
             assert torch.equal(ex.out.cpu(), qs[i].float().mul(2 + it).to(torch.bfloat16)), f"scatter differs on rank {i}"
             off = peer.ERROR_WORDS_OFFSET
             assert ex.mem.local[off: off + 16].view(torch.int32).tolist() == [0, 0, 0, 0]
+
+
+def test_exchange_serves_smaller_live_batches(lib):
+    """A serving process sizes the exchange once (max_num_seqs) and then decodes batches of any smaller size: the
+    rows, the split and the padding follow the LIVE batch (all ranks pass the same one)."""
+    R, hq, d, cap = 2, 4, 128, 11
+    exs = peer.PeerExchange.local_ranks(R, cap, hq, d, timeout_s=5.0)
+    streams = [torch.cuda.Stream() for _ in exs]
+    for ex in exs:                                   # load torch's kernels with nothing spinning (see above)
+        ex.out_grp.copy_(ex.q_grp)
+        ex.out_grp.mul_(1)
+    torch.cuda.synchronize()
+    with pytest.raises(ValueError):
+        exs[0].split(cap + 1)
+    for it, n in enumerate((cap, 5, 8, 1)):
+        g = torch.Generator().manual_seed(1000 + n)
+        qs = [torch.randn(n, hq, d, generator=g).to(torch.bfloat16) for _ in range(R)]
+        for ex, q in zip(exs, qs):
+            ex.q[:n].copy_(q.cuda())
+        torch.cuda.synchronize()
+        for phase in (0, 1):
+            for ex, s in zip(exs, streams):
+                with torch.cuda.stream(s):
+                    if phase == 0:
+                        ex.gather_q(n)
+                    else:
+                        ex.out_grp.copy_(ex.q_grp)
+                        ex.out_grp.mul_(3)
+                        ex.scatter_out(n)
+            torch.cuda.synchronize()
+        for i, ex in enumerate(exs):
+            per, b0, b1 = ex.split(n)
+            want = torch.stack([q[b0:b1] for q in qs], dim=1).reshape(b1 - b0, R * hq, d)
+            assert torch.equal(ex.q_grp[:b1 - b0].cpu(), want), f"gather differs on rank {i} at batch {n}"
+            assert torch.equal(ex.out[:n].cpu(), qs[i].float().mul(3).to(torch.bfloat16)), f"scatter, rank {i}, batch {n}"

@@ -141,6 +141,20 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             s = ops.decode_num_splits(b, self.num_heads_q, self.num_heads_kv, self.max_model_len, self._sms)
             nbytes = max(nbytes, ops.decode_workspace_bytes(b, self.num_heads_q, self.head_size, s))
         self.workspace = ops.DecodeWorkspace(device, nbytes)
+        # KV head replicated on several TP ranks (tp > total KV heads): optionally split the batch inside the replica
+        # group instead (tp.ReplicaSplit, opt-in: B200ATTN_REPLICA_SPLIT=1); built once per worker from vLLM's TP
+        # group and handed to this builder's layers, staging buffers sized for max_num_seqs here, outside any graph
+        from . import tp as _tp
+        try:
+            rs = _tp.replica_split_for_vllm(vllm_config, self.max_num_seqs)
+        except Exception:  # noqa: BLE001 - no distributed environment (single-process tests): nothing to split
+            rs = None
+        if rs is not None:
+            ctx = vllm_config.compilation_config.static_forward_context
+            for name in layer_names:
+                impl = getattr(ctx.get(name), "impl", None)
+                if isinstance(impl, B200AttentionImpl):
+                    impl.enable_replica_split(rs, self.max_num_seqs)
 
     def build(self, common_prefix_len: int, common_attn_metadata: CommonAttentionMetadata,
               fast_build: bool = False) -> B200AttentionMetadata:
@@ -216,11 +230,25 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         # optional: batch split inside a KV-head replica group (tp > total_kv_heads), see tp.ReplicaSplit
         self.replica_split = None
         self._split_ws: ops.DecodeWorkspace | None = None
+        self._split_q = self._split_out = None
 
-    def enable_replica_split(self, replica_split) -> None:
+    def enable_replica_split(self, replica_split, max_batch: int = 0) -> None:
         """Serve decode rows with the batch split over the ranks that replicate this KV head instead of
-        every rank streaming the whole head (tp.ReplicaSplit; identical results, 1/R of the KV bytes)."""
+        every rank streaming the whole head (tp.ReplicaSplit; identical results, 1/R of the KV bytes).
+        `max_batch` > 0 sizes the staging buffers and the decode workspace now (nothing is allocated in forward(),
+        which may run under CUDA-graph capture); the live decode batch may then be anything up to it."""
         self.replica_split = replica_split
+        self._split_q = self._split_out = None
+        if max_batch > 0:
+            rs = replica_split
+            per = -(-max_batch // rs.R)
+            ex = rs.exchange
+            dev = ex.q_grp.device if ex is not None else torch.device("cuda", torch.cuda.current_device())
+            if ex is None:
+                self._split_q = torch.zeros(per, rs.group_q_heads, self.head_size, dtype=torch.bfloat16, device=dev)
+            self._split_out = (ex.out_grp if ex is not None else
+                               torch.zeros(per, rs.group_q_heads, self.head_size, dtype=torch.bfloat16, device=dev))
+            self._split_ws = ops.DecodeWorkspace(dev, ops.decode_workspace_bytes(per, rs.group_q_heads, self.head_size, 1))
 
     # ------------------------------------------------------------------ cache write
     def do_kv_cache_update(self, layer, key: torch.Tensor, value: torch.Tensor,
@@ -281,8 +309,13 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         if nd > 0 and self.replica_split is not None:
             rs = self.replica_split
             per, b0, b1 = rs.plan(nd)
-            q_grp = rs.gather_q(q[:ndt])
-            out_grp = torch.zeros_like(q_grp) if b1 - b0 < per else torch.empty_like(q_grp)
+            q_grp = rs.gather_q(q[:ndt], out=None if self._split_q is None else self._split_q[:per])
+            if self._split_out is not None:      # preallocated (enable_replica_split(max_batch)): nothing allocated here
+                out_grp = self._split_out[:per]
+                if b1 - b0 < per:
+                    out_grp[b1 - b0:].zero_()
+            else:
+                out_grp = torch.zeros_like(q_grp) if b1 - b0 < per else torch.empty_like(q_grp)
             if b1 > b0:
                 if self._split_ws is None:  # sized for the group's head count, batch-independent (stream-K)
                     self._split_ws = ops.DecodeWorkspace(q.device, ops.decode_workspace_bytes(

@@ -315,16 +315,27 @@ class PeerExchange:
     def local_ranks(cls, R: int, batch: int, hq: int, d: int, device="cuda", **kw):
         return [cls(m, batch, hq, d, **kw) for m in PeerMemory.local_ranks(R, cls.layout(batch, hq, d)[2], device)]
 
-    def _run(self, ptrs, local, scatter: int):
+    def split(self, batch: int | None = None) -> tuple[int, int, int]:
+        """(rows per rank incl. padding, first local row, one past the last) for a live batch <= the one sized for."""
+        n = self.batch if batch is None else int(batch)
+        if n > self.batch:
+            raise ValueError(f"exchange was sized for batch {self.batch}, got {n}")
+        per = -(-n // self.R)
+        b0 = min(n, self.index * per)
+        return per, b0, min(n, b0 + per)
+
+    def _run(self, ptrs, local, scatter: int, batch: int | None):
+        per, b0, b1 = self.split(batch)
         stream = torch.cuda.current_stream(local.device).cuda_stream
         _lib.check("b200attn_peer_exchange", self.lib.b200attn_peer_exchange(
-            ptrs, self._flags, local.data_ptr(), self.R, self.index, self.b0, self.b1 - self.b0, self.per,
+            ptrs, self._flags, local.data_ptr(), self.R, self.index, b0, b1 - b0, per,
             self.row_bytes, scatter, self.timeout_ns, stream))
 
-    def gather_q(self) -> torch.Tensor:
-        self._run(self._q, self.q_grp, 0)
+    def gather_q(self, batch: int | None = None) -> torch.Tensor:
+        """All ranks of the group call it with the same live batch (rows [0, batch) of `q` are exchanged)."""
+        self._run(self._q, self.q_grp, 0, batch)
         return self.q_grp
 
-    def scatter_out(self) -> torch.Tensor:
-        self._run(self._out, self.out_grp, 1)
+    def scatter_out(self, batch: int | None = None) -> torch.Tensor:
+        self._run(self._out, self.out_grp, 1, batch)
         return self.out

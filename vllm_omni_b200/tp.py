@@ -109,11 +109,10 @@ class ReplicaSplit:
         per, _, _ = self.plan(q.shape[0])
         ex = self.exchange
         if ex is not None:
-            if q.shape[0] != ex.batch:
-                raise ValueError(f"exchange was sized for batch {ex.batch}, got {q.shape[0]}")
+            n = q.shape[0]                      # the live batch: anything up to the size the exchange was made for
             if q.data_ptr() != ex.q.data_ptr():
-                ex.q.copy_(q)
-            res = ex.gather_q()
+                ex.q[:n].copy_(q)
+            res = ex.gather_q(n)[:per]
             if out is not None and out.data_ptr() != res.data_ptr():
                 out.copy_(res)
                 return out
@@ -136,7 +135,7 @@ class ReplicaSplit:
         if ex is not None:
             if out_local.data_ptr() != ex.out_grp.data_ptr():
                 ex.out_grp[:out_local.shape[0]].copy_(out_local)
-            res = ex.scatter_out()
+            res = ex.scatter_out(batch)[:batch]
             if out is not None and out.data_ptr() != res.data_ptr():
                 out.copy_(res)
                 return out
@@ -149,3 +148,38 @@ class ReplicaSplit:
             out.copy_(res)
             return out
         return res
+
+
+
+def replica_split_for_vllm(vllm_config, max_num_seqs: int | None = None):
+    """Build the `ReplicaSplit` (+ peer-memory exchange) of THIS worker from vLLM's tensor-parallel group — the place
+    the reference initialises TP is `GPUARWorker.init_device` (vllm_omni/worker/gpu_ar_worker.py:69-75, vLLM's
+    `init_worker_distributed_environment`); this is called afterwards, from the metadata builder, once per worker.
+    Returns None when no KV head is replicated (tp <= total_kv_heads) or the opt-in `B200ATTN_REPLICA_SPLIT` is off:
+    the reference rule (every rank of a replica group streams the whole KV head) stays the default."""
+    import os
+    if os.environ.get("B200ATTN_REPLICA_SPLIT", "0") in ("", "0"):
+        return None
+    from vllm.distributed import get_tensor_model_parallel_rank, get_tp_group
+    mc, pc = vllm_config.model_config, vllm_config.parallel_config
+    tp = pc.tensor_parallel_size
+    total_kv = mc.get_total_num_kv_heads()
+    if tp <= total_kv:
+        return None
+    import torch.distributed as dist
+    rank = get_tensor_model_parallel_rank()
+    shard = shard_heads(mc.hf_text_config.num_attention_heads, total_kv, tp, rank)
+    tp_ranks = get_tp_group().ranks                       # global ranks of this TP group, in TP order
+    my_group = None
+    for grp in ReplicaSplit.groups(tp, shard.kv_replicas):  # every rank creates every group, in the same order
+        g = dist.new_group([tp_ranks[i] for i in grp])
+        if rank in grp:
+            my_group = g
+    exchange = None
+    try:
+        from . import peer
+        n = max_num_seqs or vllm_config.scheduler_config.max_num_seqs
+        exchange = peer.PeerExchange.create(my_group, n, shard.num_q_heads, mc.get_head_size())
+    except Exception:  # noqa: BLE001 - NCCL all_to_all is the documented fallback of ReplicaSplit
+        exchange = None
+    return ReplicaSplit(shard, my_group, exchange=exchange)
