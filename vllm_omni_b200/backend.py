@@ -136,11 +136,10 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.max_model_len = mc.max_model_len
         self.max_num_seqs = vllm_config.scheduler_config.max_num_seqs
         self._sms = ops.num_sms()
-        nbytes = 0
-        for b in _batch_sizes(self.max_num_seqs):
-            s = ops.decode_num_splits(b, self.num_heads_q, self.num_heads_kv, self.max_model_len, self._sms)
-            nbytes = max(nbytes, ops.decode_workspace_bytes(b, self.num_heads_q, self.head_size, s))
-        self.workspace = ops.DecodeWorkspace(device, nbytes)
+        # the stream-K schedules' workspace is batch-independent apart from the plan's [batch + 1] prefix; the
+        # fixed-split fallback (only taken when stream-K does not fit, i.e. never with this size) is not provisioned
+        self.workspace = ops.DecodeWorkspace(device, ops.decode_workspace_bytes(
+            max(1, self.max_num_seqs), self.num_heads_q, self.head_size, 1))
         # KV head replicated on several TP ranks (tp > total KV heads): optionally split the batch inside the replica
         # group instead (tp.ReplicaSplit, opt-in: B200ATTN_REPLICA_SPLIT=1); built once per worker from vLLM's TP
         # group and handed to this builder's layers, staging buffers sized for max_num_seqs here, outside any graph
