@@ -397,6 +397,11 @@ B200ATTN_API void b200attn_debug_set_trace(void* device_buffer);
  */
 B200ATTN_API void b200attn_debug_set_team(int32_t warps);
 
+/* TMA tensor maps this thread has encoded so far. The library caches one map per (cache pointer, strides, shape) in a
+ * 1024-entry 4-way table; in steady state (the layers' caches do not move) this number stops growing — a caller that
+ * sees it grow per step is re-encoding maps on the host at every launch. */
+B200ATTN_API uint64_t b200attn_debug_map_encodes(void);
+
 /* Byte offset, inside a decode workspace, of the plan b200attn_decode_plan writes for (batch, num_q_heads)
  * on the current device (int32 words: header 16 {positions, CTAs G, team size T, teams, batch, head groups,
  * 0, magic, teams per CTA} | team starts [12 G + 1, padded to 4] | team descriptors [12 G][4] | team info

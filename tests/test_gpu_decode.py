@@ -553,3 +553,22 @@ def test_sk3_plan_contents(lib):
         for own, lst in conts.items():
             assert plan["tinfo"][own][2] == len(lst), (own, lst, plan["tinfo"][own])
             assert plan["tinfo"][lst[0]][1] & 0x3FFFFFFF == len(lst) + 1
+
+
+def test_tensor_map_cache_holds_a_models_layers(lib):
+    """One TMA tensor map per (layer cache, K | V): after the first step over 64 layer caches no map is encoded again
+    (the table is set-associative; round 1's direct-mapped one could thrash between two layers)."""
+    c = make_case([100, 33], hq=8, hkv=2, seed=3)
+    caches = [cache_to_dev(c.kv_cache) for _ in range(64)]
+    q, bt, sl = c.q.cuda(), c.block_table.cuda(), c.seq_lens.cuda()
+    ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(2, 8, 128, 1))
+
+    def step():
+        for kv in caches:
+            ops.paged_decode(q, kv[0], kv[1], bt, sl, c.max_seq_len, c.scale, workspace=ws)
+    step()
+    n1 = lib.b200attn_debug_map_encodes()
+    step()
+    step()
+    torch.cuda.synchronize()
+    assert lib.b200attn_debug_map_encodes() == n1, "tensor maps were re-encoded for caches that did not move"

@@ -86,6 +86,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200attn_decode_plan": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i64, _i32, _vp, _sz, _vp]),
     "b200attn_debug_set_trace": (None, [_vp]),
     "b200attn_debug_set_team": (None, [C.c_int32]),
+    "b200attn_debug_map_encodes": (C.c_uint64, []),
     "b200attn_debug_plan_offset": (C.c_size_t, [C.c_int32, C.c_int32]),
     "b200attn_debug_sk_schedule": (None, [_i64, _i32, _i32, C.POINTER(_i64)]),
     "b200attn_paged_decode": (C.c_int, _DECODE_ARGS),

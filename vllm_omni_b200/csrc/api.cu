@@ -87,8 +87,30 @@ struct KvMapEntry {
   CoordPerm perm;
   bool valid;
 };
-constexpr int kMapCache = 256;  // >= 2 maps x layers of a model; direct-mapped by pointer hash
+constexpr int kMapCache = 1024;  // >> 2 maps x layers of a model; 4-way set-associative by pointer hash
+constexpr int kMapWays = 4;
 thread_local KvMapEntry g_maps[kMapCache];
+thread_local unsigned long long g_map_encodes = 0;  // tensor maps encoded by this thread (a miss costs ~1 us of host time)
+thread_local unsigned g_map_victim = 0;
+
+// The cached map for `key`, or the entry to (re)encode into: a free way of the key's set, else a round-robin victim.
+KvMapEntry* find_map(KvMapEntry* table, const KvMapKey& key, bool* hit) {
+  uint64_t h = reinterpret_cast<uintptr_t>(key.ptr) >> 8;
+  h = (h ^ (h >> 17)) * 0x9E3779B97F4A7C15ull;
+  const size_t set = (h >> 40) % (kMapCache / kMapWays) * kMapWays;
+  KvMapEntry* free_way = nullptr;
+  for (int w = 0; w < kMapWays; ++w) {
+    KvMapEntry& e = table[set + w];
+    if (e.valid && e.key == key) {
+      *hit = true;
+      return &e;
+    }
+    if (!e.valid && free_way == nullptr) free_way = &e;
+  }
+  *hit = false;
+  ++g_map_encodes;
+  return free_way != nullptr ? free_way : &table[set + (g_map_victim++ % kMapWays)];
+}
 
 // Encode (or fetch) the 4-D tensor map of one cache tensor: dims sorted by stride
 // (head_size, then slot/head/block in ascending stride order), box = 64 x 16 tokens x 1 x 1
@@ -96,13 +118,14 @@ thread_local KvMapEntry g_maps[kMapCache];
 int get_kv_map(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv,
                int32_t bs, int32_t hd, bool fp8, const CUtensorMap** out_map, CoordPerm* out_perm) {
   KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, fp8 ? 1 : 0};
-  const size_t slot = (reinterpret_cast<uintptr_t>(ptr) >> 8) % kMapCache;
-  KvMapEntry& e = g_maps[slot];
-  if (e.valid && e.key == key) {
+  bool hit = false;
+  KvMapEntry& e = *find_map(g_maps, key, &hit);
+  if (hit) {
     *out_map = &e.map;
     *out_perm = e.perm;
     return 0;
   }
+  e.valid = false;
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled entry point not found");
   const int64_t es = fp8 ? 1 : 2;
@@ -168,12 +191,13 @@ thread_local KvMapEntry g_maps5h[kMapCache];  // bf16, box of ONE 64-element hal
 int get_kv_map5(const void* ptr, int64_t sb, int64_t ss, int64_t sh, int64_t nb, int32_t hkv, int32_t bs, bool fp8,
                 const CUtensorMap** out_map, int box_halves = 2) {
   KvMapKey key{ptr, sb, ss, sh, nb, hkv, bs, fp8 ? 1 : (box_halves == 1 ? 2 : 0)};
-  const size_t slot = (reinterpret_cast<uintptr_t>(ptr) >> 8) % kMapCache;
-  KvMapEntry& e = (box_halves == 1 ? g_maps5h : g_maps5)[slot];
-  if (e.valid && e.key == key) {
+  bool hit = false;
+  KvMapEntry& e = *find_map(box_halves == 1 ? g_maps5h : g_maps5, key, &hit);
+  if (hit) {
     *out_map = &e.map;
     return 0;
   }
+  e.valid = false;
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) return fail(B200ATTN_EDRIVER, "cuTensorMapEncodeTiled entry point not found");
   if (fp8) {
@@ -945,6 +969,7 @@ void b200attn_debug_sk_schedule(int64_t total_tiles, int32_t num_warps, int32_t 
 
 void b200attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<unsigned long long*>(device_buffer); }
 void b200attn_debug_set_team(int32_t warps) { g_sk3_team = warps; }
+uint64_t b200attn_debug_map_encodes(void) { return g_map_encodes; }
 size_t b200attn_debug_plan_offset(int32_t batch, int32_t num_q_heads) {
   int sms = cached_num_sms();
   if (sms <= 0) sms = 148;
