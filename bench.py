@@ -439,7 +439,7 @@ class Arm:
         ops.paged_decode(self.dq, kc, vc, self.dbt, self.dsl, inp.max_seq_len, inp.softmax_scale,
                          out=self.dout if out is None else out, kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
                          v_scale=inp.v_scale, num_splits=self.splits if splits is None else splits, variant=v,
-                         workspace=self.ws, planned=pl, early_kv_read=True)
+                         workspace=self.ws, planned=pl, early_kv_read=True, early_q_read=True)
 
     def layer(self, kc, vc, **kw):
         from vllm_omni_b200 import ops
@@ -532,7 +532,7 @@ class Arm:
                 ops.paged_decode_partial(self.dq, kc, vc, self.dbt, self.dsl, inp.max_seq_len, inp.softmax_scale,
                                          self.dout, max(self.splits, 1), self.ws, kv_cache_dtype=wl.kv_cache_dtype,
                                          k_scale=inp.k_scale, v_scale=inp.v_scale, variant=self.variant,
-                                         planned=self.planned, early_kv_read=True)
+                                         planned=self.planned, early_kv_read=True, early_q_read=True)
 
         res = {}
         for name, fn in (("decode_plus_reduce", full), ("decode_only", partial_only)):

@@ -76,6 +76,11 @@ extern "C" {
                                             LAST 16-token tile — what a decode step's cache write does
                                             (gpu_ar_model_runner.py:421-456 slot mappings). The kernel may then
                                             stage all other KV tiles before griddepcontrol.wait. */
+#define B200ATTN_DECODE_EARLY_Q_READ 4   /* the caller guarantees that `q` was complete before the kernel this launch
+                                            follows was started (e.g. q comes out of a RoPE kernel, then this
+                                            library's cache write, then this call): the decode kernel may then load
+                                            q before griddepcontrol.wait. NOT valid after the fused RoPE + cache
+                                            write (b200attn_rope_and_cache rotates q in place). */
 
 B200ATTN_API int b200attn_abi_version(void);
 B200ATTN_API const char* b200attn_last_error(void); /* host string, thread-local */

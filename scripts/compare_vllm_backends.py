@@ -37,7 +37,7 @@ def make_ours(variant, planned=False, early=False, write=False):
                                   inp.v_scale)
         ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len, inp.softmax_scale, out=out,
                          kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale, v_scale=inp.v_scale, workspace=ws,
-                         variant=variant, planned=planned, early_kv_read=early)
+                         variant=variant, planned=planned, early_kv_read=early, early_q_read=early)
     return fn
 
 
@@ -100,7 +100,7 @@ ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)  #
 report("b200attn cooperative stream-K (default call: plan launch + decode, nothing planned ahead)", ours)
 report("b200attn cooperative stream-K, planned once per step", make_ours(ops.VARIANT_SK3, planned=True), pre=plan_step,
        note=f"one plan launch per {L} layers inside the timed graph")
-report("b200attn cooperative stream-K, planned + early KV reads (what the backend passes)",
+report("b200attn cooperative stream-K, planned + early KV / q reads (what the backend passes)",
        make_ours(ops.VARIANT_SK3, planned=True, early=True), pre=plan_step)
 report("b200attn cooperative stream-K, planned + early, cache write + decode per layer",
        make_ours(ops.VARIANT_SK3, planned=True, early=True, write=True), note="two launches per layer", pre=plan_step)

@@ -35,7 +35,7 @@ ops.decode_plan(inp.seq_lens, inp.block_table, B, hq, hkv, wl.block_size, ws)
 def run(kc, vc, planned=True, early=True):
     ops.paged_decode(inp.q, kc, vc, inp.block_table, inp.seq_lens, inp.max_seq_len, inp.softmax_scale, out=out,
                      kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale, v_scale=inp.v_scale, workspace=ws,
-                     variant=variant, planned=planned, early_kv_read=early)
+                     variant=variant, planned=planned, early_kv_read=early, early_q_read=early)
 
 
 def mmm(x):

@@ -63,7 +63,7 @@ for tp in (1, 2, 4, 8):
         def fn(kc, vc):
             ops.paged_decode(q, kc, vc, bt, sl, inp.max_seq_len, inp.softmax_scale, out=out, num_splits=splits,
                              variant=variant, workspace=ws, kv_cache_dtype=wl.kv_cache_dtype, k_scale=inp.k_scale,
-                             v_scale=inp.v_scale, planned=planned, early_kv_read=planned)
+                             v_scale=inp.v_scale, planned=planned, early_kv_read=planned, early_q_read=planned)
         return fn
 
     rows = [(f"fixed-split {s}", ops.VARIANT_STREAM, s, False) for s in (1, 2, 4, 8, 16, 32, 64)]

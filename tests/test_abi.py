@@ -88,11 +88,11 @@ def test_workspace_bytes_formula(lib):
         return ctrl + sk_rows * 129 * 4 + (plan + 4) * 4 + 256
 
     # cooperative stream-K (default), behind the v2 region: partial rows (2 parities x 2 per team, teams <= warps)
-    # with their LSEs, then its plan (header 16 | team starts | team desc, team info, warp desc 4 x warps each | cum)
+    # with their LSEs, then its plan (header 16 | team starts | team desc, team info, warp desc 4 x warps each | first block ids 32 x warps | cum)
     def sk3(batch, hq):
         nw = 148 * 12
         off = (sk2(batch, hq) + 255) // 256 * 256
-        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 12 * nw + ((batch + 1 + 3) // 4 * 4)
+        plan = 16 + ((nw + 1 + 3) // 4 * 4) + 44 * nw + ((batch + 1 + 3) // 4 * 4)
         return off + 2 * 2 * nw * 8 * 129 * 4 + (plan + 4) * 4 + 256
 
     assert f(64, 32, 128, 8) == max(fixed, sk1(64), sk3(64, 32))

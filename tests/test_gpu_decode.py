@@ -459,7 +459,7 @@ def test_sk2_planned_step_with_early_kv_reads(lib, graph, fp8, variant, monkeypa
             ops.reshape_and_cache(new_k_d[l], new_v_d[l], caches[l][0], caches[l][1], last_d, kvd, ks, vs)
             ops.paged_decode(qs[l], caches[l][0], caches[l][1], bt, sl, max(lens), cases[l].scale, out=outs[l],
                              kv_cache_dtype=kvd, k_scale=ks, v_scale=vs, workspace=ws, planned=True,
-                             early_kv_read=True, variant=variant)
+                             early_kv_read=True, early_q_read=True, variant=variant)
 
     if graph:
         side = torch.cuda.Stream()

@@ -26,6 +26,7 @@ VARIANT_SK2 = 5
 VARIANT_SK3 = 6
 DECODE_PLANNED = 1
 DECODE_EARLY_KV_READ = 2
+DECODE_EARLY_Q_READ = 4
 
 ERRORS = {1: "EINVAL", 2: "EUNSUPPORTED", 3: "EWORKSPACE", 4: "EDRIVER"}
 

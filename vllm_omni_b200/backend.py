@@ -230,6 +230,7 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         self.replica_split = None
         self._split_ws: ops.DecodeWorkspace | None = None
         self._split_q = self._split_out = None
+        self._q_rotated_by_update = False
 
     def enable_replica_split(self, replica_split, max_batch: int = 0) -> None:
         """Serve decode rows with the batch split over the ranks that replicate this KV head instead of
@@ -256,6 +257,7 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         slot_mapping.shape[0]. Skipped when this layer shares another layer's cache."""
         if self.kv_sharing_target_layer_name is not None:
             return
+        self._q_rotated_by_update = False   # q is final before this kernel starts (see forward: early_q_read)
         k_cache, v_cache = ops.split_kv_cache(kv_cache)
         ops.reshape_and_cache(key, value, k_cache, v_cache, slot_mapping, self._kv_code,
                               getattr(layer, "_k_scale", None), getattr(layer, "_v_scale", None))
@@ -271,6 +273,7 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
                                     kv_cache: torch.Tensor, layer_slot_mapping: torch.Tensor) -> None:
         """In-place RoPE on query/key + cache write of (rotated key, value) in ONE launch
         (vllm/v1/attention/backend.py:823-840). query/key/value may arrive flat ([T, H*d])."""
+        self._q_rotated_by_update = True    # this launch rotates q in place: the decode may not read q ahead of it
         k_cache, v_cache = ops.split_kv_cache(kv_cache)
         q = query.view(query.shape[0], -1, self.head_size)
         k = key.view(key.shape[0], -1, self.head_size)
@@ -331,7 +334,7 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
                              self.scale, out=out[:ndt], kv_cache_dtype=self._kv_code,
                              k_scale=k_scale, v_scale=v_scale, num_splits=md.decode_num_splits,
                              workspace=md.workspace, planned=md.decode_planned and md.decode_num_splits == 0,
-                             early_kv_read=True)
+                             early_kv_read=True, early_q_read=not self._q_rotated_by_update)
         if md.num_prefills > 0:
             n = md.num_actual_tokens
             ops.paged_prefill(q[ndt:n], k_cache, v_cache, md.block_table[nd:], md.seq_lens[nd:],

@@ -600,7 +600,7 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
     return fail(B200ATTN_EINVAL, "num_splits %d out of [0, %d]", num_splits, kMaxSplits);
   if (variant < B200ATTN_VARIANT_AUTO || variant > B200ATTN_VARIANT_SK3)
     return fail(B200ATTN_EINVAL, "unknown variant %d", variant);
-  if (flags & ~(B200ATTN_DECODE_PLANNED | B200ATTN_DECODE_EARLY_KV_READ))
+  if (flags & ~(B200ATTN_DECODE_PLANNED | B200ATTN_DECODE_EARLY_KV_READ | B200ATTN_DECODE_EARLY_Q_READ))
     return fail(B200ATTN_EINVAL, "unknown decode flags 0x%x", flags);
   // schedule: cooperative stream-K (teams of warps share an item, merges in shared memory, no reduce launch)
   // unless the caller asks for a fixed split count or another kernel
@@ -800,14 +800,20 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
       const bool pdl = env_flag("B200ATTN_PDL", true);
       if (!(flags & B200ATTN_DECODE_PLANNED)) {
         // no plan of this step in the workspace: make it now; the decode kernel then waits for it first
-        if (cudaError_t pe = launch_sk3_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms, sk3.plan, sk2.ctrl,
-                                             sk3_calib_max(), sk3_team_force(), stream))
+        if (cudaError_t pe = launch_sk3_plan(seq_lens, batch, num_kv_heads * p.subgroups, sms, block_table,
+                                             block_table_stride, p.tpp_shift, sk3.plan, sk2.ctrl, sk3_calib_max(),
+                                             sk3_team_force(), stream))
           return cuda_fail(pe, "decode plan launch");
         p.flags |= kSk2FlagWaitFirst;
       }
       if ((flags & B200ATTN_DECODE_EARLY_KV_READ) && env_flag("B200ATTN_EARLY_KV_READ", true))
         p.flags |= kSk2FlagEarlyKvRead;
-      if ((g_sk2_parity ^= 1) != 0) p.flags |= kSk2FlagParity;  // consecutive launches alternate their control words
+      if ((flags & B200ATTN_DECODE_EARLY_Q_READ) && env_flag("B200ATTN_EARLY_Q_READ", true)) p.flags |= kSk3FlagEarlyQRead;
+      // consecutive launches alternate their counter / slot sets and claim with growing ids; the step's plan launch
+      // (which serialises the stream) resets the claim words, so the ids only have to grow inside a step
+      static thread_local int launch_seq = 0;
+      launch_seq = launch_seq >= 0x3fffffff ? 1 : launch_seq + 1;
+      p.launch_id = launch_seq;
       e = launch_decode_sk3(tm_k, *mv, p, fp8, sms, pdl, stream);
     } else if (variant == B200ATTN_VARIANT_SK2) {
       const CUtensorMap *mk = nullptr, *mv = nullptr;
@@ -940,8 +946,9 @@ int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_h
   const Sk2Layout l = sk2_layout(workspace, sms);
   if (sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes) {
     const Sk3Layout l3 = sk3_layout(workspace, batch, num_q_heads, sms);
-    if (cudaError_t e3 = launch_sk3_plan(seq_lens, batch, num_kv_heads * subgroups, sms, l3.plan, l.ctrl, sk3_calib_max(),
-                                         sk3_team_force(), static_cast<cudaStream_t>(stream)))
+    if (cudaError_t e3 = launch_sk3_plan(seq_lens, batch, num_kv_heads * subgroups, sms, block_table, block_table_stride,
+                                         shift, l3.plan, l.ctrl, sk3_calib_max(), sk3_team_force(),
+                                         static_cast<cudaStream_t>(stream)))
       return cuda_fail(e3, "decode plan launch");
   }
   if (sk3_workspace_bytes(batch, num_q_heads, sms) <= workspace_bytes && !env_flag("B200ATTN_PLAN_SK2", false))

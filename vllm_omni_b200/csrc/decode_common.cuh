@@ -29,6 +29,7 @@ constexpr int kSk2PlanMagic = 0x534b3250;  // "SK2P"
 constexpr int kSk2FlagWaitFirst = 1;    // griddepcontrol.wait before the plan is read (plan made by the previous kernel)
 constexpr int kSk2FlagEarlyKvRead = 2;  // KV tiles other than a sequence's last may be loaded before the wait
 constexpr int kSk2FlagParity = 8;        // launch parity: consecutive launches on a stream alternate their claim words
+constexpr int kSk3FlagEarlyQRead = 32;   // q may be loaded before griddepcontrol.wait (B200ATTN_DECODE_EARLY_Q_READ)
 constexpr int kSk2MaxGroups = 512;      // CTAs of the persistent grid (= SMs) the control area has room for
 constexpr int kSk2CalibMinTiles = 96;   // an SM's rate is only trusted if it streamed at least this many tiles
 constexpr float kSk2CalibGain = 0.7f;   // share of the measured rate in a weight update
@@ -52,6 +53,7 @@ struct Sk2Ctrl {
   float weight[kSk2MaxGroups];        // share of the tile stream per SM (0 everywhere: uniform)
   int32_t stat_tiles[kSk2MaxGroups];  // last launch: tiles the CTA on this SM streamed ...
   int32_t stat_cycles[kSk2MaxGroups]; // ... and the cycles it took
+  int32_t claim3[kSk2MaxGroups];      // cooperative stream-K: id of the last launch of the step that took the group
 };
 
 struct DecodeParams {
@@ -96,6 +98,7 @@ struct DecodeParams {
   float* sk3_part_o;
   float* sk3_part_lse;
   int32_t* sk3_cnt;
+  int32_t launch_id;  // > 0, grows from one decode launch of a step to the next (claims, parity of the counter / slot sets)
 };
 
 // Stream-K schedule, computed identically by the decode and the reduce kernel from the tile total:

@@ -35,8 +35,9 @@ int decode_sk2_warps();
 size_t sk2_plan_ints(int batch, int nw, int hs_count);
 cudaError_t launch_sk2_reduce(const DecodeParams& p, int grid_decode, bool pdl, cudaStream_t stream);
 // cooperative stream-K (paged_decode_sk3.cu): teams of warps share an item, merges in shared memory, no reduce launch
-cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, int32_t* plan, Sk2Ctrl* ctrl,
-                            int calib_max, int team_force, cudaStream_t stream);
+cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, const int32_t* block_table,
+                            int64_t bt_stride, int tpp_shift, int32_t* plan, Sk2Ctrl* ctrl, int calib_max, int team_force,
+                            cudaStream_t stream);
 cudaError_t launch_decode_sk3(const CUtensorMap& tm_k, const CUtensorMap& tm_v, const DecodeParams& p, bool fp8,
                               int grid, bool pdl, cudaStream_t stream);
 size_t decode_sk3_smem_bytes(bool fp8);

@@ -22,7 +22,7 @@
 //    "last arriver merges" through one atomic per piece — nobody ever spins on another CTA.
 //  * Everything else is the second generation's: per-warp private ring of TMA stages issued by the warp's
 //    own lane 0, tensor-core tile math of sk_math.cuh, plan once per step, early KV reads under programmatic
-//    dependent launch, chunk group claimed by SM id.
+//    dependent launch, chunk group claimed by SM id (with the launch's id: nothing to re-arm on the way out).
 //
 // Replaces the decode branch of the reference's stock backends
 // (vllm/v1/attention/backends/flashinfer.py:1694-1822, flash_attn.py:758-819) and their split-KV
@@ -34,7 +34,7 @@ namespace b200 {
 
 // ------------------------------------------------------------------------------------------------
 // Plan layout (int32 words), G = CTAs of the grid, W = 12, NTmax = G * W teams at most:
-//   header[16] | tstart[NTmax + 1] | tdesc[NTmax][4] | tinfo[NTmax][4] | wdesc[G * W][4] | cum[batch + 1]
+//   header[16] | tstart[NTmax + 1] | tdesc[NTmax][4] | tinfo[NTmax][4] | wdesc[G * W][4] | wids[G * W][32] | cum[batch + 1]
 //   header     {positions, G, T, NT = G * (W / T), batch, hs_count, tpp_shift, magic, W / T}
 //   tstart[c]  first stream position of team c (team c = CTA group c / (W/T), warps (c % (W/T)) * T ...)
 //   tdesc[c]   {sequence, head-group, tile, tiles of the sequence} at tstart[c]
@@ -42,13 +42,16 @@ namespace b200 {
 //               pieces of that item, teams that continue the team's LAST item when the team owns it and
 //               it is cut (0: not cut), 1 if those are exactly the next teams (no empty team between)}
 //   wdesc[w]   tdesc of the first position of warp w of the grid (sequence = batch: the warp has none)
+//   wids[w]    the block ids of warp w's first 32 tiles of its first item (tile + T * lane): its first TMA needs no
+//              dependent load
 //   cum[b]     exclusive prefix of tiles per sequence
 // ------------------------------------------------------------------------------------------------
 __host__ __device__ __forceinline__ int64_t sk3_plan_tstart_off() { return kSk3PlanHdrInts; }
 __host__ __device__ __forceinline__ int64_t sk3_plan_tdesc_off(int ntmax) { return kSk3PlanHdrInts + ((ntmax + 1 + 3) & ~3); }
 __host__ __device__ __forceinline__ int64_t sk3_plan_tinfo_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 4ll * ntmax; }
 __host__ __device__ __forceinline__ int64_t sk3_plan_wdesc_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 8ll * ntmax; }
-__host__ __device__ __forceinline__ int64_t sk3_plan_cum_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 12ll * ntmax; }
+__host__ __device__ __forceinline__ int64_t sk3_plan_wids_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 12ll * ntmax; }
+__host__ __device__ __forceinline__ int64_t sk3_plan_cum_off(int ntmax) { return sk3_plan_tdesc_off(ntmax) + 44ll * ntmax; }
 
 size_t sk3_plan_ints(int batch, int groups) {
   return static_cast<size_t>(sk3_plan_cum_off(groups * kSk3Warps)) + ((static_cast<size_t>(batch) + 1 + 3) & ~size_t(3));
@@ -108,7 +111,8 @@ __host__ __device__ __forceinline__ int sk3_team_size(int avg) {
 // Phase 2: CTA ranges by weight, team ranges inside, team descriptors. Phase 3: warp descriptors.
 // Phase 4: which teams share a cut item.
 __global__ void __launch_bounds__(1024)
-sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, int groups, int32_t* __restrict__ plan,
+sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, int groups,
+                const int32_t* __restrict__ block_table, int64_t bt_stride, int tpp_shift, int32_t* __restrict__ plan,
                 Sk2Ctrl* __restrict__ ctrl, int calib_max, int team_force) {
   __shared__ int s_warp[32];
   __shared__ float s_red[32];
@@ -129,6 +133,7 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     s_carry = 0;
     s_nonempty = 0;
   }
+  if (tid < kSk2MaxGroups) ctrl->claim3[tid] = 0;  // the step's decode launches claim with ids > 0, growing
   // ---- phase 0: weights (thread g <-> SM g)
   {
     const bool have = tid < groups;
@@ -202,6 +207,9 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     plan[6] = 0;
     plan[7] = kSk3PlanMagic;
     plan[8] = tpc;
+    plan[9] = 0;
+    plan[10] = 0;
+    plan[11] = ctrl->calib_updates < calib_max ? 1 : 0;  // the decode launches of this step record their SMs' rates
     // CTA ranges: cumulative weights; every CTA gets at least one position while there are any, so the non-empty
     // CTAs are a prefix of the grid
     double acc = 0.0;
@@ -231,6 +239,14 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     const int c = g * tpc + w / T;
     const int pos = s_tstart[c] + w % T;
     wdesc[idx] = pos < s_tstart[c + 1] ? sk3_desc_of(cum_r, batch, hs_count, pos) : make_int4(batch, 0, 0, 1);
+  }
+  __syncthreads();
+  // ---- phase 3b: the block ids of every warp's first tiles
+  int32_t* wids = plan + sk3_plan_wids_off(ntmax);
+  for (int idx = tid; idx < groups * W * 32; idx += 1024) {
+    const int4 d = wdesc[idx >> 5];
+    const int tile = d.z + T * (idx & 31);
+    wids[idx] = (d.x < batch && tile < d.w) ? block_table[static_cast<int64_t>(d.x) * bt_stride + (tile >> tpp_shift)] : 0;
   }
   // ---- phase 4: cut items
   for (int c = tid; c < nt; c += 1024) {
@@ -263,9 +279,11 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
   }
 }
 
-cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, int32_t* plan, Sk2Ctrl* ctrl,
-                            int calib_max, int team_force, cudaStream_t stream) {
-  sk3_plan_kernel<<<1, 1024, 0, stream>>>(seq_lens, batch, hs_count, groups, plan, ctrl, calib_max, team_force);
+cudaError_t launch_sk3_plan(const int32_t* seq_lens, int batch, int hs_count, int groups, const int32_t* block_table,
+                            int64_t bt_stride, int tpp_shift, int32_t* plan, Sk2Ctrl* ctrl, int calib_max, int team_force,
+                            cudaStream_t stream) {
+  sk3_plan_kernel<<<1, 1024, 0, stream>>>(seq_lens, batch, hs_count, groups, block_table, bt_stride, tpp_shift, plan, ctrl,
+                                          calib_max, team_force);
   return cudaGetLastError();
 }
 
@@ -368,6 +386,7 @@ struct Sk3MergeArgs {
   int item_end;       // stream position behind the item
   int nt, ntmax;
   int peek;           // arrival count of the item this warp saw shortly before the piece ended (-1: did not look)
+  int final_piece;    // the team's last piece: nothing is staged into the stash slots afterwards
 };
 
 struct Sk3Piece {  // one piece of a cut item as it sits in its slot: normalised row (4 columns per lane) + log2-domain LSE
@@ -379,7 +398,7 @@ constexpr int kSk3FoldEarly = 2;  // pieces of an item whose partials are asked 
 
 template <int W, int D, int SB, bool FP8>
 __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>& sm, const Sk3MergeArgs a, int warp, int lane) {
-  const int parity = (p.flags & kSk2FlagParity) ? 1 : 0;
+  const int parity = p.launch_id & 1;
   const int bar_id = 1 + a.tw0 / a.T, nthr = a.T * 32;
   float* const part_o = p.sk3_part_o + static_cast<int64_t>(parity) * 2 * a.ntmax * kHeadsPerItem * kHeadDim;
   float* const part_l = p.sk3_part_lse + static_cast<int64_t>(parity) * 2 * a.ntmax * kHeadsPerItem;
@@ -501,6 +520,7 @@ __device__ __noinline__ void sk3_merge(const DecodeParams& p, Sk3Smem<W, D, SB>&
   }
   if (whole || fast) {
     if (fast && a.wi == 0 && lane == 0) cnt[own] = 0;  // ready for the launch after the next
+    if (a.final_piece) return;     // nobody refills a slot any more: the warps leave as they finish
     fence_proxy_async_smem();
     named_bar_sync(bar_id, nthr);  // the stash slots may be refilled
     return;
@@ -541,25 +561,26 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   // ---- which chunk group this CTA runs: the one of the SM it sits on (the plan sized group g for SM g), claimed
-  // with one atomic so that every group is run exactly once whatever the block scheduler did; claim words of two
-  // consecutive launches (which may overlap under programmatic dependent launch) are kept apart by the launch
-  // parity; the last CTA to finish re-arms the words of its launch.
+  // with one atomic so that every group is run exactly once whatever the block scheduler did (two CTAs on one SM
+  // one after the other, an SM id beyond the grid). A claim word holds the id of the last launch that took the group:
+  // ids grow from launch to launch inside a step (the host counts the calls; the value is part of a captured graph
+  // node) and the plan kernel, which runs alone once per step, zeroes the words — nothing is re-armed on the way out.
   Sk2Ctrl* const ctrl = p.sk2_ctrl;
-  const int parity = (p.flags & kSk2FlagParity) ? 1 : 0;
+  const int parity = p.launch_id & 1;  // counters and partial slots of consecutive launches are kept apart
   const int G = static_cast<int>(gridDim.x);
   uint32_t smid;
   asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
   const int g_spec = static_cast<int>(smid % static_cast<uint32_t>(G));
   if (threadIdx.x == 0) {
     int g = g_spec;
-    if (atomicCAS(&ctrl->claimed[parity][g], 0, 1) != 0) {
-      for (int k = 1; k <= G; ++k) {
-        const int gg = (g + k) % G;
-        if (atomicCAS(&ctrl->claimed[parity][gg], 0, 1) == 0) {
-          g = gg;
-          break;
-        }
+    if (atomicMax(&ctrl->claim3[g], p.launch_id) >= p.launch_id) {
+      g = -1;
+      for (int k = 1; k < G && g < 0; ++k) {
+        const int gg = (g_spec + k) % G;
+        if (atomicMax(&ctrl->claim3[gg], p.launch_id) < p.launch_id) g = gg;
       }
+      // every word already carries this id: the caller replayed one launch id inside a step (no SM affinity then)
+      if (g < 0) g = static_cast<int>(blockIdx.x);
     }
     sm.group = g;
   }
@@ -570,18 +591,25 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     if (threadIdx.x == 0) sm.t0 = clock64();
   };
   if (p.flags & kSk2FlagWaitFirst) wait_for_prior();  // the plan was written by the kernel right before this one
+  // rows of empty sequences are zeroed on the way out (no tile of theirs is in the stream): which ones is looked up
+  // now, so that the exit path has no load to wait for (sequence lengths do not change during the step)
+  const int eb = static_cast<int>(blockIdx.x) * W + warp;
+  bool empty_rows = false;
+  for (int b = eb; b < p.batch; b += G * W) empty_rows |= __ldg(p.seq_lens + b) <= 0;
   // ---- the warp's work: one round of independent loads, issued for the group the CTA will almost always get
   const int32_t* plan = p.sk3_plan;
   const int ntmax = G * W;
   const int4 hdr = __ldg(reinterpret_cast<const int4*>(plan));
   const int4 hdr2 = __ldg(reinterpret_cast<const int4*>(plan) + 1);
-  const int T = hdr.z, nt = hdr.w, tpc = __ldg(plan + 8);
+  const int4 hdr3 = __ldg(reinterpret_cast<const int4*>(plan) + 2);  // {teams per CTA, -, -, shares still being calibrated}
+  const int T = hdr.z, nt = hdr.w, tpc = hdr3.x;
   const int wi = warp % T, tw0 = warp - wi;
   int team = g_spec * tpc + warp / T;
   int4 wd = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_wdesc_off(ntmax)) + g_spec * W + warp);
   int4 td = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tdesc_off(ntmax)) + team);
   int4 ti = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tinfo_off(ntmax)) + team);
   int t_begin = __ldg(plan + sk3_plan_tstart_off() + team), t_end = __ldg(plan + sk3_plan_tstart_off() + team + 1);
+  int ids = __ldg(plan + sk3_plan_wids_off(ntmax) + (g_spec * W + warp) * 32 + lane);  // block ids of the first tiles
   const int32_t* cum = plan + sk3_plan_cum_off(ntmax);
   if (lane == 0) {
 #pragma unroll
@@ -597,6 +625,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   if (group != g_spec) {  // rare: this CTA runs another SM's group
     team = group * tpc + warp / T;
     wd = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_wdesc_off(ntmax)) + group * W + warp);
+    ids = __ldg(plan + sk3_plan_wids_off(ntmax) + (group * W + warp) * 32 + lane);
     td = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tdesc_off(ntmax)) + team);
     ti = __ldg(reinterpret_cast<const int4*>(plan + sk3_plan_tinfo_off(ntmax)) + team);
     t_begin = __ldg(plan + sk3_plan_tstart_off() + team);
@@ -626,7 +655,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
   Sk3Walk pf{wd.x, wd.y, wd.z, wd.w};
   int pf_left = cnt_tiles;
   int pf_t0 = pf.tile, pf_k = 0, pf_kbase = 0, pf_kvh = 0;  // block ids: tile pf_t0 + T * (pf_kbase + lane) of the item
-  int ids = 0;
+  bool first_item = true;   // the block ids of the first item came with the plan
   int pf_items_ahead = 0;   // item starts prepared by the front and not yet taken by the math (0 or 1)
   bool pf_fresh = true;     // the front stands on a tile whose item it has not prepared yet
   bool q_deferred = false;  // the prepared item's q has not been loaded (griddepcontrol.wait pending)
@@ -697,8 +726,11 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
         pf_t0 = pf.tile;
         pf_k = 0;
         pf_kbase = 0;
-        ids = sk3_load_ids(p, pf.b, pf.n, pf_t0, T, 0, lane);
-        if (waited) load_q_next(); else q_deferred = true;
+        if (!first_item) ids = sk3_load_ids(p, pf.b, pf.n, pf_t0, T, 0, lane);
+        first_item = false;
+        // q: produced by a kernel further up the stream; only with the caller's word that it was complete before this
+        // kernel's predecessor started (B200ATTN_DECODE_EARLY_Q_READ) is it read ahead of griddepcontrol.wait
+        if (waited || (p.flags & kSk3FlagEarlyQRead)) load_q_next(); else q_deferred = true;
         pf_items_ahead = 1;
         pf_fresh = false;
       }
@@ -825,6 +857,7 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
       a.nt = nt;
       a.ntmax = ntmax;
       a.peek = peek;
+      a.final_piece = piece_end == t_end;
       sk3_merge<W, D, SB, FP8>(p, sm, a, warp, lane);
       state_reset(st);
       got = false;
@@ -859,32 +892,26 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     p.trace[gw * 8 + 2] = t_end_ns;
     p.trace[gw * 8 + 3] = t_end_ns;
   }
-  // rows of empty sequences: zero, LSE = -inf (no tile of theirs is in the stream)
-  for (int b = static_cast<int>(blockIdx.x) * W + warp; b < p.batch; b += G * W) {
-    if (__ldg(p.seq_lens + b) > 0) continue;
-    for (int i = lane; i < p.num_q_heads * (kHeadDim / 4); i += 32)
-      *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(b) * p.out_stride_tok + i * 4) = make_uint2(0u, 0u);
-    if (p.lse != nullptr)
-      for (int h = lane; h < p.num_q_heads; h += 32) p.lse[static_cast<int64_t>(b) * p.num_q_heads + h] = -CUDART_INF_F;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    // what this SM achieved (the plan kernel turns it into the SM's share of the next steps' streams) ...
-    if (smid < static_cast<uint32_t>(kSk2MaxGroups)) {
-      const int32_t* tstart = plan + sk3_plan_tstart_off();
-      // summed over the launches since the last plan (every layer of a step): one launch is a noisy sample
-      const long long cyc = clock64() - sm.t0;
-      if (cyc > 0 && cyc < 0x10000000ll && ctrl->stat_cycles[smid] < 0x30000000) {
-        atomicAdd(&ctrl->stat_tiles[smid], __ldg(tstart + (group + 1) * tpc) - __ldg(tstart + group * tpc));
-        atomicAdd(&ctrl->stat_cycles[smid], static_cast<int>(cyc));
-      }
+  // rows of empty sequences: zero, LSE = -inf
+  if (empty_rows) {
+    for (int b = eb; b < p.batch; b += G * W) {
+      if (__ldg(p.seq_lens + b) > 0) continue;
+      for (int i = lane; i < p.num_q_heads * (kHeadDim / 4); i += 32)
+        *reinterpret_cast<uint2*>(p.out + static_cast<int64_t>(b) * p.out_stride_tok + i * 4) = make_uint2(0u, 0u);
+      if (p.lse != nullptr)
+        for (int h = lane; h < p.num_q_heads; h += 32) p.lse[static_cast<int64_t>(b) * p.num_q_heads + h] = -CUDART_INF_F;
     }
-    // ... and the last CTA of the launch re-arms the claim words of its parity
-    __threadfence();
-    if (atomicAdd(&ctrl->finished[parity], 1) == G - 1) {
-      for (int g = 0; g < G; ++g) ctrl->claimed[parity][g] = 0;
-      ctrl->finished[parity] = 0;
-      __threadfence();
+  }
+  if (hdr3.w == 0) return;  // the SM shares are frozen: nothing to record, every warp leaves on its own
+  __syncthreads();
+  if (threadIdx.x == 0 && smid < static_cast<uint32_t>(kSk2MaxGroups)) {
+    // what this SM achieved (the plan kernel turns it into the SM's share of the next steps' streams), summed over
+    // the launches since the last plan (every layer of a step): one launch is a noisy sample
+    const int32_t* tstart = plan + sk3_plan_tstart_off();
+    const long long cyc = clock64() - sm.t0;
+    if (cyc > 0 && cyc < 0x10000000ll && ctrl->stat_cycles[smid] < 0x30000000) {
+      atomicAdd(&ctrl->stat_tiles[smid], __ldg(tstart + (group + 1) * tpc) - __ldg(tstart + group * tpc));
+      atomicAdd(&ctrl->stat_cycles[smid], static_cast<int>(cyc));
     }
   }
 }

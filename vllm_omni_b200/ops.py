@@ -9,7 +9,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from ._lib import (DECODE_EARLY_KV_READ, DECODE_PLANNED, KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC,  # noqa: F401
+from ._lib import (DECODE_EARLY_KV_READ, DECODE_EARLY_Q_READ, DECODE_PLANNED, KV_BF16, KV_FP8_E4M3, VARIANT_AUTO, VARIANT_CPASYNC,  # noqa: F401
                    VARIANT_SK2, VARIANT_SK3, VARIANT_STREAM, VARIANT_STREAMK, VARIANT_TMA, check)
 
 WORKSPACE_MIN_BYTES = 65536  # control area (arrival / claim counters), see b200attn_workspace_init
@@ -280,14 +280,15 @@ def debug_sk3_plan(workspace: DecodeWorkspace, batch: int, num_q_heads: int) -> 
         raise RuntimeError("no cooperative stream-K plan in this workspace")
     ntmax = groups * 12
     o_desc = 16 + ((ntmax + 1 + 3) & ~3)
-    n_words = o_desc + 12 * ntmax + batch + 1
+    n_words = o_desc + 44 * ntmax + batch + 1   # (32 block ids per warp sit between the warp descriptors and the prefix)
     w = words[:n_words].cpu()
     return {"total": total, "groups": groups, "T": T, "nt": nt, "batch": b, "hs_count": hs_count, "tpc": tpc,
             "tstart": w[16:16 + ntmax + 1].tolist(),
             "tdesc": w[o_desc:o_desc + 4 * ntmax].view(ntmax, 4).tolist(),
             "tinfo": w[o_desc + 4 * ntmax:o_desc + 8 * ntmax].view(ntmax, 4).tolist(),
             "wdesc": w[o_desc + 8 * ntmax:o_desc + 12 * ntmax].view(ntmax, 4).tolist(),
-            "cum": w[o_desc + 12 * ntmax:o_desc + 12 * ntmax + batch + 1].tolist()}
+            "wids": w[o_desc + 12 * ntmax:o_desc + 44 * ntmax].view(ntmax, 32).tolist(),
+            "cum": w[o_desc + 44 * ntmax:o_desc + 44 * ntmax + batch + 1].tolist()}
 
 
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
@@ -297,10 +298,11 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                  k_scale: torch.Tensor | None = None, v_scale: torch.Tensor | None = None,
                  num_splits: int = 0, variant: int = VARIANT_AUTO,
                  workspace: DecodeWorkspace | None = None, planned: bool = False,
-                 early_kv_read: bool = False) -> torch.Tensor:
+                 early_kv_read: bool = False, early_q_read: bool = False) -> torch.Tensor:
     """Paged decode attention (query length 1). Writes `out` in place and returns it.
 
     planned: `decode_plan` was run for this step on `workspace` (skips the per-call plan launch).
+    early_q_read: see B200ATTN_DECODE_EARLY_Q_READ (q complete before the preceding kernel started).
     early_kv_read: see B200ATTN_DECODE_EARLY_KV_READ in include/b200attn.h (the caller's cache write of this
     step only touched the last token of each sequence)."""
     lib = _lib.load()
@@ -317,7 +319,8 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         s = num_splits if num_splits > 0 else decode_num_splits(
             batch, hq, k_cache.shape[2], max_seq_len)
         workspace.ensure(decode_workspace_bytes(batch, hq, d, s))
-    flags = (DECODE_PLANNED if planned else 0) | (DECODE_EARLY_KV_READ if early_kv_read else 0)
+    flags = ((DECODE_PLANNED if planned else 0) | (DECODE_EARLY_KV_READ if early_kv_read else 0) |
+             (DECODE_EARLY_Q_READ if early_q_read else 0))
     args = _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_len,
                         softmax_scale, kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace, flags)
     check("b200attn_paged_decode", lib.b200attn_paged_decode(*args))
@@ -327,11 +330,13 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
 def paged_decode_partial(q, k_cache, v_cache, block_table, seq_lens, max_seq_len, softmax_scale,
                          out, num_splits: int, workspace: DecodeWorkspace,
                          lse=None, kv_cache_dtype="auto", k_scale=None, v_scale=None,
-                         variant: int = VARIANT_AUTO, planned: bool = False, early_kv_read: bool = False) -> None:
+                         variant: int = VARIANT_AUTO, planned: bool = False, early_kv_read: bool = False,
+                         early_q_read: bool = False) -> None:
     """First launch only (profiling sweeps): split-K partial kernel."""
     lib = _lib.load()
     workspace.ensure(decode_workspace_bytes(q.shape[0], q.shape[1], q.shape[2], num_splits))
-    flags = (DECODE_PLANNED if planned else 0) | (DECODE_EARLY_KV_READ if early_kv_read else 0)
+    flags = ((DECODE_PLANNED if planned else 0) | (DECODE_EARLY_KV_READ if early_kv_read else 0) |
+             (DECODE_EARLY_Q_READ if early_q_read else 0))
     args = _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_len,
                         softmax_scale, kv_cache_dtype, k_scale, v_scale, num_splits, variant, workspace, flags)
     check("b200attn_paged_decode_partial", lib.b200attn_paged_decode_partial(*args))
