@@ -35,6 +35,7 @@ constexpr int kSk2CalibMinTiles = 96;   // an SM's rate is only trusted if it st
 constexpr float kSk2CalibGain = 0.7f;   // share of the measured rate in a weight update
 constexpr int kSk2CalibUpdatesDefault = 8;  // weight updates before the weights are frozen (B200ATTN_SK2_CALIB)
 constexpr int kSk2FlagDebugInterleave = 4;  // debug: chunk c on CTA c % grid (timeline experiments; no merge, wrong output)
+constexpr int kSk3CalibMinTiles = 3000;     // cooperative stream-K: an SM's rate is a sum over launches; it is used once it covers this many tiles
 constexpr float kSk3CalibGainLate = 0.4f;   // cooperative stream-K: weight-update gain after the first four updates
 constexpr int kSk3CalibUpdatesDefault = 24; // ... and the number of updates before the weights are frozen (B200ATTN_SK3_CALIB)
 constexpr int kSk3Warps = 12;            // cooperative stream-K (paged_decode_sk3.cu): warps per CTA

@@ -139,7 +139,8 @@ sk3_plan_kernel(const int32_t* __restrict__ seq_lens, int batch, int hs_count, i
     const bool have = tid < groups;
     const int tiles = have ? ctrl->stat_tiles[tid] : 0, cyc = have ? ctrl->stat_cycles[tid] : 0;
     const float w_raw = have ? ctrl->weight[tid] : 0.f;
-    const float rate = (tiles >= kSk2CalibMinTiles && cyc > 0) ? static_cast<float>(tiles) / static_cast<float>(cyc) : 0.f;
+    // (a step whose plan is made per call, or a small one, keeps summing until the sample is worth using)
+    const float rate = (tiles >= kSk3CalibMinTiles && cyc > 0) ? static_cast<float>(tiles) / static_cast<float>(cyc) : 0.f;
     const int missing = __syncthreads_or(have && rate == 0.f);  // some SM has no (or too little) history
     const bool upd = !missing && ctrl->calib_updates < calib_max;
     const float rsum = sk3_block_sum(rate, s_red, tid), wsum = sk3_block_sum(w_raw, s_red, tid);
@@ -585,10 +586,13 @@ paged_decode_sk3_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_c
     sm.group = g;
   }
   bool waited = false;
+  // (the SM's rate is measured from here: a CTA that starts while the previous kernel's stragglers still run does
+  // useful work from its first instruction — it only waits before the last tile of a sequence or its first store,
+  // tens of microseconds in, when the predecessor is long gone)
+  if (threadIdx.x == 0) sm.t0 = clock64();
   auto wait_for_prior = [&]() {
     griddep_wait();
     waited = true;
-    if (threadIdx.x == 0) sm.t0 = clock64();
   };
   if (p.flags & kSk2FlagWaitFirst) wait_for_prior();  // the plan was written by the kernel right before this one
   // rows of empty sequences are zeroed on the way out (no tile of theirs is in the stream): which ones is looked up
