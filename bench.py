@@ -386,7 +386,10 @@ class Arm:
         # schedule: stream-K (no split count) unless a split count or a fixed-split variant is asked for
         self.streamk = args.variant in (ops.VARIANT_STREAMK, ops.VARIANT_SK2, ops.VARIANT_SK3) or (
             args.variant == ops.VARIANT_AUTO and args.splits == 0)
-        self.variant = (args.variant or ops.VARIANT_SK3) if self.streamk else (args.variant or ops.VARIANT_STREAM)
+        # default schedule = the library's own choice (B200ATTN_VARIANT_AUTO): the cooperative stream-K kernel, except for
+        # fp8 caches (issue-bound: the leaner first-generation stream-K + its reduce launch, see api.cu)
+        dflt = ops.VARIANT_STREAMK if (wl.fp8 and global_batch <= 2048) else ops.VARIANT_SK3
+        self.variant = (args.variant or dflt) if self.streamk else (args.variant or ops.VARIANT_STREAM)
         self.planned = self.variant in (ops.VARIANT_SK2, ops.VARIANT_SK3)
         self.splits = 0 if self.streamk else (args.splits or ops.decode_num_splits(B, hq, hkv, inp.max_seq_len))
         self.ws = ops.DecodeWorkspace("cuda", ops.decode_workspace_bytes(max(self.dB, 1), self.dhq, d, max(self.splits, 1)))
@@ -663,7 +666,7 @@ def run_b200(args, wl):
     if world == 1 and not args.ragged and tj.exists():
         tdoc = json.loads(tj.read_text())
         ent = tdoc.get(wl.name, {})
-        if ent.get("kernel_sources_sha") == kernel_sources_sha():
+        if ent.get("kernel_sources_sha") == kernel_sources_sha() and ("sk3" in ent.get("kernel", "")) == (arm.variant == 6):
             traffic = ent.get("dram_bytes_per_launch")
             traffic_note = f"ncu --set full capture {ent.get('capture', '')} of these kernel sources"
         else:

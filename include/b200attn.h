@@ -68,7 +68,12 @@ extern "C" {
 /* b200attn_paged_decode flags */
 #define B200ATTN_DECODE_PLANNED 1        /* b200attn_decode_plan was run on this workspace for exactly these
                                             seq_lens / block_table / batch / head counts / block_size (once per
-                                            step; every layer of the step then skips the plan launch) */
+                                            step; every layer of the step then skips the plan launch). "Once per
+                                            step" also under CUDA-graph replay: a replayed step needs its plan
+                                            launch (in the graph or before it) — the plan re-arms the words the
+                                            step's launches claim their share of the stream with; launches
+                                            replayed without it still compute the right result but lose the
+                                            SM-aware shares. */
 #define B200ATTN_DECODE_EARLY_KV_READ 2  /* the caller guarantees that, among this library's kernels still in
                                             flight when the decode kernel starts (they release their dependents
                                             early: programmatic dependent launch), the only KV-cache bytes being
@@ -403,7 +408,7 @@ B200ATTN_API void b200attn_debug_set_trace(void* device_buffer);
 B200ATTN_API void b200attn_debug_set_team(int32_t warps);
 
 /* TMA tensor maps this thread has encoded so far. The library caches one map per (cache pointer, strides, shape) in a
- * 1024-entry 4-way table; in steady state (the layers' caches do not move) this number stops growing — a caller that
+ * 1024-entry 8-way table; in steady state (the layers' caches do not move) this number stops growing — a caller that
  * sees it grow per step is re-encoding maps on the host at every launch. */
 B200ATTN_API uint64_t b200attn_debug_map_encodes(void);
 

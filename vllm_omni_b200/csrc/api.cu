@@ -82,34 +82,37 @@ struct KvMapKey {
   }
 };
 struct KvMapEntry {
+  unsigned long long stamp;  // last use (least recently used way of a set is replaced)
   KvMapKey key;
   CUtensorMap map;
   CoordPerm perm;
   bool valid;
 };
-constexpr int kMapCache = 1024;  // >> 2 maps x layers of a model; 4-way set-associative by pointer hash
-constexpr int kMapWays = 4;
+constexpr int kMapCache = 1024;  // >> 2 maps x layers of a model; 8-way set-associative by pointer hash, LRU within a set
+constexpr int kMapWays = 8;
 thread_local KvMapEntry g_maps[kMapCache];
 thread_local unsigned long long g_map_encodes = 0;  // tensor maps encoded by this thread (a miss costs ~1 us of host time)
-thread_local unsigned g_map_victim = 0;
+thread_local unsigned long long g_map_clock = 0;
 
-// The cached map for `key`, or the entry to (re)encode into: a free way of the key's set, else a round-robin victim.
+// The cached map for `key`, or the entry to (re)encode into: a free way of the key's set, else its least recently used.
 KvMapEntry* find_map(KvMapEntry* table, const KvMapKey& key, bool* hit) {
   uint64_t h = reinterpret_cast<uintptr_t>(key.ptr) >> 8;
   h = (h ^ (h >> 17)) * 0x9E3779B97F4A7C15ull;
   const size_t set = (h >> 40) % (kMapCache / kMapWays) * kMapWays;
-  KvMapEntry* free_way = nullptr;
+  KvMapEntry* victim = nullptr;
   for (int w = 0; w < kMapWays; ++w) {
     KvMapEntry& e = table[set + w];
     if (e.valid && e.key == key) {
       *hit = true;
+      e.stamp = ++g_map_clock;
       return &e;
     }
-    if (!e.valid && free_way == nullptr) free_way = &e;
+    if (victim == nullptr || (!e.valid && victim->valid) || (e.valid == victim->valid && e.stamp < victim->stamp)) victim = &e;
   }
   *hit = false;
   ++g_map_encodes;
-  return free_way != nullptr ? free_way : &table[set + (g_map_victim++ % kMapWays)];
+  victim->stamp = ++g_map_clock;
+  return victim;
 }
 
 // Encode (or fetch) the 4-D tensor map of one cache tensor: dims sorted by stride
@@ -605,6 +608,22 @@ static int decode_impl(bool run_partial, bool run_reduce, const void* q, int64_t
   // schedule: cooperative stream-K (teams of warps share an item, merges in shared memory, no reduce launch)
   // unless the caller asks for a fixed split count or another kernel
   bool use_sk3 = variant == B200ATTN_VARIANT_SK3 || (variant == B200ATTN_VARIANT_AUTO && num_splits == 0);
+  // fp8 caches: the kernel is bound by instruction issue (e4m3 -> f16 conversions), not by HBM, so the schedule with
+  // the leanest streaming loop wins — the first-generation stream-K (per-warp chunks + reduce launch): 183 us against
+  // 203 us at cfg4 (profiles/README.md). AUTO takes it where it fits (batch <= 2048); B200ATTN_FP8_SCHEDULE=coop
+  // keeps the cooperative kernel.
+  if (use_sk3 && variant == B200ATTN_VARIANT_AUTO && kv_dtype == B200ATTN_KV_FP8_E4M3 && batch <= kSkMaxBatch &&
+      workspace != nullptr && sk_workspace_bytes(batch, sms) <= workspace_bytes) {
+    const char* v = getenv("B200ATTN_FP8_SCHEDULE");
+    if (v == nullptr || *v == '\0' || strcmp(v, "coop") != 0) {
+      const int tpp = block_size / kTileTokens;
+      if (tpp > 0 && tpp * kTileTokens == block_size && (tpp & (tpp - 1)) == 0) {
+        use_sk3 = false;
+        variant = B200ATTN_VARIANT_STREAMK;
+        flags &= ~B200ATTN_DECODE_PLANNED;  // this schedule rebuilds its plan in the kernel: the step's plan is not used
+      }
+    }
+  }
   if (use_sk3) {
     const int tpp = block_size / kTileTokens;
     const bool fits = workspace != nullptr && tpp > 0 && tpp * kTileTokens == block_size && (tpp & (tpp - 1)) == 0 &&
