@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 9
+#define B200ATTN_ABI_VERSION 10
 
 #if defined(__GNUC__)
 #define B200ATTN_API __attribute__((visibility("default")))
@@ -245,6 +245,44 @@ B200ATTN_API int b200attn_paged_decode(
     const float* k_scale, const float* v_scale, int32_t scale_numel,
     int32_t num_splits, int32_t variant, int32_t flags,
     void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * b200attn_paged_decode for callers that cannot allocate device memory (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc): no workspace argument, no cudaMalloc / cudaFree /
+ * allocating library call inside. NO COUNTERPART IN THE
+ * REFERENCE.
+ *
+ * Same arguments and result as b200attn_paged_decode with variant = B200ATTN_VARIANT_STREAM (the fixed-split
+ * schedule: persistent decode kernel + LSE-reduce launch; bit-identical to that call for the same num_splits),
+ * bf16 caches only. The split-KV partial rows go to a file-scope `static __device__` array of
+ * B200ATTN_STATIC_SCRATCH_BYTES (8 MiB) inside the library: every GPU that loads the library holds those
+ * 8 MiB until the process exits.
+ *
+ * Limit: batch * num_q_heads * num_splits <= B200ATTN_STATIC_MAX_ROWS partial rows (num_splits == 0 picks
+ * b200attn_decode_num_splits' value; num_splits == 1 writes `out` directly and has no limit). Anything beyond
+ * is rejected with -B200ATTN_EWORKSPACE and a message that names the limit; fp8 caches with
+ * -B200ATTN_EUNSUPPORTED.
+ *
+ * The array is shared by every call on the device and keeps the previous call's contents. Nothing in it has
+ * to start at zero (a call reads only the rows it wrote itself), but two calls that overlap on the GPU —
+ * different streams, or different host threads on different streams — RACE on it: serialise them (one stream,
+ * or events) or use b200attn_paged_decode with a workspace each.
+ */
+#define B200ATTN_STATIC_SCRATCH_BYTES 8388608
+#define B200ATTN_STATIC_MAX_ROWS 16000
+B200ATTN_API size_t b200attn_static_scratch_bytes(void);
+B200ATTN_API int b200attn_paged_decode_static(
+    const void* q, int64_t q_stride_tok,
+    const void* k_cache, const void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    int64_t num_blocks,
+    void* out, int64_t out_stride_tok,
+    float* lse,
+    const int32_t* block_table, int64_t block_table_stride,
+    const int32_t* seq_lens, int32_t batch, int32_t max_seq_len,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+    float softmax_scale, int32_t kv_dtype,
+    int32_t num_splits, void* stream);
 
 /*
  * The two launches of b200attn_paged_decode, exported separately for profiling sweeps.

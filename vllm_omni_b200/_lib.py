@@ -12,7 +12,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 PEER_FLAG_BYTES = 8192
 AR_AUTO, AR_ONESHOT, AR_TWOSHOT, AR_MULTIMEM, AR_PUSH, AR_PUSH2 = 0, 1, 2, 3, 4, 5
 KV_BF16 = 0
@@ -27,6 +27,8 @@ VARIANT_SK3 = 6
 DECODE_PLANNED = 1
 DECODE_EARLY_KV_READ = 2
 DECODE_EARLY_Q_READ = 4
+STATIC_SCRATCH_BYTES = 8388608   # b200attn_paged_decode_static: the library's own scratch array
+STATIC_MAX_ROWS = 16000          # ... and the partial rows (batch x query heads x splits) it holds
 
 ERRORS = {1: "EINVAL", 2: "EUNSUPPORTED", 3: "EWORKSPACE", 4: "EDRIVER"}
 
@@ -92,6 +94,9 @@ SIGNATURES: dict[str, tuple] = {
     "b200attn_debug_sk_schedule": (None, [_i64, _i32, _i32, C.POINTER(_i64)]),
     "b200attn_paged_decode": (C.c_int, _DECODE_ARGS),
     "b200attn_paged_decode_partial": (C.c_int, _DECODE_ARGS),
+    "b200attn_static_scratch_bytes": (_sz, []),
+    # _DECODE_ARGS without the scales, variant, flags and workspace
+    "b200attn_paged_decode_static": (C.c_int, [*_DECODE_ARGS[:-9], _i32, _vp]),
     "b200attn_lse_reduce": (C.c_int, [
         _vp, _i64, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _sz, _vp]),
     "b200attn_paged_prefill": (C.c_int, [

@@ -941,6 +941,83 @@ int b200attn_lse_reduce(void* out, int64_t out_stride_tok, float* lse, const int
                      const_cast<void*>(workspace), workspace_bytes, stream);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Decode without a caller workspace and without any allocation: the split-KV partials live in a device array that
+// is part of the library image. No counterpart in the reference; added for
+// callers that cannot call cudaMalloc (graph capture, tight serving loops, harnesses that forbid it).
+//
+// In HOST code the array's name is only a stand-in for the device symbol — passing it to a kernel would hand the
+// kernel a host address. Its device address is looked up once per device with cudaGetSymbolAddress (that device
+// current) and cached below.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kStaticScratchBytes = B200ATTN_STATIC_SCRATCH_BYTES;
+constexpr int kStaticMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+static_assert(kWsCtrlBytes + static_cast<size_t>(B200ATTN_STATIC_MAX_ROWS) * (kHeadDim + 1) * sizeof(float) + 256 <=
+                  kStaticScratchBytes,
+              "B200ATTN_STATIC_MAX_ROWS partial rows do not fit the static scratch array");
+static void* g_static_scratch_ptr[kStaticMaxDevices];  // device address of g_static_scratch per device (0 = not asked yet)
+
+static int static_scratch_address(void** ptr) {
+  int dev = 0;
+  if (cudaError_t e = cudaGetDevice(&dev)) return cuda_fail(e, "cudaGetDevice (static scratch)");
+  if (dev < 0 || dev >= kStaticMaxDevices)
+    return fail(B200ATTN_EUNSUPPORTED, "static scratch: device ordinal %d out of [0, %d)", dev, kStaticMaxDevices);
+  void* p = __atomic_load_n(&g_static_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    // the same value whichever thread gets here first: no lock needed
+    if (cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch))
+      return cuda_fail(e, "cudaGetSymbolAddress (static scratch)");
+    if (p == nullptr) return fail(B200ATTN_EDRIVER, "cudaGetSymbolAddress returned a null static scratch address");
+    __atomic_store_n(&g_static_scratch_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *ptr = p;
+  return 0;
+}
+
+size_t b200attn_static_scratch_bytes(void) { return kStaticScratchBytes; }
+
+int b200attn_paged_decode_static(const void* q, int64_t q_stride_tok, const void* k_cache, const void* v_cache,
+                                 int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+                                 int64_t num_blocks, void* out, int64_t out_stride_tok, float* lse,
+                                 const int32_t* block_table, int64_t block_table_stride, const int32_t* seq_lens,
+                                 int32_t batch, int32_t max_seq_len, int32_t num_q_heads, int32_t num_kv_heads,
+                                 int32_t head_size, int32_t block_size, float softmax_scale, int32_t kv_dtype,
+                                 int32_t num_splits, void* stream) {
+  if (batch < 0) return fail(B200ATTN_EINVAL, "batch < 0");
+  if (batch == 0) return 0;
+  if (kv_dtype != B200ATTN_KV_BF16)
+    return fail(B200ATTN_EUNSUPPORTED,
+                "b200attn_paged_decode_static runs the fixed-split schedule, which is built for bf16 caches only");
+  if (num_q_heads <= 0 || num_kv_heads <= 0 || (num_q_heads % num_kv_heads) != 0)
+    return fail(B200ATTN_EINVAL, "num_q_heads %d not a multiple of num_kv_heads %d", num_q_heads, num_kv_heads);
+  if (num_splits < 0 || num_splits > kMaxSplits)
+    return fail(B200ATTN_EINVAL, "num_splits %d out of [0, %d]", num_splits, kMaxSplits);
+  const int sms = cached_num_sms();
+  if (sms <= 0) return cuda_fail(cudaGetLastError(), "device query");
+  int splits = num_splits;
+  if (splits == 0)
+    splits = b200attn_decode_num_splits(batch, num_q_heads, num_kv_heads, max_seq_len < 1 ? 1 : max_seq_len, sms);
+  // one KV range per sequence writes `out` directly and needs no scratch at all
+  const int64_t rows = splits > 1 ? static_cast<int64_t>(batch) * num_q_heads * splits : 0;
+  if (rows > B200ATTN_STATIC_MAX_ROWS)
+    return fail(B200ATTN_EWORKSPACE,
+                "static scratch holds %d partial rows (%zu B array), batch %d x %d query heads x %d splits needs %lld: "
+                "pass a smaller num_splits (1 needs none) or use b200attn_paged_decode with a workspace of your own",
+                B200ATTN_STATIC_MAX_ROWS, kStaticScratchBytes, batch, num_q_heads, splits,
+                static_cast<long long>(rows));
+  void* scratch = nullptr;
+  if (int rc = static_scratch_address(&scratch)) return rc;
+  // Nothing in the array has to start at zero for this schedule: the reduce launch reads exactly the partial rows
+  // (sequence, head, split < splits of that sequence) that the decode launch of the same call wrote; what an
+  // earlier call left in the other rows is never read.
+  return decode_impl(true, true, q, q_stride_tok, k_cache, v_cache, cache_stride_block, cache_stride_slot,
+                     cache_stride_head, num_blocks, out, out_stride_tok, lse, block_table, block_table_stride,
+                     seq_lens, batch, max_seq_len, num_q_heads, num_kv_heads, head_size, block_size, softmax_scale,
+                     kv_dtype, nullptr, nullptr, 1, splits, B200ATTN_VARIANT_STREAM, 0, scratch, kStaticScratchBytes,
+                     stream);
+}
+
 int b200attn_decode_plan(const int32_t* seq_lens, int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                          const int32_t* block_table, int64_t block_table_stride, int32_t block_size,
                          void* workspace, size_t workspace_bytes, void* stream) {

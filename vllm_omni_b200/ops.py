@@ -327,6 +327,23 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     return out
 
 
+def paged_decode_static(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                        block_table: torch.Tensor, seq_lens: torch.Tensor, max_seq_len: int,
+                        softmax_scale: float, out: torch.Tensor, lse: torch.Tensor | None = None,
+                        num_splits: int = 0) -> torch.Tensor:
+    """`paged_decode` through b200attn_paged_decode_static: fixed-split schedule with the partial rows in the
+    library's own 8 MiB device array — no workspace, and no allocation on this side either (`out` is the caller's).
+    bf16 caches; batch * Hq * num_splits <= _lib.STATIC_MAX_ROWS. Calls that overlap on the GPU race on the array."""
+    lib = _lib.load()
+    if q.shape[0] == 0:
+        return out
+    a = _decode_args(q, k_cache, v_cache, out, lse, block_table, seq_lens, max_seq_len, softmax_scale,
+                     "auto", None, None, num_splits, VARIANT_STREAM, None)
+    # drop k_scale, v_scale, scale_numel, variant, flags, workspace, bytes
+    check("b200attn_paged_decode_static", lib.b200attn_paged_decode_static(*a[:22], a[25], a[30]))
+    return out
+
+
 def paged_decode_partial(q, k_cache, v_cache, block_table, seq_lens, max_seq_len, softmax_scale,
                          out, num_splits: int, workspace: DecodeWorkspace,
                          lse=None, kv_cache_dtype="auto", k_scale=None, v_scale=None,
