@@ -338,6 +338,40 @@ B200ATTN_API int b200attn_paged_prefill(
     void* stream);
 
 /*
+ * b200attn_paged_prefill for FP8 (e4m3) caches on the tcgen05 / TMEM kernel. Same computation, same reference
+ * call site (vllm/v1/attention/backends/flash_attn.py:758-819 with an fp8 kv_cache_dtype; FlashInfer's fp8
+ * prefill, vllm/v1/attention/backends/flashinfer.py:1600-1690). Two steps on `stream`:
+ *   1. the e4m3 pages that the `batch` sequences own are rewritten as bf16 pages in `staging` (the e4m3 VALUES,
+ *      which bf16 holds exactly; slots at or past seq_lens[b] as zeros) together with their own block table;
+ *   2. the tcgen05 prefill kernel runs over the staged pages with k_scale folded into the softmax scale and
+ *      v_scale into the final normalisation — the same arithmetic as a dequantised cache, without rounding the
+ *      dequantised values.
+ * The staging costs 5 bytes of HBM traffic per cached element per layer, 1-2 % of a prefill step; without a staging
+ * buffer b200attn_paged_prefill serves fp8 caches on its mma.sync kernel.
+ *
+ * max_seq_len: host upper bound of seq_lens[0..batch) (REQUIRED here: it sizes the staged block table).
+ * total_kv_tokens: host upper bound of sum(seq_lens), or 0 if unknown (then batch * max_seq_len is provisioned).
+ * staging: device buffer of b200attn_prefill_staging_bytes(...) for the same arguments, 1 KiB aligned, contents
+ *          undefined on entry and exit; one buffer can serve every layer of a step in turn (stream order).
+ */
+B200ATTN_API size_t b200attn_prefill_staging_bytes(int32_t batch, int32_t max_seq_len, int64_t total_kv_tokens,
+                                                   int32_t num_kv_heads, int32_t head_size, int32_t block_size);
+B200ATTN_API int b200attn_paged_prefill_fp8_staged(
+    const void* q, int64_t q_stride_tok,
+    const void* k_cache, const void* v_cache,
+    int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+    int64_t num_blocks,
+    void* out, int64_t out_stride_tok,
+    const int32_t* block_table, int64_t block_table_stride,
+    const int32_t* seq_lens, const int32_t* query_start_loc,
+    int32_t batch, int32_t num_tokens, int32_t max_query_len,
+    int32_t max_seq_len, int64_t total_kv_tokens,
+    int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+    float softmax_scale,
+    const float* k_scale, const float* v_scale, int32_t scale_numel,
+    void* staging, size_t staging_bytes, void* stream);
+
+/*
  * Gather of one request's cached K or V rows into a dense [seq_len, num_kv_heads,
  * head_size] tensor (same dtype as the cache, no dequantisation). Device-side twin of the
  * reference's per-layer Python indexing in

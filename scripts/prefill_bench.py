@@ -25,7 +25,7 @@ def pairs(S, n):
     return n * (S - n) + n * (n + 1) // 2
 
 
-for fp8 in ((False,) if "--bf16-only" in sys.argv else (False, True)):
+for fp8 in ((False,) if "--bf16-only" in sys.argv else (True,) if "--fp8-only" in sys.argv else (False, True)):
     for name, seqs in CASES:
         B = len(seqs)
         lens = torch.tensor([s for s, _ in seqs], dtype=torch.int32)
@@ -52,9 +52,12 @@ for fp8 in ((False,) if "--bf16-only" in sys.argv else (False, True)):
         out = torch.empty_like(q)
         flops = 4.0 * D * HQ * sum(pairs(int(s), n) for s, n in seqs)
 
+        staging = ops.PrefillStaging("cuda") if fp8 else None  # fp8 on the tcgen05 kernel: bf16 staging of the pages
+
         def ours():
             ops.paged_prefill(q, kv[0], kv[1], bt_d, lens_d, qsl, max(qlens), D ** -0.5, out=out, kv_cache_dtype=dt,
-                              k_scale=ks, v_scale=vs)
+                              k_scale=ks, v_scale=vs, staging=staging, max_seq_len=int(lens.max()),
+                              total_kv_tokens=int(lens.sum()))
 
         def fa():
             from vllm.vllm_flash_attn import flash_attn_varlen_func
@@ -71,8 +74,8 @@ for fp8 in ((False,) if "--bf16-only" in sys.argv else (False, True)):
 
         os.environ["B200ATTN_PREFILL_UMMA"] = "0"
         impls = [("b200attn paged_prefill (mma.sync)", ours)]
-        if not fp8:
-            impls.append(("b200attn paged_prefill (tcgen05/TMEM)", ours_umma))
+        impls.append(("b200attn paged_prefill (tcgen05/TMEM" + (", fp8 pages staged as bf16 per call)" if fp8 else ")"),
+                      ours_umma))
         if not fp8:
             out2 = torch.empty_like(q)
             for ver in (2, 4):

@@ -16,24 +16,28 @@ TOL = 2e-3
 @pytest.fixture(autouse=True, params=["mma_sync", "umma"])
 def prefill_kernel(request, monkeypatch):
     """Every case runs on both prefill kernels: the mma.sync one (paged_prefill.cu) and the tcgen05 / TMEM one
-    (paged_prefill_umma.cu, bf16 caches). The library reads the switch at every call."""
-    if request.param == "umma" and request.node.callspec.params.get("fp8", False):
-        pytest.skip("fp8 caches are served by the mma.sync kernel")
+    (paged_prefill_umma.cu; fp8 caches reach it through the bf16 staging of b200attn_paged_prefill_fp8_staged).
+    The library and ops.paged_prefill read the switch at every call."""
     monkeypatch.setenv("B200ATTN_PREFILL_UMMA", "1" if request.param == "umma" else "0")
     return request.param
 
 
-def run_prefill(c, q_lens, hq, seed=0, q_std=1.0):
+def run_prefill(c, q_lens, hq, seed=0, q_std=1.0, total_kv_tokens=0):
     g = torch.Generator().manual_seed(seed)
     T = sum(q_lens)
     q = (torch.randn(T, hq, 128, generator=g) * q_std).to(torch.bfloat16)
     qsl = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32)
     cache = cache_to_dev(c.kv_cache)
     out = torch.full((T, hq, 128), 7.0, dtype=torch.bfloat16, device="cuda")
+    staging = ops.PrefillStaging("cuda") if c.fp8 else None
     ops.paged_prefill(q.cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl.cuda(),
                       max(q_lens), c.scale, out=out, kv_cache_dtype=c.kv_cache_dtype, k_scale=to_dev(c.k_scale),
-                      v_scale=to_dev(c.v_scale))
+                      v_scale=to_dev(c.v_scale), staging=staging, max_seq_len=c.max_seq_len,
+                      total_kv_tokens=total_kv_tokens)
     torch.cuda.synchronize()
+    if c.fp8:  # the staged path ran exactly when the tcgen05 kernel is selected
+        import os
+        assert (staging.buf is not None) == (os.environ["B200ATTN_PREFILL_UMMA"] == "1")
     ref = oracle.ref_paged_prefill(q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, c.scale,
                                    c.fp8, c.k_scale, c.v_scale)
     return out, ref
@@ -75,11 +79,60 @@ def test_prefill_gqa_group_shapes(lib, hq, hkv, fp8):
     check(out, ref)
 
 
+@pytest.mark.parametrize("fp8", [False, True])
 @pytest.mark.parametrize("bs", [32, 64])
-def test_prefill_larger_block_sizes(lib, bs):
-    c = make_case([200, 65], hq=8, hkv=2, bs=bs, seed=bs)
+def test_prefill_larger_block_sizes(lib, bs, fp8):
+    c = make_case([200, 65], hq=8, hkv=2, bs=bs, seed=bs, fp8=fp8)
     out, ref = run_prefill(c, [200, 3], 8)
     check(out, ref)
+
+
+@pytest.mark.parametrize("per_head", [True, False])
+def test_fp8_prefill_staging_ragged_batch(lib, per_head):
+    """Staged fp8 pages: ragged lengths (a sequence of one token, lengths on and off page boundaries), garbage in the
+    unused slots, the tight page budget (sum of the lengths known on the host), per-head and scalar scales — and a
+    second step on the same staging buffer with other sequences."""
+    staging = ops.PrefillStaging("cuda")
+    for lens, q_lens, seed in (([1, 700, 16, 33, 2048, 95], [1, 300, 16, 2, 64, 95], 3), ([129, 40], [129, 7], 4)):
+        c = make_case(lens, hq=16, hkv=2, seed=seed, fp8=True, per_head_scale=per_head, garbage_fill=True)
+        g = torch.Generator().manual_seed(seed)
+        q = torch.randn(sum(q_lens), 16, 128, generator=g).to(torch.bfloat16)
+        qsl = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32)
+        cache = cache_to_dev(c.kv_cache)
+        out = ops.paged_prefill(q.cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl.cuda(),
+                                max(q_lens), c.scale, kv_cache_dtype=c.kv_cache_dtype, k_scale=to_dev(c.k_scale),
+                                v_scale=to_dev(c.v_scale), staging=staging, max_seq_len=max(lens),
+                                total_kv_tokens=sum(lens))
+        torch.cuda.synchronize()
+        ref = oracle.ref_paged_prefill(q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, c.scale,
+                                       True, c.k_scale, c.v_scale)
+        check(out, ref)
+
+
+def test_fp8_prefill_staging_too_small_is_rejected(lib, prefill_kernel):
+    from vllm_omni_b200 import _lib
+    if prefill_kernel != "umma":
+        pytest.skip("one run is enough")
+    c = make_case([100], hq=8, hkv=1, seed=1, fp8=True)
+    cache = cache_to_dev(c.kv_cache)
+    q = torch.zeros(4, 8, 128, dtype=torch.bfloat16, device="cuda")
+    qsl = torch.tensor([0, 4], dtype=torch.int32).cuda()
+    need = ops.prefill_staging_bytes(1, 100, 0, 1, 128, 16)
+    assert need >= 7 * 2 * 16 * 128 * 2
+    small = torch.empty(need - 1024, dtype=torch.uint8, device="cuda")
+    off = (-small.data_ptr()) % 1024
+    rc = lib.b200attn_paged_prefill_fp8_staged(
+        q.data_ptr(), q.stride(0), cache[0].data_ptr(), cache[1].data_ptr(), cache[0].stride(0), cache[0].stride(1),
+        cache[0].stride(2), cache[0].shape[0], q.data_ptr(), q.stride(0), c.block_table.cuda().data_ptr(),
+        c.block_table.stride(0), c.seq_lens.cuda().data_ptr(), qsl.data_ptr(), 1, 4, 4, 100, 0, 8, 1, 128, 16, 0.1,
+        to_dev(c.k_scale).data_ptr(), to_dev(c.v_scale).data_ptr(), 1, small.data_ptr() + off, small.numel() - off,
+        None)
+    assert rc == -_lib_code("EWORKSPACE") and b"staging needs" in lib.b200attn_last_error()
+
+
+def _lib_code(name):
+    from vllm_omni_b200 import _lib
+    return {v: k for k, v in _lib.ERRORS.items()}[name]
 
 
 def test_prefill_last_row_equals_decode_kernel(lib):

@@ -109,6 +109,19 @@ SIGNATURES: dict[str, tuple] = {
         _i32, _i32, _i32, _i32,
         _f32, _i32,
         _vp, _vp, _i32, _vp]),
+    "b200attn_prefill_staging_bytes": (_sz, [_i32, _i32, _i64, _i32, _i32, _i32]),
+    "b200attn_paged_prefill_fp8_staged": (C.c_int, [
+        _vp, _i64,
+        _vp, _vp, *_CACHE_ARGS, _i64,
+        _vp, _i64,
+        _vp, _i64,
+        _vp, _vp,
+        _i32, _i32, _i32,
+        _i32, _i64,                      # max_seq_len, total_kv_tokens
+        _i32, _i32, _i32, _i32,
+        _f32,
+        _vp, _vp, _i32,
+        _vp, _sz, _vp]),                 # staging, bytes, stream
     "b200attn_gather_kv": (C.c_int, [
         _vp, *_CACHE_ARGS, _i64, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "b200attn_peer_allreduce_algo": (_i32, [_i64, _i32, _i32, _i64]),

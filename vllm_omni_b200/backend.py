@@ -112,6 +112,9 @@ class B200AttentionMetadata:
     causal: bool = True
     # the step's stream-K plan is in `workspace` (made once by the builder; every layer's decode skips its own)
     decode_planned: bool = False
+    # fp8 caches: bf16 staging of the prefill sequences' pages for the tcgen05 prefill kernel (shared by the layers)
+    prefill_staging: ops.PrefillStaging | None = None
+    prefill_total_kv_tokens: int = 0  # host bound of sum(seq_lens[num_decodes:]), 0 = unknown
 
 
 class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadata]):
@@ -136,6 +139,7 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.max_model_len = mc.max_model_len
         self.max_num_seqs = vllm_config.scheduler_config.max_num_seqs
         self._sms = ops.num_sms()
+        self.prefill_staging = ops.PrefillStaging(device)  # nothing is allocated until an fp8 prefill needs it
         # the stream-K schedules' workspace is batch-independent apart from the plan's [batch + 1] prefix; the
         # fixed-split fallback (only taken when stream-K does not fit, i.e. never with this size) is not provisioned
         self.workspace = ops.DecodeWorkspace(device, ops.decode_workspace_bytes(
@@ -169,18 +173,21 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             ops.decode_plan(cam.seq_lens, cam.block_table_tensor, nd, self.num_heads_q, self.num_heads_kv,
                             self.block_size, self.workspace)
             planned = True
-        pqsl, pmax = None, 0
+        pqsl, pmax, ptotal = None, 0, 0
         if np_ > 0:
             pqsl = cam.query_start_loc[nd:] - ndt
             cpu = cam.query_start_loc_cpu
             pmax = int((cpu[nd + 1:] - cpu[nd:-1]).max()) if nd > 0 else cam.max_query_len
+            ub = getattr(cam, "seq_lens_cpu_upper_bound", None)  # host copy without a sync (newer vLLM only)
+            ptotal = int(ub[nd:nd + np_].sum()) if ub is not None else 0
         return B200AttentionMetadata(
             num_actual_tokens=cam.num_actual_tokens, max_query_len=cam.max_query_len,
             query_start_loc=cam.query_start_loc, max_seq_len=cam.max_seq_len, seq_lens=cam.seq_lens,
             block_table=cam.block_table_tensor, slot_mapping=cam.slot_mapping, num_decodes=nd,
             num_decode_tokens=ndt, num_prefills=np_, num_prefill_tokens=npt,
             prefill_query_start_loc=pqsl, prefill_max_query_len=pmax, decode_num_splits=splits,
-            workspace=self.workspace, causal=cam.causal, decode_planned=planned)
+            workspace=self.workspace, causal=cam.causal, decode_planned=planned,
+            prefill_staging=self.prefill_staging, prefill_total_kv_tokens=ptotal)
 
 
 def _batch_sizes(max_num_seqs: int):
@@ -340,5 +347,6 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
             ops.paged_prefill(q[ndt:n], k_cache, v_cache, md.block_table[nd:], md.seq_lens[nd:],
                               md.prefill_query_start_loc, md.prefill_max_query_len, self.scale,
                               out=out[ndt:n], kv_cache_dtype=self._kv_code, k_scale=k_scale,
-                              v_scale=v_scale)
+                              v_scale=v_scale, staging=md.prefill_staging, max_seq_len=md.max_seq_len,
+                              total_kv_tokens=md.prefill_total_kv_tokens)
         return output

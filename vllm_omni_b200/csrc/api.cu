@@ -1131,8 +1131,8 @@ int b200attn_paged_prefill(const void* q, int64_t q_stride_tok, const void* k_ca
   p.tpp_shift = shift;
   p.tpp_mask = tpp - 1;
   p.scale_log2 = softmax_scale * kLog2e;
-  p.k_scale = k_scale;
-  p.v_scale = v_scale;
+  p.k_scale = fp8 ? k_scale : nullptr;  // bf16 caches carry no scales (the tcgen05 kernel applies any it is given)
+  p.v_scale = fp8 ? v_scale : nullptr;
   p.scale_stride = scale_numel > 1 ? 1 : 0;
   // bf16 caches: the tcgen05 / TMEM kernel (B200ATTN_PREFILL_UMMA=0 selects the mma.sync kernel, which also serves fp8)
   const bool umma = !fp8 && env_flag("B200ATTN_PREFILL_UMMA", kPrefillUmmaDefault);
@@ -1147,6 +1147,139 @@ int b200attn_paged_prefill(const void* q, int64_t q_stride_tok, const void* k_ca
   cudaError_t e = umma ? launch_paged_prefill_umma(tm_k, *mv, p, static_cast<cudaStream_t>(stream))
                        : launch_paged_prefill(tm_k, *mv, p, fp8, static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? 0 : cuda_fail(e, "paged_prefill launch");
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp8 prefill on the tcgen05 kernel: stage the step's e4m3 pages as bf16 (cache_ops.cu), then run
+// paged_prefill_umma_kernel over the staged pages with the scales folded in.
+// staging = [pages | cum: batch + 1 i32 | staged block table: batch x max_pages i32], each part 1 KiB aligned
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct StageLayout {
+  size_t cum_off, bt_off, pages_off, page_bytes, total;
+  int64_t capacity_pages;
+  int max_pages;
+};
+StageLayout stage_layout(int batch, int max_seq_len, int64_t total_kv_tokens, int num_kv_heads, int head_size,
+                         int block_size) {
+  StageLayout l{};
+  l.max_pages = (max_seq_len + block_size - 1) / block_size;
+  if (l.max_pages < 1) l.max_pages = 1;
+  int64_t cap = static_cast<int64_t>(batch) * l.max_pages;
+  if (total_kv_tokens > 0) {  // sum over the sequences of ceil(S / bs) <= sum(S) / bs + batch
+    const int64_t tight = total_kv_tokens / block_size + batch;
+    if (tight < cap) cap = tight;
+  }
+  l.capacity_pages = cap;
+  // pages first: their address (and with it the cached tensor map) does not move with the batch
+  const size_t a = 1024;
+  l.page_bytes = static_cast<size_t>(num_kv_heads) * 2 * block_size * head_size * sizeof(__nv_bfloat16);
+  l.pages_off = 0;
+  l.cum_off = (static_cast<size_t>(cap) * l.page_bytes + a - 1) / a * a;
+  l.bt_off = l.cum_off + ((static_cast<size_t>(batch) + 1) * sizeof(int32_t) + a - 1) / a * a;
+  l.total = l.bt_off + (static_cast<size_t>(batch) * l.max_pages * sizeof(int32_t) + a - 1) / a * a;
+  return l;
+}
+}  // namespace
+
+size_t b200attn_prefill_staging_bytes(int32_t batch, int32_t max_seq_len, int64_t total_kv_tokens,
+                                      int32_t num_kv_heads, int32_t head_size, int32_t block_size) {
+  if (batch <= 0 || max_seq_len <= 0 || num_kv_heads <= 0 || head_size <= 0 || block_size <= 0) return 0;
+  return stage_layout(batch, max_seq_len, total_kv_tokens, num_kv_heads, head_size, block_size).total;
+}
+
+int b200attn_paged_prefill_fp8_staged(const void* q, int64_t q_stride_tok, const void* k_cache, const void* v_cache,
+                                      int64_t cache_stride_block, int64_t cache_stride_slot, int64_t cache_stride_head,
+                                      int64_t num_blocks, void* out, int64_t out_stride_tok, const int32_t* block_table,
+                                      int64_t block_table_stride, const int32_t* seq_lens,
+                                      const int32_t* query_start_loc, int32_t batch, int32_t num_tokens,
+                                      int32_t max_query_len, int32_t max_seq_len, int64_t total_kv_tokens,
+                                      int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+                                      float softmax_scale, const float* k_scale, const float* v_scale,
+                                      int32_t scale_numel, void* staging, size_t staging_bytes, void* stream) {
+  (void)max_query_len;
+  if (batch < 0 || num_tokens < 0) return fail(B200ATTN_EINVAL, "batch/num_tokens < 0");
+  if (batch == 0 || num_tokens == 0) return 0;
+  if (q == nullptr || out == nullptr || block_table == nullptr || seq_lens == nullptr || query_start_loc == nullptr)
+    return fail(B200ATTN_EINVAL, "null q/out/block_table/seq_lens/query_start_loc");
+  if (num_q_heads <= 0 || num_kv_heads <= 0 || (num_q_heads % num_kv_heads) != 0)
+    return fail(B200ATTN_EINVAL, "num_q_heads %d not a multiple of num_kv_heads %d", num_q_heads, num_kv_heads);
+  if (int rc = check_cache_args(k_cache, v_cache, cache_stride_block, cache_stride_slot, cache_stride_head,
+                                num_blocks, num_kv_heads, head_size, block_size, B200ATTN_KV_FP8_E4M3))
+    return rc;
+  if ((q_stride_tok % 2) || (reinterpret_cast<uintptr_t>(q) % 4))
+    return fail(B200ATTN_EINVAL, "q rows must be 4-byte aligned");
+  if ((out_stride_tok % 4) || (reinterpret_cast<uintptr_t>(out) % 8))
+    return fail(B200ATTN_EINVAL, "out rows must be 8-byte aligned");
+  const int tpp = block_size / kTileTokens;
+  int shift = -1;
+  for (int sh = 0; sh < 16; ++sh)
+    if ((1 << sh) == tpp) shift = sh;
+  if (shift < 0) return fail(B200ATTN_EUNSUPPORTED, "prefill needs block_size = 16 * 2^k (got %d)", block_size);
+  if (k_scale == nullptr || v_scale == nullptr) return fail(B200ATTN_EINVAL, "fp8 cache needs scales");
+  if (scale_numel != 1 && scale_numel != num_kv_heads)
+    return fail(B200ATTN_EINVAL, "scale_numel %d must be 1 or num_kv_heads", scale_numel);
+  if (max_seq_len < 1) return fail(B200ATTN_EINVAL, "max_seq_len must bound the sequences of the step (got %d)", max_seq_len);
+  const StageLayout l = stage_layout(batch, max_seq_len, total_kv_tokens, num_kv_heads, head_size, block_size);
+  if (staging == nullptr || staging_bytes < l.total || (reinterpret_cast<uintptr_t>(staging) % 1024))
+    return fail(B200ATTN_EWORKSPACE, "fp8 prefill staging needs %zu B, 1 KiB aligned (got %zu)", l.total, staging_bytes);
+  if (l.capacity_pages > 0x7fffffff) return fail(B200ATTN_EINVAL, "too many staged pages");
+  uint8_t* base = static_cast<uint8_t*>(staging);
+  StageFp8Params sp{};
+  sp.k_cache = static_cast<const uint8_t*>(k_cache);
+  sp.v_cache = static_cast<const uint8_t*>(v_cache);
+  sp.cs_block = cache_stride_block;
+  sp.cs_slot = cache_stride_slot;
+  sp.cs_head = cache_stride_head;
+  sp.num_blocks = num_blocks;
+  sp.block_table = block_table;
+  sp.bt_stride = block_table_stride;
+  sp.seq_lens = seq_lens;
+  sp.batch = batch;
+  sp.max_pages = l.max_pages;
+  sp.num_kv_heads = num_kv_heads;
+  sp.block_size = block_size;
+  sp.capacity_pages = l.capacity_pages;
+  sp.cum = reinterpret_cast<int32_t*>(base + l.cum_off);
+  sp.stage_bt = reinterpret_cast<int32_t*>(base + l.bt_off);
+  sp.pages = reinterpret_cast<__nv_bfloat16*>(base + l.pages_off);
+  if (cudaError_t e = launch_stage_fp8(sp, static_cast<cudaStream_t>(stream))) return cuda_fail(e, "fp8 staging launch");
+
+  PrefillParams p{};
+  p.q = static_cast<const __nv_bfloat16*>(q);
+  p.q_stride_tok = q_stride_tok;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.out_stride_tok = out_stride_tok;
+  p.block_table = sp.stage_bt;
+  p.bt_stride = l.max_pages;
+  p.seq_lens = seq_lens;
+  p.query_start_loc = query_start_loc;
+  p.batch = batch;
+  p.num_tokens = num_tokens;
+  p.num_q_heads = num_q_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.group = num_q_heads / num_kv_heads;
+  p.subgroups = (p.group + kHeadsPerItem - 1) / kHeadsPerItem;
+  p.tpp_shift = shift;
+  p.tpp_mask = tpp - 1;
+  p.scale_log2 = softmax_scale * kLog2e;
+  p.k_scale = k_scale;
+  p.v_scale = v_scale;
+  p.scale_stride = scale_numel > 1 ? 1 : 0;
+  // the staged pages as a bf16 cache in the product layout [page][Hkv][K|V][bs][d]
+  const int64_t s_slot = head_size, s_head = 2ll * block_size * head_size, s_block = s_head * num_kv_heads;
+  const __nv_bfloat16* sk = sp.pages;
+  const __nv_bfloat16* sv = sp.pages + static_cast<int64_t>(block_size) * head_size;
+  const CUtensorMap *mk = nullptr, *mv = nullptr;
+  // page dimension of the map = what the caller's buffer could hold: one encode per staging buffer, not per step
+  const int64_t map_pages = static_cast<int64_t>(staging_bytes / l.page_bytes);
+  if (int rc = get_kv_map5(sk, s_block, s_slot, s_head, map_pages, num_kv_heads, block_size, false, &mk, 1))
+    return rc;
+  const CUtensorMap tm_k = *mk;  // copy before the second lookup can evict it
+  if (int rc = get_kv_map5(sv, s_block, s_slot, s_head, map_pages, num_kv_heads, block_size, false, &mv, 1))
+    return rc;
+  cudaError_t e = launch_paged_prefill_umma(tm_k, *mv, p, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? 0 : cuda_fail(e, "paged_prefill (staged fp8) launch");
 }
 
 int b200attn_gather_kv(const void* cache, int64_t cache_stride_block, int64_t cache_stride_slot,

@@ -75,6 +75,23 @@ cudaError_t launch_paged_prefill_umma(const CUtensorMap& tm_k, const CUtensorMap
                                       cudaStream_t stream);
 size_t prefill_umma_smem_bytes();
 
+// fp8 prefill staging (cache_ops.cu): e4m3 pages of the step's prefill sequences -> bf16 pages + their block table
+struct StageFp8Params {
+  const uint8_t* k_cache;
+  const uint8_t* v_cache;
+  int64_t cs_block, cs_slot, cs_head;  // bytes (= e4m3 elements)
+  int64_t num_blocks;
+  const int32_t* block_table;
+  int64_t bt_stride;
+  const int32_t* seq_lens;
+  int32_t batch, max_pages, num_kv_heads, block_size;
+  int64_t capacity_pages;
+  int32_t* cum;          // [batch + 1] exclusive prefix of pages per sequence
+  int32_t* stage_bt;     // [batch][max_pages] staged page ids
+  __nv_bfloat16* pages;  // [capacity_pages][Hkv][2][bs][128]
+};
+cudaError_t launch_stage_fp8(const StageFp8Params& p, cudaStream_t stream);
+
 struct CacheWriteParams {
   const __nv_bfloat16* key;
   const __nv_bfloat16* value;

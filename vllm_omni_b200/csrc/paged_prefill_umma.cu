@@ -3,7 +3,8 @@
 // 8 query heads of one KV head = 128 rows are exactly one M = 128 UMMA tile with no padding at G = 8, and a CTA
 // owns TWO such tiles (32 consecutive query tokens) that share every staged K/V block, which halves the L2 -> SM
 // traffic that bounded the one-tile version (measured 408 TFLOP/s at 3.1 TB/s of L2 reads).
-// The mma.sync kernel in paged_prefill.cu stays the path for FP8 caches and is the comparison point.
+// FP8 caches reach this kernel through the bf16 staging of cache_ops.cu (stage_fp8_pages_kernel, scales applied
+// here); the mma.sync kernel in paged_prefill.cu is the unstaged fp8 path and the comparison point.
 // Same call as paged_prefill.cu (vllm/v1/attention/backends/flash_attn.py:758-819 with max_query_len > 1).
 //
 // Per KV block of 64 tokens (4 pages of 16) and per tile t:
@@ -228,7 +229,9 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     const int pos = ctx0 + i0 + i;  // cache position of this row's query token
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t tm_o = tmem + 256 + t * 128 + lane_off;
-    const float scale = p.scale_log2;
+    // staged fp8 caches (b200attn_paged_prefill_fp8_staged): K and V hold the raw e4m3 values, the head's
+    // dequantisation scales are folded into the softmax scale and the final normalisation
+    const float scale = p.scale_log2 * (p.k_scale != nullptr ? __ldg(p.k_scale + kvh * p.scale_stride) : 1.f);
     float m = -CUDART_INF_F, l = 0.f;
     for (int j = 0; j < nblk; ++j) {
       const int buf = j & 1, st = j % kUpStages;
@@ -338,7 +341,7 @@ paged_prefill_umma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid
     }
     // ---- epilogue: O / l -> bf16 -> global (256 contiguous bytes per row)
     uint32_t x[32];
-    const float inv = l > 0.f ? 1.f / l : 0.f;
+    const float inv = (l > 0.f ? 1.f / l : 0.f) * (p.v_scale != nullptr ? __ldg(p.v_scale + kvh * p.scale_stride) : 1.f);
     if (nblk > 0) {
       mbar_wait(&sm.pv_done[t], (nblk - 1) & 1);
       tc_fence_after_sync();

@@ -372,11 +372,56 @@ def lse_reduce(out: torch.Tensor, seq_lens: torch.Tensor, max_seq_len: int, num_
         int(num_splits), int(variant), workspace.ptr, workspace.nbytes, _stream()))
 
 
+class PrefillStaging:
+    """Caller-owned bf16 staging of the fp8 pages a step's prefill sequences own (b200attn_paged_prefill_fp8_staged):
+    one buffer serves every layer of a step in turn; grown on demand, outside graphs."""
+
+    def __init__(self, device: torch.device | str = "cuda"):
+        self.device = torch.device(device)
+        self.buf: torch.Tensor | None = None
+
+    def ensure(self, nbytes: int) -> None:
+        if self.buf is None or self.buf.numel() < nbytes:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("fp8 prefill staging too small and cannot grow during graph capture")
+            self.buf = None  # release before the larger allocation
+            self.buf = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=self.device)
+
+    @property
+    def ptr(self) -> int:
+        return self.buf.data_ptr()
+
+    @property
+    def nbytes(self) -> int:
+        return self.buf.numel()
+
+
+def prefill_staging_bytes(batch: int, max_seq_len: int, total_kv_tokens: int, num_kv_heads: int, head_size: int,
+                          block_size: int) -> int:
+    return int(_lib.load().b200attn_prefill_staging_bytes(int(batch), int(max_seq_len), int(total_kv_tokens),
+                                                          int(num_kv_heads), int(head_size), int(block_size)))
+
+
+def _fp8_prefill_staged_enabled() -> bool:
+    """fp8 caches take the tcgen05 kernel through the bf16 staging unless B200ATTN_PREFILL_UMMA=0 (the switch that
+    also sends bf16 caches to the mma.sync kernel) or B200ATTN_PREFILL_FP8_STAGED=0."""
+    import os
+    off = ("0", "n", "N", "f", "F")
+    return not (os.environ.get("B200ATTN_PREFILL_UMMA", "1")[:1] in off
+                or os.environ.get("B200ATTN_PREFILL_FP8_STAGED", "1")[:1] in off)
+
+
 def paged_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                   block_table: torch.Tensor, seq_lens: torch.Tensor, query_start_loc: torch.Tensor,
                   max_query_len: int, softmax_scale: float, out: torch.Tensor | None = None,
-                  kv_cache_dtype: str | int = "auto", k_scale=None, v_scale=None) -> torch.Tensor:
-    """Causal varlen attention over the paged cache (prefill / extend / mixed batches)."""
+                  kv_cache_dtype: str | int = "auto", k_scale=None, v_scale=None,
+                  staging: PrefillStaging | None = None, max_seq_len: int = 0,
+                  total_kv_tokens: int = 0) -> torch.Tensor:
+    """Causal varlen attention over the paged cache (prefill / extend / mixed batches).
+
+    staging + max_seq_len (host bound of seq_lens; total_kv_tokens = host bound of their sum, 0 if unknown): fp8
+    caches are staged as bf16 pages and served by the tcgen05 kernel (b200attn_paged_prefill_fp8_staged); without
+    them fp8 caches run on the mma.sync kernel."""
     lib = _lib.load()
     _need_cuda(q, k_cache, v_cache, block_table, seq_lens, query_start_loc)
     if out is None:
@@ -393,6 +438,16 @@ def paged_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         raise ValueError("query_start_loc/seq_lens must be int32")
     batch = query_start_loc.numel() - 1
     ks, vs, sn = _scales(k_scale, v_scale, fp8)
+    if fp8 and staging is not None and max_seq_len > 0 and batch > 0 and _fp8_prefill_staged_enabled():
+        staging.ensure(prefill_staging_bytes(batch, max_seq_len, total_kv_tokens, hkv, d, bs))
+        off = (-staging.ptr) % 1024  # the library wants the staging 1 KiB aligned
+        check("b200attn_paged_prefill_fp8_staged", lib.b200attn_paged_prefill_fp8_staged(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, nb,
+            out.data_ptr(), out.stride(0), block_table.data_ptr(), block_table.stride(0),
+            seq_lens.data_ptr(), query_start_loc.data_ptr(), batch, q.shape[0], int(max_query_len),
+            int(max_seq_len), int(total_kv_tokens), q.shape[1], hkv, d, bs, float(softmax_scale), ks, vs, sn,
+            staging.ptr + off, staging.nbytes - off, _stream()))
+        return out
     check("b200attn_paged_prefill", lib.b200attn_paged_prefill(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), sb, ss, sh, nb,
         out.data_ptr(), out.stride(0), block_table.data_ptr(), block_table.stride(0),
