@@ -318,6 +318,8 @@ B200ATTN_API int b200attn_lse_reduce(
  * prefill / extend, mixed batches). Correctness path for the non-decode tokens a
  * registered backend also receives (vllm/v1/attention/backends/flash_attn.py:758-819 with
  * max_query_len > 1). The new tokens' K/V must already be in the cache.
+ * bf16 caches run on the tcgen05 / TMEM kernel; fp8 caches on the mma.sync kernel here, and on the tcgen05 kernel
+ * through b200attn_paged_prefill_fp8_staged below.
  *
  * Sequence b owns query rows [query_start_loc[b], query_start_loc[b+1]); with
  * q_len = their count and S_b = seq_lens[b], query i (0-based) attends to cache
