@@ -201,3 +201,17 @@ def test_oracle_all_reduce_is_sequential_fp32_then_one_rounding():
     c = torch.tensor([0.00390625, 1.0, 0.0]).to(torch.bfloat16)
     out = oracle.ref_all_reduce_bf16([a, b, c])
     assert out.tolist() == [1.0078125, 258.0, 0.0]                    # 1 + 2^-7 is representable; a bf16 running sum would give 1.0
+
+
+def test_fp8_prefill_staging_size_is_host_arithmetic(lib):
+    """b200attn_prefill_staging_bytes: pages for batch x ceil(max_seq_len / bs), or for the tighter host bound of the
+    summed lengths, plus the prefix and the staged block table (each part rounded to 1 KiB)."""
+    f = lib.b200attn_prefill_staging_bytes
+    page = 4 * 2 * 16 * 128 * 2                       # [Hkv][K|V][bs][d] bf16
+    up = lambda n: (n + 1023) // 1024 * 1024          # noqa: E731
+    dense = f(3, 1000, 0, 4, 128, 16)
+    assert dense == 3 * 63 * page + up(4 * 4) + up(3 * 63 * 4)
+    tight = f(3, 1000, 1100, 4, 128, 16)              # 1100 tokens in all: at most 1100 // 16 + 3 pages
+    assert tight == up(71 * page) + up(4 * 4) + up(3 * 63 * 4) and tight < dense
+    assert f(3, 1000, 10 ** 9, 4, 128, 16) == dense   # a useless bound changes nothing
+    assert f(0, 1000, 0, 4, 128, 16) == 0 and f(3, 0, 0, 4, 128, 16) == 0
