@@ -73,6 +73,7 @@ for fp8 in ((False,) if "--bf16-only" in sys.argv else (True,) if "--fp8-only" i
                 os.environ["B200ATTN_PREFILL_UMMA"] = "0"
 
         os.environ["B200ATTN_PREFILL_UMMA"] = "0"
+        os.environ["B200ATTN_PREFILL_FP8_STAGED"] = "force"  # time the staged path on every case (default: a rule)
         impls = [("b200attn paged_prefill (mma.sync)", ours)]
         impls.append(("b200attn paged_prefill (tcgen05/TMEM" + (", fp8 pages staged as bf16 per call)" if fp8 else ")"),
                       ours_umma))

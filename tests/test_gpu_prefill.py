@@ -19,6 +19,8 @@ def prefill_kernel(request, monkeypatch):
     (paged_prefill_umma.cu; fp8 caches reach it through the bf16 staging of b200attn_paged_prefill_fp8_staged).
     The library and ops.paged_prefill read the switch at every call."""
     monkeypatch.setenv("B200ATTN_PREFILL_UMMA", "1" if request.param == "umma" else "0")
+    # fp8: always staged in the tcgen05 runs (the default stages only calls with enough new tokens per sequence)
+    monkeypatch.setenv("B200ATTN_PREFILL_FP8_STAGED", "force")
     return request.param
 
 
@@ -107,6 +109,28 @@ def test_fp8_prefill_staging_ragged_batch(lib, per_head):
         ref = oracle.ref_paged_prefill(q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, c.scale,
                                        True, c.k_scale, c.v_scale)
         check(out, ref)
+
+
+def test_fp8_prefill_staging_rule(lib, prefill_kernel, monkeypatch):
+    """Default policy of ops.paged_prefill: stage when group x new tokens per sequence >= 256 (long prompts, chunked
+    prefill), not for a few new tokens per sequence over long contexts."""
+    if prefill_kernel != "umma":
+        pytest.skip("one run is enough")
+    monkeypatch.setenv("B200ATTN_PREFILL_FP8_STAGED", "1")
+    for lens, q_lens, staged in (([300, 200], [300, 150], True), ([300, 200, 150], [3, 2, 1], False)):
+        c = make_case(lens, hq=8, hkv=1, seed=7, fp8=True)
+        staging = ops.PrefillStaging("cuda")
+        g = torch.Generator().manual_seed(5)
+        q = torch.randn(sum(q_lens), 8, 128, generator=g).to(torch.bfloat16)
+        qsl = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32)
+        cache = cache_to_dev(c.kv_cache)
+        out = ops.paged_prefill(q.cuda(), cache[0], cache[1], c.block_table.cuda(), c.seq_lens.cuda(), qsl.cuda(),
+                                max(q_lens), c.scale, kv_cache_dtype=c.kv_cache_dtype, k_scale=to_dev(c.k_scale),
+                                v_scale=to_dev(c.v_scale), staging=staging, max_seq_len=max(lens))
+        torch.cuda.synchronize()
+        assert (staging.buf is not None) == staged
+        check(out, oracle.ref_paged_prefill(q, c.kv_cache[0], c.kv_cache[1], c.block_table, c.seq_lens, qsl, c.scale,
+                                            True, c.k_scale, c.v_scale))
 
 
 def test_fp8_prefill_staging_too_small_is_rejected(lib, prefill_kernel):

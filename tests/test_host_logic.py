@@ -215,3 +215,22 @@ def test_fp8_prefill_staging_size_is_host_arithmetic(lib):
     assert tight == up(71 * page) + up(4 * 4) + up(3 * 63 * 4) and tight < dense
     assert f(3, 1000, 10 ** 9, 4, 128, 16) == dense   # a useless bound changes nothing
     assert f(0, 1000, 0, 4, 128, 16) == 0 and f(3, 0, 0, 4, 128, 16) == 0
+
+
+def test_fp8_prefill_staging_rule_is_host_arithmetic(monkeypatch):
+    """ops._fp8_prefill_staged: group x new tokens per sequence >= 256 (break-even ~210, see its docstring)."""
+    from vllm_omni_b200 import ops
+    monkeypatch.delenv("B200ATTN_PREFILL_FP8_STAGED", raising=False)
+    monkeypatch.delenv("B200ATTN_PREFILL_UMMA", raising=False)
+    assert ops._fp8_prefill_staged(8192, 1, 8)            # one long prompt
+    assert ops._fp8_prefill_staged(16 * 64, 16, 8)        # 64 new tokens on each of 16 contexts (measured 1.9x)
+    assert not ops._fp8_prefill_staged(16 * 16, 16, 8)    # 16 new tokens each: the staging would cost what it saves
+    assert not ops._fp8_prefill_staged(64 * 4, 64, 8)     # speculative decoding rows
+    assert ops._fp8_prefill_staged(64 * 64, 64, 4) and not ops._fp8_prefill_staged(64 * 32, 64, 4)
+    monkeypatch.setenv("B200ATTN_PREFILL_FP8_STAGED", "force")
+    assert ops._fp8_prefill_staged(3, 3, 8)
+    monkeypatch.setenv("B200ATTN_PREFILL_UMMA", "0")
+    assert not ops._fp8_prefill_staged(8192, 1, 8)
+    monkeypatch.setenv("B200ATTN_PREFILL_UMMA", "1")
+    monkeypatch.setenv("B200ATTN_PREFILL_FP8_STAGED", "0")
+    assert not ops._fp8_prefill_staged(8192, 1, 8)

@@ -402,13 +402,24 @@ def prefill_staging_bytes(batch: int, max_seq_len: int, total_kv_tokens: int, nu
                                                           int(num_kv_heads), int(head_size), int(block_size)))
 
 
-def _fp8_prefill_staged_enabled() -> bool:
-    """fp8 caches take the tcgen05 kernel through the bf16 staging unless B200ATTN_PREFILL_UMMA=0 (the switch that
-    also sends bf16 caches to the mma.sync kernel) or B200ATTN_PREFILL_FP8_STAGED=0."""
+def _fp8_prefill_staged(num_tokens: int, batch: int, group: int) -> bool:
+    """Whether an fp8 prefill call takes the tcgen05 kernel through the bf16 staging.
+
+    Staging moves 5 B per cached element of every sequence of the call; the tcgen05 kernel saves about
+    (1/200 - 1/750) ps per flop against the mma.sync fp8 kernel (profiles/r2_prefill_fp8_staged.jsonl). With
+    flops ~ 512 * group * new tokens * context / 2 per KV head the two meet at about 210 = group * new tokens per
+    sequence: long prompts and chunked prefill gain 2-3.7x, short extends over long contexts (speculative decoding:
+    a handful of new tokens per sequence) would lose — those stay on the mma.sync kernel.
+    B200ATTN_PREFILL_FP8_STAGED: 0 = never, force = always, otherwise the rule above; B200ATTN_PREFILL_UMMA=0 (the
+    switch that also sends bf16 caches to the mma.sync kernel) turns it off too."""
     import os
-    off = ("0", "n", "N", "f", "F")
-    return not (os.environ.get("B200ATTN_PREFILL_UMMA", "1")[:1] in off
-                or os.environ.get("B200ATTN_PREFILL_FP8_STAGED", "1")[:1] in off)
+    mode = os.environ.get("B200ATTN_PREFILL_FP8_STAGED", "1").lower()
+    if os.environ.get("B200ATTN_PREFILL_UMMA", "1")[:1] in ("0", "n", "N", "f", "F") or mode in ("0", "n", "no", "f", "false", "off"):
+        return False
+    return mode == "force" or num_tokens * group >= FP8_STAGED_MIN_WORK * batch
+
+
+FP8_STAGED_MIN_WORK = 256  # group x new tokens per sequence from which the staged fp8 prefill pays (break-even ~210)
 
 
 def paged_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
@@ -420,8 +431,9 @@ def paged_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     """Causal varlen attention over the paged cache (prefill / extend / mixed batches).
 
     staging + max_seq_len (host bound of seq_lens; total_kv_tokens = host bound of their sum, 0 if unknown): fp8
-    caches are staged as bf16 pages and served by the tcgen05 kernel (b200attn_paged_prefill_fp8_staged); without
-    them fp8 caches run on the mma.sync kernel."""
+    caches are staged as bf16 pages and served by the tcgen05 kernel (b200attn_paged_prefill_fp8_staged) when the
+    call has enough new tokens per sequence to pay for the staging (`_fp8_prefill_staged`); otherwise, and without a
+    staging buffer, fp8 caches run on the mma.sync kernel."""
     lib = _lib.load()
     _need_cuda(q, k_cache, v_cache, block_table, seq_lens, query_start_loc)
     if out is None:
@@ -438,7 +450,8 @@ def paged_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         raise ValueError("query_start_loc/seq_lens must be int32")
     batch = query_start_loc.numel() - 1
     ks, vs, sn = _scales(k_scale, v_scale, fp8)
-    if fp8 and staging is not None and max_seq_len > 0 and batch > 0 and _fp8_prefill_staged_enabled():
+    if (fp8 and staging is not None and max_seq_len > 0 and batch > 0
+            and _fp8_prefill_staged(q.shape[0], batch, q.shape[1] // hkv)):
         staging.ensure(prefill_staging_bytes(batch, max_seq_len, total_kv_tokens, hkv, d, bs))
         off = (-staging.ptr) % 1024  # the library wants the staging 1 KiB aligned
         check("b200attn_paged_prefill_fp8_staged", lib.b200attn_paged_prefill_fp8_staged(
