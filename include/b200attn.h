@@ -342,7 +342,7 @@ B200ATTN_API int b200attn_paged_prefill(
 /*
  * b200attn_paged_prefill for FP8 (e4m3) caches on the tcgen05 / TMEM kernel. Same computation, same reference
  * call site (vllm/v1/attention/backends/flash_attn.py:758-819 with an fp8 kv_cache_dtype; FlashInfer's fp8
- * prefill, vllm/v1/attention/backends/flashinfer.py:1600-1690). Two steps on `stream`:
+ * prefill branch, vllm/v1/attention/backends/flashinfer.py:1514-1688). Two steps on `stream`:
  *   1. the e4m3 pages that the `batch` sequences own are rewritten as bf16 pages in `staging` (the e4m3 VALUES,
  *      which bf16 holds exactly; slots at or past seq_lens[b] as zeros) together with their own block table;
  *   2. the tcgen05 prefill kernel runs over the staged pages with k_scale folded into the softmax scale and
